@@ -1,0 +1,195 @@
+/* prisma_b200 — C ABI of the batched, device-resident packet-routing environment (libprisma_b200.so).
+ *
+ * This is the drop-in boundary for PRISMA's environment step loop.  What each entry point replaces
+ * in the reference (paths relative to the reference checkout):
+ *
+ *   prb_create / prb_destroy   the ns-3 process launch + topology build
+ *                              (prisma/source/run_ns3.py:7-78, prisma/ns3/sim.cc:122-700) and the
+ *                              per-node ZMQ bind (prisma/ns3_model/ns3env.py:41-60,397-402)
+ *   prb_reset                  Ns3Env.reset (prisma/ns3_model/ns3env.py:422-426) for every env
+ *   prb_step                   Ns3Env.step (ns3env.py:417-420) == Ns3ZmqBridge.send_actions +
+ *                              rx_env_state (ns3env.py:179-247) == OpenGymInterface::NotifyCurrentState
+ *                              (ns3-gym/src/opengym/model/opengym_interface.cc:213-286): one call advances
+ *                              EVERY environment to its next valid Notify()
+ *   prb_run                    the same loop with the agent hook evaluated on the device
+ *                              (Forwarder.take_action, prisma/source/forwarder.py:171-195): sp / table agents
+ *   prb_set_policy             Forwarder agent selection (forwarder.py:171-195, argument_parser.py:64-70)
+ *   prb_set_inject_trace       replaces PoissonGeneratorApplication's RNG draws by a recorded trace
+ *                              (prisma/ns3/poisson-application.cc:265-358) — parity / replay mode
+ *   prb_counters               PacketManager::getInfo's global statistics
+ *                              (prisma/ns3/packet-manager.cc:119-176, compute-stats-v2.cc:115-266)
+ *   prb_seconds_to_ns ...      ns-3 Time / DataRate arithmetic used to derive the integer-ns inputs
+ *                              (ns3-gym/src/core/model/nstime.h:235-236,456-475, int64x64-128.{h,cc},
+ *                               ns3-gym/src/network/utils/data-rate.cc:235-240)
+ *
+ * Conventions: every call returns 0 or a negative prb_status; prb_last_error() gives the message of the
+ * last failure on the calling thread.  A handle is bound to one CUDA device and one stream; handles are
+ * not thread-safe, distinct handles are independent.  Pointers are HOST pointers unless the parameter
+ * name ends in _dev.  There is no CPU execution path: without a CUDA device prb_create fails.
+ */
+#ifndef PRISMA_B200_H
+#define PRISMA_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PRB_MAX_K 16          /* overlay degree limit (observation = 1 + k words) */
+#define PRB_MAX_NODES 250
+#define PRB_LASTHOP_NONE 1000 /* prisma/ns3/poisson-application.cc:309 */
+#define PRB_MAX_LOST 8
+
+enum prb_status { PRB_OK = 0, PRB_EINVAL = -1, PRB_ECUDA = -2, PRB_ENOMEM = -3, PRB_ESTATE = -4, PRB_EOVERFLOW = -5 };
+
+/* packet types: prisma/ns3/enum-and-constants.h:5-11 */
+enum { PRB_DATA = 0, PRB_BIG_SIGN = 1, PRB_SMALL_SIGN = 2, PRB_PING_FWD = 3, PRB_PING_BACK = 4 };
+/* event-log record kinds */
+enum { PRB_EV_INJ = 0, PRB_EV_ARR = 1, PRB_EV_ENQ = 2, PRB_EV_DRP = 3, PRB_EV_TXB = 4, PRB_EV_RCV = 5 };
+/* agent hooks evaluated on the device (prb_run) */
+enum { PRB_POLICY_ZERO = 0, PRB_POLICY_TABLE = 1, PRB_POLICY_TRACE = 2, PRB_POLICY_RANDOM = 3 };
+enum { PRB_INJECT_TRACE = 0, PRB_INJECT_PHILOX = 1 };
+/* env error bits (prb_errors) */
+enum { PRB_ERR_POOL = 1, PRB_ERR_LOG = 2, PRB_ERR_PING_WINDOW = 4, PRB_ERR_TRACE = 8, PRB_ERR_SEQ = 16 };
+
+typedef struct prb_config
+{
+  int32_t num_envs;                /* E independent environments on this handle                         */
+  int32_t n_nodes;                 /* N underlay nodes                                   sim.cc:303-305 */
+  int32_t n_overlay;               /* M overlay nodes                                    sim.cc:304     */
+  const uint8_t *phys_adj;         /* [N*N] physical adjacency                           sim.cc:274-276 */
+  const uint8_t *overlay_adj;      /* [M*M] overlay adjacency                            sim.cc:277-279 */
+  const int32_t *map_overlay;      /* [N] overlay index or -1                            sim.cc:281-282 */
+  const uint64_t *traffic_bps;     /* [N*N] ceil(rate*load_factor), 0 = no flow          sim.cc:623     */
+  const int32_t *route_out;        /* [N*N] optional: out link of x towards d, else global routing  sim.cc:683 */
+  const double *opt_rejected;      /* [N*N] optional                                     sim.cc:284-285 */
+  uint64_t link_cap_bps;           /* link_cap                                           sim.cc:422     */
+  int64_t link_delay_ns;           /* link_delay                                         sim.cc:423     */
+  uint32_t packet_size;            /* packet_size (payload bytes)                        sim.cc:150     */
+  uint32_t max_out_buffer_size;    /* max_out_buffer_size, bytes                         sim.cc:424     */
+  int64_t sim_time_ns;             /* simTime                                            sim.cc:703     */
+  int64_t ping_interval_ns;        /* pingPacketIntervalTime      data-packet-manager.cc:117-122        */
+  uint32_t moving_average_size;    /* movingAverageObsSize                               sim.cc:549     */
+  int32_t ping_as_obs;             /* pingAsObs                                          sim.cc:548     */
+  int32_t activate_underlay_traffic; /* activateUnderlayTraffic                          sim.cc:505-507 */
+  int32_t train;                   /* train: one small-signalling packet per hop   packet-routing-gym.cc:205-208 */
+  int32_t signaling_type;          /* 0 ideal, 1 NN, 2 target, 3 digital_twin            sim.cc:371-393 */
+  int32_t opt_agent;               /* agent_type == "opt"                                sim.cc:376-377 */
+  double loss_penalty;             /* loss_penalty                                       sim.cc:246-247 */
+  uint64_t seed;                   /* synthetic traffic: Philox key                                      */
+  uint64_t env_id_base;            /* synthetic traffic: id of env 0 (env e draws stream env_id_base+e)  */
+  int32_t pool_capacity;           /* packet records per env, 0 = derive from the topology              */
+  int32_t lanes_per_env;           /* 0 = default (32: one warp per environment)                        */
+} prb_config;
+
+/* one record of the parity event log (same vocabulary as the reference harness) — 64 bytes */
+typedef struct prb_event
+{
+  int64_t t_ns;
+  int32_t kind;      /* PRB_EV_* */
+  int32_t node;      /* node where the record is taken (traffic node of i = N+i) */
+  int32_t link;      /* directed link id (access link of node i = L+i) */
+  int32_t pad_;
+  int64_t uid;       /* data packets: uid, others -1 */
+  int32_t size;      /* bytes incl. PPP */
+  int32_t type, src, dst, last_hop, next_hop, valable;
+  int32_t qbytes;    /* ENQ/DRP/TXB: queue bytes after the operation, else -1 */
+} prb_event;
+
+/* one Gym step (one valid Notify()) of one environment — 208 bytes, all fields 4- or 8-byte */
+typedef struct prb_step_rec
+{
+  int64_t t_ns;         /*   0 simulated time of the step                                              */
+  int64_t uid;          /*   8 data: packet uid; small signalling: uid it reports; else -1              */
+  double hop_time;      /*  16 now - time of the packet's previous decision, s (forwarder.py:360)       */
+  int32_t node;         /*  24 underlay id of the stepping overlay node                                 */
+  int32_t overlay;      /*  28 its overlay index == the reference's per-node env index                  */
+  int32_t ptype;        /*  32 PRB_DATA / PRB_SMALL_SIGN / PRB_BIG_SIGN                                  */
+  int32_t done;         /*  36 getGameOver (data-packet-manager.cc:224-227)                             */
+  int32_t action;       /*  40 action applied (-1: Forwarder ignores the policy, forwarder.py:149-150)  */
+  int32_t need_action;  /*  44 1: prb_step consumes actions_dev[e] for this record                      */
+  int32_t nobs;         /*  48                                                                          */
+  int32_t is_new;       /*  52 first time the agents see this packet (forwarder.py:316-317)             */
+  int32_t prev_node;    /*  56 underlay id of the previous decision maker, -1 if new                    */
+  int32_t n_lost;       /*  60 lost uids flushed with this step (data-packet-manager.cc:229-237)        */
+  float e2e_delay;      /*  64 info field 0 (packet-manager.cc:121-122)                                 */
+  int32_t valid;        /*  68 1: this env produced a step; 0: it reached simTime (obs[0] == -1 sentinel) */
+  int32_t obs[1 + PRB_MAX_K]; /* 72 */
+  int32_t pad_;         /* 140 */
+  int64_t lost_uid[PRB_MAX_LOST]; /* 144 most recent first */
+} prb_step_rec;
+
+/* per-environment statistics (compute-stats-v2.cc:59-72,115-266) — 200 bytes */
+typedef struct prb_counters
+{
+  int64_t overlay_injected, overlay_arrived, overlay_lost;
+  int64_t underlay_injected, underlay_arrived, underlay_lost;
+  int64_t bytes_data, bytes_signaling;
+  int64_t n_e2e, n_cost, n_underlay_e2e, n_underlay_cost;
+  float sum_e2e, sum_cost, sum_underlay_e2e, sum_underlay_cost;      /* float32 sums in push order */
+  float avg_e2e, avg_cost, avg_underlay_e2e, avg_underlay_cost, signaling_overhead;
+  int32_t errors;           /* PRB_ERR_* bits, must be 0 */
+  int64_t packet_hops;      /* Receive() on switch<->switch devices, any packet type */
+  int64_t data_hops;        /* same, data packets only */
+  int64_t env_steps;        /* valid Notify() calls */
+  int64_t decisions;        /* steps where the agent chose a next hop */
+  int64_t events;           /* simulator events executed */
+  int64_t vanished;         /* action >= k (data-packet-manager.cc:294-297) */
+  int64_t end_ns;           /* simulated clock */
+} prb_counters;
+
+typedef struct prb_env prb_env;
+
+const char *prb_last_error (void);
+const char *prb_version (void);
+
+/* ---- ns-3 arithmetic on the host (inputs of prb_config are integer ns / bit/s) ---- */
+int64_t prb_seconds_to_ns (double seconds);
+double prb_ns_to_seconds (int64_t ns);
+int64_t prb_tx_time_ns (uint32_t bytes, uint64_t bps);
+/* directed links in device-creation order (sim.cc:414-433); returns L, fills from/to when non-NULL */
+int32_t prb_build_links (int32_t n, const uint8_t *adj, int32_t *from, int32_t *to);
+/* ns-3 global routing as the reference uses it: out link of node x towards node d, -1 on the diagonal */
+int32_t prb_global_routes (int32_t n, const uint8_t *adj, int32_t *route_out);
+
+/* ---- environment ---- */
+int prb_create (const prb_config *cfg, int device, void *cuda_stream, prb_env **out);
+int prb_destroy (prb_env *env);
+int prb_reset (prb_env *env);
+int prb_num_links (prb_env *env);        /* L (switch<->switch, directed) */
+int prb_state_bytes (prb_env *env, int64_t *blob_bytes, int64_t *pool_bytes);
+
+/* traffic: recorded injections shared by every env (replay), or NULL/0 to go back to Philox */
+int prb_set_inject_trace (prb_env *env, int64_t n, const int64_t *t_ns, const int32_t *src, const int32_t *dst,
+                          const int64_t *uid, const uint8_t *valable, const uint8_t *rejected);
+/* agent hook evaluated on the device: TABLE data[M*M] (row = stepping overlay node, column = obs[0]);
+ * TRACE data[n] actions in decision order; RANDOM uses seed (+ env index); data_dev != 0: data is a DEVICE
+ * pointer that stays owned by the caller */
+int prb_set_policy (prb_env *env, int kind, const int32_t *data, int64_t n, uint64_t seed);
+
+/* parity logs: per-env capacities (records); 0 disables */
+int prb_enable_log (prb_env *env, int64_t event_capacity, int64_t step_capacity);
+int prb_read_events (prb_env *env, int32_t e, prb_event *out, int64_t capacity, int64_t *n);
+int prb_read_steps (prb_env *env, int32_t e, prb_step_rec *out, int64_t capacity, int64_t *n);
+
+/* fused-agent mode: advance every env until simulated time until_ns (or simTime) */
+int prb_run (prb_env *env, int64_t until_ns);
+/* Gym mode: apply actions_dev[e] (int32, device; may be NULL on the first call) to the pending step of
+ * every env that asked for one, then advance every env to its next valid Notify(); out_dev[e] (device,
+ * E records) receives it */
+int prb_step (prb_env *env, const int32_t *actions_dev, prb_step_rec *out_dev);
+/* the same through host buffers (copies inside) */
+int prb_step_host (prb_env *env, const int32_t *actions, prb_step_rec *out);
+
+int prb_counters_host (prb_env *env, prb_counters *out /* [E] */);
+int prb_counters_dev (prb_env *env, prb_counters *out_dev /* [E] device */);
+int prb_queue_bytes (prb_env *env, int32_t e, int32_t *out /* [L] */);
+int prb_sync (prb_env *env);
+/* number of kernel launches issued by this handle so far */
+int64_t prb_launch_count (prb_env *env);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -187,6 +187,27 @@ class EnvConfig:
             return float(self.loss_penalty)
         return (((self.max_out_buffer_size + 512 + 30) * 8) / self.link_cap + 0.001) * num_nodes
 
+    def abi_params(self, arrays: "Optional[EnvArrays]" = None, **over) -> dict:
+        """The prb_config fields (include/prisma_b200.h) as a dict: integer-ns times through the library's
+        ns-3 `Seconds()` arithmetic, the float32 `pingPacketIntervalTime` of sim.cc:201, the derived loss
+        penalty of argument_parser.py:163."""
+        from . import _abi
+        L = _abi.lib()
+        a = arrays if arrays is not None else self.load()
+        p = dict(num_envs=self.num_envs, n_nodes=a.n_nodes, n_overlay=a.n_overlay, phys_adj=a.phys_adj,
+                 overlay_adj=a.overlay_adj, map_overlay=a.map_overlay, traffic_bps=a.traffic_bps,
+                 opt_rejected=a.opt_rejected if self.agent_type == "opt" else None,
+                 link_cap_bps=int(self.link_cap), link_delay_ns=L.prb_seconds_to_ns(float(self.link_delay) * 0.001),
+                 packet_size=int(self.packet_size), max_out_buffer_size=int(self.max_out_buffer_size),
+                 sim_time_ns=L.prb_seconds_to_ns(float(self.simTime)),
+                 ping_interval_ns=L.prb_seconds_to_ns(float(np.float32(self.pingPacketIntervalTime))),
+                 moving_average_size=int(self.movingAverageObsSize), ping_as_obs=int(self.pingAsObs),
+                 activate_underlay_traffic=int(self.activateUnderlayTraffic), train=int(self.train),
+                 signaling_type=self.signaling_type, opt_agent=1 if self.agent_type == "opt" else 0,
+                 loss_penalty=self.derived_loss_penalty(a.n_overlay), seed=int(self.seed), env_id_base=0)
+        p.update(over)
+        return p
+
     def effective_signaling(self) -> bool:
         """sim.cc:373-375: sp / opt agents and ideal signalling switch the control plane off."""
         return bool(self.signalingSim) and self.agent_type not in ("sp", "opt") and self.signaling_type != "ideal"

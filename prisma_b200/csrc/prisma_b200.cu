@@ -1,0 +1,730 @@
+/* prisma_b200 — sm_100a kernels and the C ABI of include/prisma_b200.h.
+ *
+ * Execution model: one group of G lanes (default G = 32, a full warp) owns one environment.  The
+ * environment's state is one contiguous blob in HBM (layout: model.h) plus a packet-record pool.  Per
+ * simulated event every lane scans its share of the pending-timer slots, the group agrees on the
+ * minimum (timestamp, scheduler uid) with warp reductions, and the group leader executes the event
+ * (sim_core.cuh).  In run mode the blob is staged in shared memory for the whole launch, so HBM sees one
+ * read and one write of the blob per launch plus the packet records that move.
+ *
+ * There is no host execution path in this file: every entry point that advances an environment launches
+ * a kernel.
+ */
+#include <cuda_runtime.h>
+
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "model.h"
+
+using namespace prb;
+
+#define PRB_VERSION "prisma_b200 0.1 (sm_100a)"
+
+static thread_local std::string g_err;
+
+static int
+fail (int code, const std::string &msg)
+{
+  g_err = msg;
+  return code;
+}
+
+#define CUDA_TRY(expr)                                                                                   \
+  do                                                                                                     \
+    {                                                                                                    \
+      cudaError_t e_ = (expr);                                                                           \
+      if (e_ != cudaSuccess)                                                                             \
+        return fail (PRB_ECUDA, std::string (#expr) + ": " + cudaGetErrorString (e_));                   \
+    }                                                                                                    \
+  while (0)
+
+/* ------------------------------------------------------------------------------------------------
+ * Device side
+ * ---------------------------------------------------------------------------------------------- */
+
+struct LaunchArgs
+{
+  char *blobs;            /* [E * blob_bytes] */
+  Pkt *pools;             /* [E * P] */
+  prb_event *ev_logs;     /* [E * ev_cap] or null */
+  prb_step_rec *st_logs;  /* [E * st_cap] or null */
+  const int32_t *actions; /* gym mode, may be null */
+  prb_step_rec *out;      /* gym mode */
+  int64_t until_ns;
+};
+
+/* minimum (ts, seq) over the lanes of a group; every lane of the group gets the winner's slot */
+template <int G>
+__device__ __forceinline__ void
+group_min (unsigned gmask, int64_t ts, uint32_t seq, int slot, int64_t &mts, uint32_t &mseq, int &mslot)
+{
+  uint32_t hi = (uint32_t) ((uint64_t) ts >> 32), lo = (uint32_t) (uint64_t) ts;
+  uint32_t mhi = __reduce_min_sync (gmask, hi);
+  uint32_t mlo = __reduce_min_sync (gmask, hi == mhi ? lo : 0xFFFFFFFFu);
+  bool cand = hi == mhi && lo == mlo;
+  uint32_t ms = __reduce_min_sync (gmask, cand ? seq : 0xFFFFFFFFu);
+  unsigned b = __ballot_sync (gmask, cand && seq == ms);
+  int src = __ffs (b) - 1;
+  mslot = __shfl_sync (gmask, slot, src);
+  mts = (int64_t) (((uint64_t) mhi << 32) | mlo);
+  mseq = ms;
+}
+
+/* per-lane scan of timer slots first, first+G, ... < last: keeps the (ts, seq) minimum */
+template <int G>
+__device__ __forceinline__ void
+scan_slots (const int64_t *t_ts, const uint32_t *t_seq, int first, int last, int64_t &bts, uint32_t &bseq, int &bslot)
+{
+  for (int s = first; s < last; s += G)
+    {
+      int64_t t = t_ts[s];
+      if (t > bts) continue;
+      if (t == T_IDLE) continue;
+      uint32_t q = t_seq[s];
+      if (t < bts || q < bseq)
+        {
+          bts = t; bseq = q; bslot = s;
+        }
+    }
+}
+
+/* Advance every environment: run mode until `until_ns`, gym mode until the next valid Notify().
+ * SMEM: the env blob lives in shared memory during the launch. */
+template <int G, bool LOG, bool SMEM>
+__global__ void __launch_bounds__ (128)
+k_advance (const __grid_constant__ Static st, const LaunchArgs a)
+{
+  extern __shared__ __align__ (16) char smem[];
+  constexpr int GROUPS_PER_WARP = 32 / G;
+  const int lane = threadIdx.x & 31;
+  const int gl = lane % G;                                   /* lane inside the group */
+  const int group_in_block = threadIdx.x / G;
+  const int env = blockIdx.x * (blockDim.x / G) + group_in_block;
+  const unsigned gmask = G == 32 ? 0xFFFFFFFFu : (((1u << G) - 1u) << ((lane / G) * G));
+  (void) GROUPS_PER_WARP;
+  bool active = env < st.E;
+  char *gblob = a.blobs + (size_t) (active ? env : 0) * st.blob_bytes;
+  char *blob = gblob;
+  if (SMEM)
+    {
+      blob = smem + (size_t) group_in_block * st.blob_bytes;
+      if (active)
+        {
+          const uint4 *src = (const uint4 *) gblob;
+          uint4 *dst = (uint4 *) blob;
+          for (int i = gl; i < st.blob_bytes / 16; i += G) dst[i] = src[i];
+        }
+      __syncwarp (gmask);
+    }
+  Dyn d;
+  bind_state (st, blob, d);
+  d.pool = a.pools + (size_t) (active ? env : 0) * st.P;
+  d.ev_log = LOG && a.ev_logs ? a.ev_logs + (size_t) (active ? env : 0) * st.ev_cap : nullptr;
+  d.st_log = LOG && a.st_logs ? a.st_logs + (size_t) (active ? env : 0) * st.st_cap : nullptr;
+  Scal *sc = d.sc;
+  __shared__ prb_step_rec scratch_rec[128 / G];
+  prb_step_rec *rec = (st.mode == MODE_GYM && a.out) ? &a.out[active ? env : 0] : &scratch_rec[group_in_block];
+  Sim<LOG> sim (st, d, env, rec);
+  const int64_t stop = st.sim_time_ns;
+  const int64_t until = a.until_ns;
+
+  if (active && gl == 0)
+    {
+      if (st.mode == MODE_GYM) rec->valid = 0;
+      if (sc->finished)
+        active = false;
+      else
+        {
+          if (!sc->started) sim.start ();
+          if (sc->pending) sim.resume (a.actions ? a.actions[env] : 0);
+        }
+    }
+  active = __shfl_sync (gmask, active ? 1 : 0, (lane / G) * G) != 0;
+  __syncwarp (gmask);
+
+  /* flows are scanned lazily: a lane rescans its flow slots only after one of them fired */
+  const int flow0 = 2 * st.LA + st.M;
+  int64_t fts = T_IDLE; uint32_t fseq = 0xFFFFFFFFu; int fslot = -1;
+  if (active) scan_slots<G> (d.t_ts, d.t_seq, flow0 + gl, st.S, fts, fseq, fslot);
+
+  while (__any_sync (gmask, active))
+    {
+      int64_t bts = fts; uint32_t bseq = fseq; int bslot = fslot;
+      if (active) scan_slots<G> (d.t_ts, d.t_seq, gl, flow0, bts, bseq, bslot);
+      int64_t mts; uint32_t mseq; int mslot;
+      group_min<G> (gmask, bts, bseq, bslot, mts, mseq, mslot);
+      if (!active) continue;
+      int status = ST_CONTINUE;
+      bool stop_now = false;
+      if (mts == T_IDLE)
+        {
+          if (gl == 0) sc->finished = 1;
+          stop_now = true;
+        }
+      else if (mts > stop || (mts == stop && mseq > sc->stop_seq))
+        {
+          if (gl == 0)
+            {
+              sc->now = stop;
+              sc->finished = 1;
+            }
+          stop_now = true;
+        }
+      else if (mts >= until && until < stop)
+        stop_now = true;
+      if (stop_now)
+        {
+          active = false;
+          continue;
+        }
+      if (gl == 0) status = sim.handle (mslot, mts);
+      __syncwarp (gmask);
+      status = __shfl_sync (gmask, status, (lane / G) * G);
+      if (mslot >= flow0 && mslot == fslot)
+        {
+          fts = T_IDLE; fseq = 0xFFFFFFFFu; fslot = -1;
+          scan_slots<G> (d.t_ts, d.t_seq, flow0 + gl, st.S, fts, fseq, fslot);
+        }
+      if (status == ST_PAUSE) active = false;
+    }
+  __syncwarp (gmask);
+  if (env < st.E && gl == 0)
+    {
+      if (!sc->pending && until < stop && sc->now < until && !sc->finished) sc->now = until;
+      sc->c.end_ns = sc->now;
+    }
+  if (SMEM)
+    {
+      __syncwarp (gmask);
+      if (env < st.E)
+        {
+          const uint4 *src = (const uint4 *) blob;
+          uint4 *dst = (uint4 *) gblob;
+          for (int i = gl; i < st.blob_bytes / 16; i += G) dst[i] = src[i];
+        }
+    }
+}
+
+/* reset: every env gets the initial blob, its policy RNG, and a fully linked free list */
+__global__ void
+k_reset (const __grid_constant__ Static st, char *blobs, Pkt *pools, const char *blob0)
+{
+  const int64_t words = st.blob_bytes / 16;
+  const int64_t total = words * st.E;
+  const int64_t stride = (int64_t) gridDim.x * blockDim.x;
+  const int64_t tid = (int64_t) blockIdx.x * blockDim.x + threadIdx.x;
+  for (int64_t i = tid; i < total; i += stride)
+    ((uint4 *) blobs)[i] = ((const uint4 *) blob0)[i % words];
+  const int64_t np = (int64_t) st.P * st.E;
+  for (int64_t i = tid; i < np; i += stride)
+    {
+      int k = (int) (i % st.P);
+      pools[i].next = (uint16_t) (k + 1 < st.P ? k + 1 : NIL);
+    }
+}
+
+__global__ void
+k_seed_policy (const __grid_constant__ Static st, char *blobs)
+{
+  int e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= st.E) return;
+  Scal *sc = (Scal *) (blobs + (size_t) e * st.blob_bytes + st.off_scal);
+  uint64_t r = (st.policy_seed + (uint64_t) e) * 0x9E3779B97F4A7C15ULL + 0x1234567ULL;
+  sc->pol_rng = r ? r : 1;
+  sc->pol_pos = 0;
+}
+
+__global__ void
+k_counters (const __grid_constant__ Static st, const char *blobs, prb_counters *out)
+{
+  int e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= st.E) return;
+  const Scal *sc = (const Scal *) (blobs + (size_t) e * st.blob_bytes + st.off_scal);
+  prb_counters c = sc->c;
+  finalize_counters (c);
+  out[e] = c;
+}
+
+__global__ void
+k_queue_bytes (const __grid_constant__ Static st, const char *blobs, int e, int32_t *out)
+{
+  int l = blockIdx.x * blockDim.x + threadIdx.x;
+  if (l >= st.L) return;
+  const uint32_t *q = (const uint32_t *) (blobs + (size_t) e * st.blob_bytes + st.off_q_bytes);
+  out[l] = (int32_t) q[l];
+}
+
+__global__ void
+k_log_counts (const __grid_constant__ Static st, const char *blobs, int e, int64_t *out)
+{
+  const Scal *sc = (const Scal *) (blobs + (size_t) e * st.blob_bytes + st.off_scal);
+  out[0] = sc->ev_n;
+  out[1] = sc->st_n;
+}
+
+/* ------------------------------------------------------------------------------------------------
+ * Host side
+ * ---------------------------------------------------------------------------------------------- */
+
+struct prb_env
+{
+  HostModel hm;
+  Static dst;                 /* Static with DEVICE table pointers */
+  HostTrace tr;
+  int device = 0;
+  cudaStream_t stream = nullptr;
+  int G = 32;
+  int max_smem = 0;
+  char *d_tables = nullptr;   /* one allocation for all read-only tables */
+  char *d_blob0 = nullptr;
+  char *d_blobs = nullptr;
+  Pkt *d_pools = nullptr;
+  prb_event *d_ev = nullptr;
+  prb_step_rec *d_st = nullptr;
+  int32_t *d_pol = nullptr;   int64_t pol_cap = 0;
+  char *d_trace = nullptr;
+  int32_t *d_flow_first = nullptr;
+  prb_counters *d_counters = nullptr;
+  prb_step_rec *d_out = nullptr;
+  int32_t *d_actions = nullptr;
+  int64_t *d_scratch = nullptr;
+  int64_t launches = 0;
+  bool log_on = false;
+};
+
+template <typename T>
+static const T *
+place (std::vector<char> &buf, const std::vector<T> &v, size_t &off_out)
+{
+  size_t off = (buf.size () + 15) / 16 * 16;
+  buf.resize (off + std::max<size_t> (v.size () * sizeof (T), 16));
+  if (!v.empty ()) memcpy (buf.data () + off, v.data (), v.size () * sizeof (T));
+  off_out = off;
+  return nullptr;
+}
+
+static int
+upload_tables (prb_env *env)
+{
+  HostModel &hm = env->hm;
+  std::vector<char> buf;
+  size_t o[16];
+  place (buf, hm.link_from, o[0]); place (buf, hm.link_to, o[1]); place (buf, hm.link_rc, o[2]);
+  place (buf, hm.tx_ns, o[3]); place (buf, hm.szc_bytes, o[4]); place (buf, hm.route, o[5]);
+  place (buf, hm.map_overlay, o[6]); place (buf, hm.o2u, o[7]); place (buf, hm.agent_k, o[8]);
+  place (buf, hm.agent_nbr, o[9]); place (buf, hm.agent_sign_szc, o[10]); place (buf, hm.flow_src, o[11]);
+  place (buf, hm.flow_dst, o[12]); place (buf, hm.flow_mean_s, o[13]); place (buf, hm.opt_rejected, o[14]);
+  CUDA_TRY (cudaMalloc (&env->d_tables, buf.size ()));
+  CUDA_TRY (cudaMemcpyAsync (env->d_tables, buf.data (), buf.size (), cudaMemcpyHostToDevice, env->stream));
+  CUDA_TRY (cudaStreamSynchronize (env->stream));
+  Static &s = env->dst;
+  s = hm.st;
+  char *b = env->d_tables;
+  s.link_from = (const int16_t *) (b + o[0]); s.link_to = (const int16_t *) (b + o[1]);
+  s.link_rc = (const uint8_t *) (b + o[2]); s.tx_ns = (const int64_t *) (b + o[3]);
+  s.szc_bytes = (const uint16_t *) (b + o[4]); s.route = (const int16_t *) (b + o[5]);
+  s.map_overlay = (const int16_t *) (b + o[6]); s.o2u = (const int16_t *) (b + o[7]);
+  s.agent_k = (const uint8_t *) (b + o[8]); s.agent_nbr = (const int16_t *) (b + o[9]);
+  s.agent_sign_szc = (const uint8_t *) (b + o[10]); s.flow_src = (const int16_t *) (b + o[11]);
+  s.flow_dst = (const int16_t *) (b + o[12]); s.flow_mean_s = (const double *) (b + o[13]);
+  s.opt_rejected = hm.opt_rejected.empty () ? nullptr : (const double *) (b + o[14]);
+  s.pol_data = nullptr; s.pol_n = 0;
+  s.tr_t = nullptr; s.tr_uid = nullptr; s.tr_flags = nullptr; s.tr_next = nullptr; s.flow_first = nullptr;
+  return PRB_OK;
+}
+
+template <int G, bool LOG>
+static int
+launch_advance_g (prb_env *env, const LaunchArgs &a)
+{
+  const Static &st = env->dst;
+  const int threads = 128;
+  const int envs_per_block = threads / G;
+  const int blocks = (st.E + envs_per_block - 1) / envs_per_block;
+  size_t smem = (size_t) envs_per_block * st.blob_bytes;
+  /* shared-memory staging pays when the launch executes many events per env (run mode) and the blobs of
+   * a block fit; gym-mode launches execute a handful of events and work on the blob in place */
+  bool use_smem = st.mode == MODE_RUN && smem + sizeof (prb_step_rec) * envs_per_block + 1024 <= (size_t) env->max_smem;
+  if (use_smem)
+    {
+      auto k = k_advance<G, LOG, true>;
+      CUDA_TRY (cudaFuncSetAttribute (k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
+      k<<<blocks, threads, smem, env->stream>>> (st, a);
+    }
+  else
+    k_advance<G, LOG, false><<<blocks, threads, 0, env->stream>>> (st, a);
+  CUDA_TRY (cudaGetLastError ());
+  env->launches++;
+  return PRB_OK;
+}
+
+static int
+launch_advance (prb_env *env, const LaunchArgs &a)
+{
+  bool log = env->log_on;
+  switch (env->G)
+    {
+    case 32: return log ? launch_advance_g<32, true> (env, a) : launch_advance_g<32, false> (env, a);
+    case 16: return log ? launch_advance_g<16, true> (env, a) : launch_advance_g<16, false> (env, a);
+    case 8: return log ? launch_advance_g<8, true> (env, a) : launch_advance_g<8, false> (env, a);
+    default: return fail (PRB_EINVAL, "lanes_per_env must be 8, 16 or 32");
+    }
+}
+
+extern "C" {
+
+const char *prb_last_error (void) { return g_err.c_str (); }
+const char *prb_version (void) { return PRB_VERSION; }
+int64_t prb_seconds_to_ns (double s) { return host_seconds_to_ns (s); }
+
+double
+prb_ns_to_seconds (int64_t ns)
+{
+  Static st;
+  host_invert_1e9 (&st.inv1e9_hi, &st.inv1e9_lo);
+  return ns < 0 ? -ns_to_seconds (st, -ns) : ns_to_seconds (st, ns);
+}
+
+int64_t prb_tx_time_ns (uint32_t bytes, uint64_t bps) { return host_tx_time_ns (bytes, bps); }
+int32_t prb_build_links (int32_t n, const uint8_t *adj, int32_t *from, int32_t *to) { return host_build_links (n, adj, from, to); }
+int32_t prb_global_routes (int32_t n, const uint8_t *adj, int32_t *route_out) { return host_global_routes (n, adj, route_out); }
+
+int
+prb_destroy (prb_env *env)
+{
+  if (!env) return PRB_OK;
+  cudaSetDevice (env->device);
+  cudaStreamSynchronize (env->stream);
+  cudaFree (env->d_tables); cudaFree (env->d_blob0); cudaFree (env->d_blobs); cudaFree (env->d_pools);
+  cudaFree (env->d_ev); cudaFree (env->d_st); cudaFree (env->d_pol); cudaFree (env->d_trace);
+  cudaFree (env->d_flow_first); cudaFree (env->d_counters); cudaFree (env->d_out); cudaFree (env->d_actions);
+  cudaFree (env->d_scratch);
+  delete env;
+  return PRB_OK;
+}
+
+int
+prb_create (const prb_config *cfg, int device, void *cuda_stream, prb_env **out)
+{
+  if (!cfg || !out) return fail (PRB_EINVAL, "null argument");
+  *out = nullptr;
+  int ndev = 0;
+  if (cudaGetDeviceCount (&ndev) != cudaSuccess || ndev <= 0)
+    return fail (PRB_ECUDA, "no CUDA device: prisma_b200 has no CPU execution path");
+  if (device < 0 || device >= ndev) return fail (PRB_EINVAL, "bad device index");
+  prb_env *env = new prb_env ();
+  if (!build_model (*cfg, env->hm))
+    {
+      std::string msg = env->hm.error;
+      delete env;
+      return fail (PRB_EINVAL, msg);
+    }
+  env->device = device;
+  env->stream = (cudaStream_t) cuda_stream;
+  env->G = cfg->lanes_per_env > 0 ? cfg->lanes_per_env : 32;
+  if (env->G != 32 && env->G != 16 && env->G != 8)
+    {
+      delete env;
+      return fail (PRB_EINVAL, "lanes_per_env must be 8, 16 or 32");
+    }
+  int rc = PRB_OK;
+  auto guard = [&] (int r) { if (r != PRB_OK) { prb_destroy (env); } return r; };
+  if (cudaSetDevice (device) != cudaSuccess) return guard (fail (PRB_ECUDA, "cudaSetDevice failed"));
+  cudaDeviceGetAttribute (&env->max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, device);
+  if ((rc = upload_tables (env)) != PRB_OK) return guard (rc);
+  const Static &st = env->dst;
+  auto alloc = [&] (void **p, size_t bytes) -> int {
+    cudaError_t e = cudaMalloc (p, bytes);
+    if (e != cudaSuccess) return fail (PRB_ENOMEM, std::string ("cudaMalloc: ") + cudaGetErrorString (e));
+    return PRB_OK;
+  };
+  if ((rc = alloc ((void **) &env->d_blob0, st.blob_bytes)) != PRB_OK) return guard (rc);
+  if ((rc = alloc ((void **) &env->d_blobs, (size_t) st.blob_bytes * st.E)) != PRB_OK) return guard (rc);
+  if ((rc = alloc ((void **) &env->d_pools, sizeof (Pkt) * (size_t) st.P * st.E)) != PRB_OK) return guard (rc);
+  if ((rc = alloc ((void **) &env->d_counters, sizeof (prb_counters) * (size_t) st.E)) != PRB_OK) return guard (rc);
+  if ((rc = alloc ((void **) &env->d_out, sizeof (prb_step_rec) * (size_t) st.E)) != PRB_OK) return guard (rc);
+  if ((rc = alloc ((void **) &env->d_actions, sizeof (int32_t) * (size_t) st.E)) != PRB_OK) return guard (rc);
+  if ((rc = alloc ((void **) &env->d_scratch, 4096)) != PRB_OK) return guard (rc);
+  if ((rc = alloc ((void **) &env->d_flow_first, sizeof (int32_t) * std::max (st.F, 1))) != PRB_OK) return guard (rc);
+  if (cudaMemcpyAsync (env->d_blob0, env->hm.blob0.data (), st.blob_bytes, cudaMemcpyHostToDevice, env->stream) != cudaSuccess)
+    return guard (fail (PRB_ECUDA, "upload of the initial state failed"));
+  if (cudaMemsetAsync (env->d_actions, 0, sizeof (int32_t) * (size_t) st.E, env->stream) != cudaSuccess)
+    return guard (fail (PRB_ECUDA, "memset failed"));
+  *out = env;
+  rc = prb_reset (env);
+  if (rc != PRB_OK)
+    {
+      *out = nullptr;
+      return guard (rc);
+    }
+  return PRB_OK;
+}
+
+int
+prb_reset (prb_env *env)
+{
+  if (!env) return fail (PRB_EINVAL, "null handle");
+  CUDA_TRY (cudaSetDevice (env->device));
+  const Static &st = env->dst;
+  int64_t work = std::max<int64_t> ((int64_t) st.blob_bytes / 16 * st.E, (int64_t) st.P * st.E);
+  int blocks = (int) std::min<int64_t> ((work + 255) / 256, 148 * 16);
+  k_reset<<<blocks, 256, 0, env->stream>>> (st, env->d_blobs, env->d_pools, env->d_blob0);
+  CUDA_TRY (cudaGetLastError ());
+  k_seed_policy<<<(st.E + 127) / 128, 128, 0, env->stream>>> (st, env->d_blobs);
+  CUDA_TRY (cudaGetLastError ());
+  env->launches += 2;
+  return PRB_OK;
+}
+
+int prb_num_links (prb_env *env) { return env ? env->dst.L : PRB_EINVAL; }
+
+int
+prb_state_bytes (prb_env *env, int64_t *blob_bytes, int64_t *pool_bytes)
+{
+  if (!env) return fail (PRB_EINVAL, "null handle");
+  if (blob_bytes) *blob_bytes = env->dst.blob_bytes;
+  if (pool_bytes) *pool_bytes = (int64_t) sizeof (Pkt) * env->dst.P;
+  return PRB_OK;
+}
+
+int
+prb_set_inject_trace (prb_env *env, int64_t n, const int64_t *t_ns, const int32_t *src, const int32_t *dst,
+                      const int64_t *uid, const uint8_t *valable, const uint8_t *rejected)
+{
+  if (!env) return fail (PRB_EINVAL, "null handle");
+  CUDA_TRY (cudaSetDevice (env->device));
+  Static &st = env->dst;
+  CUDA_TRY (cudaStreamSynchronize (env->stream));
+  if (n <= 0 || !t_ns)
+    {
+      st.inject_mode = PRB_INJECT_PHILOX;
+      return PRB_OK;
+    }
+  if (n >= (1ll << 31)) return fail (PRB_EINVAL, "trace too long");
+  if (!build_trace (env->hm, n, t_ns, src, dst, uid, valable, rejected, env->tr))
+    return fail (PRB_EINVAL, "injection trace names a flow that the configuration does not have");
+  size_t o_t = 0, o_uid = o_t + 8 * n, o_next = o_uid + 4 * n, o_fl = o_next + 4 * n, total = o_fl + n + 16;
+  cudaFree (env->d_trace);
+  env->d_trace = nullptr;
+  CUDA_TRY (cudaMalloc (&env->d_trace, total));
+  CUDA_TRY (cudaMemcpyAsync (env->d_trace + o_t, env->tr.t.data (), 8 * n, cudaMemcpyHostToDevice, env->stream));
+  CUDA_TRY (cudaMemcpyAsync (env->d_trace + o_uid, env->tr.uid.data (), 4 * n, cudaMemcpyHostToDevice, env->stream));
+  CUDA_TRY (cudaMemcpyAsync (env->d_trace + o_next, env->tr.next.data (), 4 * n, cudaMemcpyHostToDevice, env->stream));
+  CUDA_TRY (cudaMemcpyAsync (env->d_trace + o_fl, env->tr.flags.data (), n, cudaMemcpyHostToDevice, env->stream));
+  CUDA_TRY (cudaMemcpyAsync (env->d_flow_first, env->hm.flow_first.data (), sizeof (int32_t) * std::max (st.F, 1),
+                             cudaMemcpyHostToDevice, env->stream));
+  CUDA_TRY (cudaStreamSynchronize (env->stream));
+  st.inject_mode = PRB_INJECT_TRACE;
+  st.tr_n = n;
+  st.tr_t = (const int64_t *) (env->d_trace + o_t);
+  st.tr_uid = (const uint32_t *) (env->d_trace + o_uid);
+  st.tr_next = (const int32_t *) (env->d_trace + o_next);
+  st.tr_flags = (const uint8_t *) (env->d_trace + o_fl);
+  st.flow_first = env->d_flow_first;
+  return PRB_OK;
+}
+
+int
+prb_set_policy (prb_env *env, int kind, const int32_t *data, int64_t n, uint64_t seed)
+{
+  if (!env) return fail (PRB_EINVAL, "null handle");
+  CUDA_TRY (cudaSetDevice (env->device));
+  Static &st = env->dst;
+  if (kind < PRB_POLICY_ZERO || kind > PRB_POLICY_RANDOM) return fail (PRB_EINVAL, "unknown policy kind");
+  if (kind == PRB_POLICY_TABLE)
+    {
+      if (!data || n != (int64_t) st.M * st.M) return fail (PRB_EINVAL, "a table policy needs M*M entries");
+      /* rows must name existing neighbours or the packet vanishes (data-packet-manager.cc:294-297): allowed */
+    }
+  if (kind == PRB_POLICY_TRACE && (!data || n <= 0)) return fail (PRB_EINVAL, "a trace policy needs actions");
+  if (data && n > 0)
+    {
+      if (n > env->pol_cap)
+        {
+          CUDA_TRY (cudaStreamSynchronize (env->stream));
+          cudaFree (env->d_pol);
+          env->d_pol = nullptr;
+          CUDA_TRY (cudaMalloc (&env->d_pol, sizeof (int32_t) * n));
+          env->pol_cap = n;
+        }
+      CUDA_TRY (cudaMemcpyAsync (env->d_pol, data, sizeof (int32_t) * n, cudaMemcpyHostToDevice, env->stream));
+    }
+  st.policy = kind;
+  st.pol_data = env->d_pol;
+  st.pol_n = data ? n : 0;
+  bool reseed = kind == PRB_POLICY_RANDOM || kind == PRB_POLICY_TRACE;
+  if (reseed)
+    {
+      st.policy_seed = seed;
+      k_seed_policy<<<(st.E + 127) / 128, 128, 0, env->stream>>> (st, env->d_blobs);
+      CUDA_TRY (cudaGetLastError ());
+      env->launches++;
+    }
+  return PRB_OK;
+}
+
+int
+prb_enable_log (prb_env *env, int64_t event_capacity, int64_t step_capacity)
+{
+  if (!env) return fail (PRB_EINVAL, "null handle");
+  CUDA_TRY (cudaSetDevice (env->device));
+  CUDA_TRY (cudaStreamSynchronize (env->stream));
+  Static &st = env->dst;
+  cudaFree (env->d_ev); env->d_ev = nullptr;
+  cudaFree (env->d_st); env->d_st = nullptr;
+  st.ev_cap = std::max<int64_t> (event_capacity, 0);
+  st.st_cap = std::max<int64_t> (step_capacity, 0);
+  env->log_on = st.ev_cap > 0 || st.st_cap > 0;
+  if (st.ev_cap > 0) CUDA_TRY (cudaMalloc (&env->d_ev, sizeof (prb_event) * (size_t) st.ev_cap * st.E));
+  if (st.st_cap > 0) CUDA_TRY (cudaMalloc (&env->d_st, sizeof (prb_step_rec) * (size_t) st.st_cap * st.E));
+  return PRB_OK;
+}
+
+static int
+log_counts (prb_env *env, int32_t e, int64_t *ev_n, int64_t *st_n)
+{
+  const Static &st = env->dst;
+  if (e < 0 || e >= st.E) return fail (PRB_EINVAL, "env index out of range");
+  k_log_counts<<<1, 1, 0, env->stream>>> (st, env->d_blobs, e, env->d_scratch);
+  CUDA_TRY (cudaGetLastError ());
+  int64_t h[2];
+  CUDA_TRY (cudaMemcpyAsync (h, env->d_scratch, 16, cudaMemcpyDeviceToHost, env->stream));
+  CUDA_TRY (cudaStreamSynchronize (env->stream));
+  *ev_n = h[0];
+  *st_n = h[1];
+  return PRB_OK;
+}
+
+int
+prb_read_events (prb_env *env, int32_t e, prb_event *out, int64_t capacity, int64_t *n)
+{
+  if (!env || !n) return fail (PRB_EINVAL, "null argument");
+  CUDA_TRY (cudaSetDevice (env->device));
+  int64_t en, sn;
+  int rc = log_counts (env, e, &en, &sn);
+  if (rc != PRB_OK) return rc;
+  *n = en;
+  if (out && en > 0)
+    {
+      if (!env->d_ev) return fail (PRB_ESTATE, "event log is not enabled");
+      int64_t k = std::min (en, capacity);
+      CUDA_TRY (cudaMemcpyAsync (out, env->d_ev + (size_t) e * env->dst.ev_cap, sizeof (prb_event) * k, cudaMemcpyDeviceToHost, env->stream));
+      CUDA_TRY (cudaStreamSynchronize (env->stream));
+    }
+  return PRB_OK;
+}
+
+int
+prb_read_steps (prb_env *env, int32_t e, prb_step_rec *out, int64_t capacity, int64_t *n)
+{
+  if (!env || !n) return fail (PRB_EINVAL, "null argument");
+  CUDA_TRY (cudaSetDevice (env->device));
+  int64_t en, sn;
+  int rc = log_counts (env, e, &en, &sn);
+  if (rc != PRB_OK) return rc;
+  *n = sn;
+  if (out && sn > 0)
+    {
+      if (!env->d_st) return fail (PRB_ESTATE, "step log is not enabled");
+      int64_t k = std::min (sn, capacity);
+      CUDA_TRY (cudaMemcpyAsync (out, env->d_st + (size_t) e * env->dst.st_cap, sizeof (prb_step_rec) * k, cudaMemcpyDeviceToHost, env->stream));
+      CUDA_TRY (cudaStreamSynchronize (env->stream));
+    }
+  return PRB_OK;
+}
+
+int
+prb_run (prb_env *env, int64_t until_ns)
+{
+  if (!env) return fail (PRB_EINVAL, "null handle");
+  CUDA_TRY (cudaSetDevice (env->device));
+  Static &st = env->dst;
+  st.mode = MODE_RUN;
+  LaunchArgs a;
+  a.blobs = env->d_blobs; a.pools = env->d_pools; a.ev_logs = env->d_ev; a.st_logs = env->d_st;
+  a.actions = nullptr; a.out = nullptr; a.until_ns = until_ns;
+  return launch_advance (env, a);
+}
+
+int
+prb_step (prb_env *env, const int32_t *actions_dev, prb_step_rec *out_dev)
+{
+  if (!env || !out_dev) return fail (PRB_EINVAL, "null argument");
+  CUDA_TRY (cudaSetDevice (env->device));
+  Static &st = env->dst;
+  st.mode = MODE_GYM;
+  LaunchArgs a;
+  a.blobs = env->d_blobs; a.pools = env->d_pools; a.ev_logs = env->d_ev; a.st_logs = env->d_st;
+  a.actions = actions_dev; a.out = out_dev; a.until_ns = st.sim_time_ns;
+  return launch_advance (env, a);
+}
+
+int
+prb_step_host (prb_env *env, const int32_t *actions, prb_step_rec *out)
+{
+  if (!env || !out) return fail (PRB_EINVAL, "null argument");
+  CUDA_TRY (cudaSetDevice (env->device));
+  const Static &st = env->dst;
+  if (actions)
+    CUDA_TRY (cudaMemcpyAsync (env->d_actions, actions, sizeof (int32_t) * (size_t) st.E, cudaMemcpyHostToDevice, env->stream));
+  int rc = prb_step (env, env->d_actions, env->d_out);
+  if (rc != PRB_OK) return rc;
+  CUDA_TRY (cudaMemcpyAsync (out, env->d_out, sizeof (prb_step_rec) * (size_t) st.E, cudaMemcpyDeviceToHost, env->stream));
+  CUDA_TRY (cudaStreamSynchronize (env->stream));
+  return PRB_OK;
+}
+
+int
+prb_counters_dev (prb_env *env, prb_counters *out_dev)
+{
+  if (!env || !out_dev) return fail (PRB_EINVAL, "null argument");
+  CUDA_TRY (cudaSetDevice (env->device));
+  const Static &st = env->dst;
+  k_counters<<<(st.E + 127) / 128, 128, 0, env->stream>>> (st, env->d_blobs, out_dev);
+  CUDA_TRY (cudaGetLastError ());
+  env->launches++;
+  return PRB_OK;
+}
+
+int
+prb_counters_host (prb_env *env, prb_counters *out)
+{
+  if (!env || !out) return fail (PRB_EINVAL, "null argument");
+  int rc = prb_counters_dev (env, env->d_counters);
+  if (rc != PRB_OK) return rc;
+  CUDA_TRY (cudaMemcpyAsync (out, env->d_counters, sizeof (prb_counters) * (size_t) env->dst.E, cudaMemcpyDeviceToHost, env->stream));
+  CUDA_TRY (cudaStreamSynchronize (env->stream));
+  return PRB_OK;
+}
+
+int
+prb_queue_bytes (prb_env *env, int32_t e, int32_t *out)
+{
+  if (!env || !out) return fail (PRB_EINVAL, "null argument");
+  CUDA_TRY (cudaSetDevice (env->device));
+  const Static &st = env->dst;
+  if (e < 0 || e >= st.E) return fail (PRB_EINVAL, "env index out of range");
+  if (st.L > 1000) return fail (PRB_EINVAL, "too many links for the scratch buffer");
+  k_queue_bytes<<<(st.L + 127) / 128, 128, 0, env->stream>>> (st, env->d_blobs, e, (int32_t *) env->d_scratch);
+  CUDA_TRY (cudaGetLastError ());
+  CUDA_TRY (cudaMemcpyAsync (out, env->d_scratch, sizeof (int32_t) * st.L, cudaMemcpyDeviceToHost, env->stream));
+  CUDA_TRY (cudaStreamSynchronize (env->stream));
+  return PRB_OK;
+}
+
+int
+prb_sync (prb_env *env)
+{
+  if (!env) return fail (PRB_EINVAL, "null handle");
+  CUDA_TRY (cudaSetDevice (env->device));
+  CUDA_TRY (cudaStreamSynchronize (env->stream));
+  return PRB_OK;
+}
+
+int64_t prb_launch_count (prb_env *env) { return env ? env->launches : 0; }
+
+}  /* extern "C" */

@@ -88,3 +88,67 @@ def first_event_mismatch(a, b, fields=EVENT_FIELDS):
     if len(a) != len(b):
         return min(len(a), len(b))
     return None
+
+
+# ---- comparisons between the oracle (po_*) and the product / host-harness records (prb_*) ----
+
+STEP_FIELDS = ["t_ns", "node", "overlay", "uid", "ptype", "done", "action", "nobs", "is_new", "prev_node", "n_lost"]
+
+
+def assert_steps_equal(oracle_dec, steps, check_action=True):
+    """po_decision[] (oracle) vs prb_step_rec[] (CUDA path / host harness): every Gym step, bit for bit."""
+    assert len(oracle_dec) == len(steps), (len(oracle_dec), len(steps))
+    for f in STEP_FIELDS:
+        if f == "action" and not check_action:
+            continue
+        a, b = oracle_dec[f], steps[f]
+        if f == "uid":
+            keep = oracle_dec["ptype"] != 1          # big signalling carries no uid
+            a, b = a[keep], b[keep]
+        bad = np.nonzero(np.asarray(a) != np.asarray(b))[0]
+        assert len(bad) == 0, (f, int(bad[0]), oracle_dec[bad[0]], steps[bad[0]])
+    k = steps["obs"].shape[1]
+    mask = np.arange(k)[None, :] < steps["nobs"][:, None]
+    assert np.array_equal(np.where(mask, oracle_dec["obs"][:, :k], 0), np.where(mask, steps["obs"], 0))
+    # reward (hop time): exact ns difference scaled once -> identical doubles; e2e delay: identical float32
+    assert np.array_equal(oracle_dec["hop_time"].view(np.uint64), steps["hop_time"].view(np.uint64))
+    assert np.array_equal(oracle_dec["e2e_delay"].view(np.uint32), steps["e2e_delay"].view(np.uint32))
+    nl = np.minimum(steps["n_lost"], 8)
+    lm = np.arange(8)[None, :] < nl[:, None]
+    assert np.array_equal(np.where(lm, oracle_dec["lost_uid"], 0), np.where(lm, steps["lost_uid"], 0))
+
+
+COUNTER_INTS = ["overlay_injected", "overlay_arrived", "overlay_lost", "underlay_injected", "underlay_arrived",
+                "underlay_lost", "bytes_data", "bytes_signaling", "n_e2e", "n_cost", "n_underlay_e2e",
+                "n_underlay_cost", "packet_hops", "data_hops", "env_steps", "decisions", "events", "vanished", "end_ns"]
+COUNTER_FLOATS = ["sum_e2e", "sum_cost", "sum_underlay_e2e", "sum_underlay_cost", "avg_e2e", "avg_cost",
+                  "avg_underlay_e2e", "avg_underlay_cost", "signaling_overhead"]
+
+
+def assert_counters_equal(oc, pc):
+    """oracle counters dict vs product counters (dict or numpy record): integers and float32 bits."""
+    import struct
+    for k in COUNTER_INTS:
+        assert int(oc[k]) == int(pc[k]), (k, oc[k], pc[k])
+    for k in COUNTER_FLOATS:
+        a = struct.unpack("I", struct.pack("f", float(oc[k])))[0]
+        b = struct.unpack("I", struct.pack("f", float(pc[k])))[0]
+        assert a == b, (k, oc[k], pc[k])
+    assert int(pc["errors"]) == 0
+
+
+def replay_inputs(g):
+    """(injection arrays, policy kind, policy data, seed) of a golden fixture."""
+    inj = g.injections
+    return (inj["t_ns"], inj["src"], inj["dst"], inj["uid"], inj["valable"], inj["rejected"]), g.policy, g.table, g.policy_seed
+
+
+def oracle_run(cfg, arrays, oracle_mod, policy="table", table=None, seed=7, env_id=0, until_ns=None, inject=None, **over):
+    """Run the CPU restatement on one environment (Philox traffic unless `inject` is given)."""
+    p = oracle_params(cfg, arrays, oracle_mod, env_id=env_id, inject_mode=1, **over)
+    sim = oracle_mod.OracleSim(p)
+    if inject is not None:
+        sim.set_inject_trace(*inject)
+    sim.set_policy(policy, table, seed=seed)
+    sim.run(until_ns)
+    return sim

@@ -1,0 +1,125 @@
+"""TEST INFRASTRUCTURE — ctypes front end of tests/host_harness/libhost_sim.so: the kernel body of
+prisma_b200 compiled with g++ for one environment (see host_sim.cpp).  Only tests import this."""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+from prisma_b200 import _abi
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB = os.path.join(HERE, "libhost_sim.so")
+SRC = [os.path.join(HERE, "host_sim.cpp"),
+       os.path.join(HERE, "..", "..", "prisma_b200", "csrc", "sim_core.cuh"),
+       os.path.join(HERE, "..", "..", "prisma_b200", "csrc", "model.h"),
+       os.path.join(HERE, "..", "..", "include", "prisma_b200.h")]
+_lib = None
+
+
+def build():
+    subprocess.check_call(["g++", "-O2", "-g", "-std=c++17", "-ffp-contract=off", "-fno-fast-math", "-fPIC", "-shared",
+                           "-Wall", "-Wno-unused-function", "-Wno-unknown-pragmas", "-o", LIB, SRC[0]])
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB) or any(os.path.getmtime(LIB) < os.path.getmtime(s) for s in SRC):
+            build()
+        L = C.CDLL(LIB)
+        vp, i32, i64 = C.c_void_p, C.c_int32, C.c_int64
+        L.hs_create.restype = vp
+        L.hs_create.argtypes = [C.POINTER(_abi.PrbConfig), C.c_int, i64, i64]
+        L.hs_destroy.argtypes = [vp]
+        L.hs_set_inject_trace.argtypes = [vp, i64, C.POINTER(i64), C.POINTER(i32), C.POINTER(i32), C.POINTER(i64),
+                                          C.POINTER(C.c_uint8), C.POINTER(C.c_uint8)]
+        L.hs_set_policy.argtypes = [vp, C.c_int, C.POINTER(i32), i64, C.c_uint64]
+        L.hs_run.argtypes = [vp, i64]
+        L.hs_step.argtypes = [vp, i32, C.POINTER(_abi.PrbStepRec)]
+        L.hs_counters.argtypes = [vp, C.POINTER(_abi.PrbCounters)]
+        L.hs_num_events.restype = i64
+        L.hs_num_events.argtypes = [vp]
+        L.hs_events.restype = vp
+        L.hs_events.argtypes = [vp]
+        L.hs_num_steps.restype = i64
+        L.hs_num_steps.argtypes = [vp]
+        L.hs_steps.restype = vp
+        L.hs_steps.argtypes = [vp]
+        L.hs_num_links.argtypes = [vp]
+        L.hs_queue_bytes.argtypes = [vp, i32]
+        L.hs_seconds_to_ns.restype = i64
+        L.hs_seconds_to_ns.argtypes = [C.c_double]
+        L.hs_ns_to_seconds.restype = C.c_double
+        L.hs_ns_to_seconds.argtypes = [vp, i64]
+        L.hs_tx_time_ns.restype = i64
+        L.hs_tx_time_ns.argtypes = [C.c_uint32, C.c_uint64]
+        L.hs_invert_1e9.argtypes = [C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
+        L.hs_global_routes.argtypes = [i32, C.POINTER(C.c_uint8), C.POINTER(i32)]
+        _lib = L
+    return _lib
+
+
+class HostSim:
+    def __init__(self, params, env_index=0, ev_cap=1 << 21, st_cap=1 << 20):
+        self._keep = []
+        self.cfg = _abi.fill_config(_abi.PrbConfig(), self._keep, params)
+        self.h = lib().hs_create(C.byref(self.cfg), env_index, ev_cap, st_cap)
+        if not self.h:
+            raise ValueError("hs_create failed")
+
+    def close(self):
+        if self.h:
+            lib().hs_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def set_inject_trace(self, t_ns, src, dst, uid, valable, rejected):
+        a = [np.ascontiguousarray(t_ns, dtype=np.int64), np.ascontiguousarray(src, dtype=np.int32),
+             np.ascontiguousarray(dst, dtype=np.int32), np.ascontiguousarray(uid, dtype=np.int64),
+             np.ascontiguousarray(valable, dtype=np.uint8), np.ascontiguousarray(rejected, dtype=np.uint8)]
+        rc = lib().hs_set_inject_trace(self.h, len(a[0]), _abi.ptr(a[0], C.c_int64), _abi.ptr(a[1], C.c_int32),
+                                       _abi.ptr(a[2], C.c_int32), _abi.ptr(a[3], C.c_int64),
+                                       _abi.ptr(a[4], C.c_uint8), _abi.ptr(a[5], C.c_uint8))
+        if rc != 0:
+            raise ValueError("bad injection trace")
+
+    def set_policy(self, kind, data=None, seed=1):
+        d = np.ascontiguousarray(data if data is not None else [], dtype=np.int32).ravel()
+        lib().hs_set_policy(self.h, _abi.POLICY[kind], _abi.ptr(d, C.c_int32), d.size, int(seed))
+
+    def run(self, until_ns=None):
+        lib().hs_run(self.h, int(until_ns if until_ns is not None else self.cfg.sim_time_ns))
+
+    def step(self, action=0):
+        r = _abi.PrbStepRec()
+        lib().hs_step(self.h, int(action), C.byref(r))
+        return r
+
+    def counters(self):
+        c = _abi.PrbCounters()
+        lib().hs_counters(self.h, C.byref(c))
+        return {n: getattr(c, n) for n, _ in c._fields_}
+
+    def events(self):
+        n = lib().hs_num_events(self.h)
+        if n == 0:
+            return np.zeros(0, dtype=_abi.EVENT_DTYPE)
+        buf = (C.c_char * (n * 64)).from_address(lib().hs_events(self.h))
+        return np.frombuffer(buf, dtype=_abi.EVENT_DTYPE).copy()
+
+    def steps(self):
+        n = lib().hs_num_steps(self.h)
+        if n == 0:
+            return np.zeros(0, dtype=_abi.STEP_DTYPE)
+        buf = (C.c_char * (n * 208)).from_address(lib().hs_steps(self.h))
+        return np.frombuffer(buf, dtype=_abi.STEP_DTYPE).copy()
+
+    def queue_bytes(self):
+        nl = lib().hs_num_links(self.h)
+        return np.array([lib().hs_queue_bytes(self.h, l) for l in range(nl)], dtype=np.int32)
