@@ -1,0 +1,372 @@
+#!/usr/bin/env python3
+"""Headline benchmark: packet-hops/s of the batched environment step loop (BASELINE.json metric).
+
+  python bench.py [--gpus N] [--steps K] [--warmup W]              # this repo's CUDA path
+  python bench.py --impl reference [--gpus N] [--steps K] ...      # the reference's own CPU code, host cores
+
+Workload (BASELINE.json configs[1]): Abilene 11-node underlay from the reference's examples, frozen
+dq_routing-style agent (a next-hop table indexed by (node, destination); the sp-pretrained table), 4096
+parallel environments per GPU, load_factor 0.9, seeded synthetic Poisson traffic (Philox), pings on.
+One "step" advances every environment by --chunk simulated seconds (one k_advance launch).  Multi-GPU:
+environments are independent, each rank owns 4096 of them, no collective in the step ("weak" scaling);
+torch.distributed is used for the barrier and the max-over-ranks / sum reductions of the report only.
+
+Timing: W untimed warm-up steps, then K steps each bracketed by CUDA events on the launch stream, L2
+flushed (256 MB memset) between steps outside the event pairs; max over ranks of the summed step times.
+"""
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+FIX = os.path.join(ROOT, "tests", "fixtures")
+METRIC = "packet_hops_per_s"
+UNIT = "packet-hops/s"
+B_HOP_BASE = 144      # algorithmic bytes per packet hop = 144 + 4*(1+k)
+
+
+def workload_cfg(envs, sim_time, topo="abilene", load_factor=0.9):
+    from prisma_b200.config import EnvConfig
+    d = os.path.join(FIX, topo)
+    return EnvConfig(physical_adjacency_matrix_path=os.path.join(d, "topology_files", "physical_adjacency_matrix.txt"),
+                     overlay_adjacency_matrix_path=os.path.join(d, "topology_files", "overlay_adjacency_matrix.txt"),
+                     map_overlay_path=os.path.join(d, "topology_files", "map_overlay.txt"),
+                     traffic_matrix_root_path=os.path.join(d, "traffic_matrices"),
+                     num_envs=envs, simTime=sim_time, load_factor=load_factor, pingAsObs=0, activateUnderlayTraffic=1,
+                     agent_type="dqn_routing", seed=100)
+
+
+def config_dict(args, world):
+    return {"workload": "abilene_11node_dq_routing_table_%denvs_per_gpu_lf0.9" % args.envs,
+            "topology": "prisma/examples/abilene (TM 0)", "agent": "dq_routing frozen as next-hop table (sp-pretrained)",
+            "envs_per_gpu": args.envs, "total_envs": args.envs * world, "load_factor": 0.9,
+            "sim_seconds_per_step": args.chunk, "link_cap": 500000, "link_delay_ms": 1, "packet_size": 512,
+            "max_out_buffer_size": 16260, "traffic": "Philox-4x32-10 Poisson per flow",
+            "l2": "flushed between steps (256 MB memset outside the event pairs)", "parallelism": "env-sharded x%d" % world}
+
+
+class ClockSampler:
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index = index
+        self.p = None
+
+    def start(self):
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                       "--format=csv,noheader,nounits", "-lms", "100"],
+                                      stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+        except Exception:
+            self.p = None
+
+    def stop(self):
+        lines = []
+        if self.p is not None:
+            time.sleep(0.15)
+            self.p.terminate()
+            try:
+                out, _ = self.p.communicate(timeout=5)
+                lines = out.strip().splitlines()
+            except Exception:
+                self.p.kill()
+        if not lines:
+            try:
+                lines = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                        "--format=csv,noheader,nounits"], stdout=subprocess.PIPE, text=True,
+                                       timeout=10).stdout.strip().splitlines()
+            except Exception:
+                lines = []
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in lines:
+            t = [x.strip() for x in ln.split(",")]
+            if len(t) < 6:
+                continue
+            try:
+                sm.append(float(t[0]))
+                mx.append(float(t[1]))
+            except ValueError:
+                continue
+            for n, v in zip(names, t[2:6]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def measured_peak_gbs():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    try:
+        return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    except Exception:
+        return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def recorded_traffic(args):
+    """dram bytes per k_advance launch from the committed ncu capture of this exact workload, if any."""
+    p = os.path.join(ROOT, "profiles", "roofline_traffic.json")
+    try:
+        j = json.load(open(p))
+        if j.get("envs") == args.envs and abs(j.get("chunk", -1) - args.chunk) < 1e-12:
+            return float(j["dram_bytes_per_launch"])
+    except Exception:
+        pass
+    return None
+
+
+# ------------------------------------------------------------------------------------------------
+# reference arm / CPU baseline: the reference's own ns-3 program on the host cores
+# ------------------------------------------------------------------------------------------------
+
+def ref_sample(sim_time, procs, load_factor=0.9):
+    """One prisma_ref process per core, each one environment for `sim_time` simulated seconds of the same
+    workload (sp table agent evaluated in-process: no ZMQ, no Python in the loop).  Returns
+    (hops, env_steps, wall_seconds, kind)."""
+    from oracle import oracle, run_ref
+    from prisma_b200.env import sp_table
+    cfg = workload_cfg(1, sim_time, load_factor=load_factor)
+    arrays = cfg.load()
+    table = sp_table(arrays)
+    if run_ref.available():
+        tmp = tempfile.mkdtemp(prefix="prb_ref_")
+        rej = os.path.join(tmp, "rej.txt")
+        np.savetxt(rej, np.zeros((arrays.n_nodes, arrays.n_nodes)), fmt="%.6f")
+        files = {"adj": cfg.physical_adjacency_matrix_path, "overlay": cfg.overlay_adjacency_matrix_path,
+                 "map": cfg.map_overlay_path, "rej": rej,
+                 "tm": os.path.join(cfg.traffic_matrix_root_path, "node_intensity_normalized_0.txt")}
+        res = [None] * procs
+
+        def work(i):
+            out = os.path.join(tmp, "o%d" % i)
+            run_ref.run(files, out, sim_time=sim_time, seed=100 + i, load_factor=load_factor, policy="table",
+                        policy_data=table, events=False, loss_penalty=cfg.derived_loss_penalty(arrays.n_overlay),
+                        activate_underlay_traffic=True, ping_as_obs=False)
+            res[i] = run_ref.parse_summary(out)
+        th = [threading.Thread(target=work, args=(i,)) for i in range(procs)]
+        t0 = time.perf_counter()
+        for t in th:
+            t.start()
+        for t in th:
+            t.join()
+        dt = time.perf_counter() - t0
+        hops = sum(r["packet_hops"] for r in res)
+        steps = sum(r["env_steps"] for r in res)
+        return hops, steps, dt, "reference"
+    # the reference binary did not travel: time the C restatement instead (ctypes releases the GIL)
+    from tests import common
+    res = [None] * procs
+
+    def work(i):
+        p = common.oracle_params(cfg, arrays, oracle, env_id=i, inject_mode=1)
+        sim = oracle.OracleSim(p, log_events=False)
+        sim.set_policy("table", table)
+        sim.run()
+        res[i] = sim.counters()
+    th = [threading.Thread(target=work, args=(i,)) for i in range(procs)]
+    t0 = time.perf_counter()
+    for t in th:
+        t.start()
+    for t in th:
+        t.join()
+    dt = time.perf_counter() - t0
+    return sum(r["packet_hops"] for r in res), sum(r["env_steps"] for r in res), dt, "port"
+
+
+def run_reference_arm(args, rank, world):
+    if rank != 0:
+        return
+    cores = os.cpu_count() or 1
+    sim_time = args.ref_sim_time
+    for _ in range(args.warmup if args.warmup < 2 else 1):
+        ref_sample(min(sim_time, 2.0), cores)
+    hops = steps = 0
+    total = 0.0
+    kind = "reference"
+    for _ in range(args.steps):
+        h, s, dt, kind = ref_sample(sim_time, cores)
+        hops += h
+        steps += s
+        total += dt
+    value = hops / total
+    sample = "%d steps x %d processes (one per core) x 1 env x %g simulated s, Abilene lf 0.9, sp table agent in-process" % (
+        args.steps, cores, sim_time)
+    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": 1000.0 * total / args.steps, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "int64", "data": "synthetic",
+            "config": config_dict(args, world),
+            "env_steps_per_s": steps / total,
+            "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": kind, "sample": sample},
+            "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------------------------
+# this repo's arm
+# ------------------------------------------------------------------------------------------------
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="prisma_b200", choices=["prisma_b200", "reference"])
+    ap.add_argument("--envs", type=int, default=4096, help="environments per GPU")
+    ap.add_argument("--chunk", type=float, default=1.0, help="simulated seconds per step")
+    ap.add_argument("--lanes", type=int, default=0, help="lanes per environment (0 = library default)")
+    ap.add_argument("--ref-sim-time", type=float, default=10.0, dest="ref_sim_time")
+    ap.add_argument("--cpu-sim-time", type=float, default=30.0, dest="cpu_sim_time")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if args.warmup < 3 and args.impl != "reference":
+        args.warmup = 3
+
+    if args.impl == "reference":
+        run_reference_arm(args, rank, world)
+        return
+
+    import torch
+    import torch.distributed as dist
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device (prisma_b200 has no CPU path; use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local_rank)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+    from prisma_b200 import build as pb
+    if rank == 0:
+        pb.build()
+    if world > 1:
+        dist.barrier()
+    from prisma_b200.env import BatchedRoutingEnv, sp_table
+
+    K, W = args.steps, args.warmup
+    total_steps = W + 2 * K
+    cfg = workload_cfg(args.envs, total_steps * args.chunk + 1.0)
+    arrays = cfg.load()
+    table = sp_table(arrays)
+    kdeg = max(len(x) for x in arrays.overlay_neighbors())
+    b_hop = B_HOP_BASE + 4 * (1 + kdeg)
+    env = BatchedRoutingEnv(cfg, device=local_rank, arrays=arrays, env_id_base=rank * args.envs, lanes_per_env=args.lanes)
+    env.set_policy("table", table)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+    lib, h = env.lib, env.h
+
+    def hops_now():
+        c = env.counters()
+        env.check_errors(c)
+        return int(c["packet_hops"].sum()), int(c["env_steps"].sum()), int(c["events"].sum())
+
+    t_sim = 0.0
+    for _ in range(W):
+        t_sim += args.chunk
+        env.run(until_s=t_sim)
+    torch.cuda.synchronize()
+    hops0, steps0, events0 = hops_now()
+
+    # ---- timed region: K steps, device-resident ----
+    sampler = ClockSampler(local_rank)
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    sampler.start()
+    launches0 = env.launch_count
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(K)]
+    for i in range(K):
+        flush.zero_()
+        t_sim += args.chunk
+        ev[i][0].record()
+        env.run(until_s=t_sim)
+        ev[i][1].record()
+    torch.cuda.synchronize()
+    launches = env.launch_count - launches0
+    clocks = sampler.stop()
+    if world > 1:
+        dist.barrier()
+    step_ms = [a.elapsed_time(b) for a, b in ev]
+    elapsed = sum(step_ms) / 1000.0
+    hops1, steps1, events1 = hops_now()
+    d_hops, d_steps, d_events = hops1 - hops0, steps1 - steps0, events1 - events0
+
+    # ---- e2e: the public host-buffer calls, copies inside the timed region ----
+    tab_host = np.ascontiguousarray(table, dtype=np.int32)
+    cnt = np.empty(args.envs, dtype=env.counters().dtype)
+    import ctypes as C
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    e2e_wall = 0.0
+    for i in range(K):
+        flush.zero_()
+        torch.cuda.synchronize()
+        t_sim += args.chunk
+        t0 = time.perf_counter()
+        env.set_policy("table", tab_host)                      # H2D: the agent's table
+        env.run(until_s=t_sim)
+        lib.prb_counters_host(h, cnt.ctypes.data_as(C.c_void_p))   # D2H: per-env statistics (synchronises)
+        e2e_wall += time.perf_counter() - t0
+    hops2 = int(cnt["packet_hops"].sum())
+    e2e_hops = hops2 - hops1
+    h2d = int(tab_host.nbytes)
+    d2h = int(cnt.nbytes)
+
+    # ---- reductions over ranks ----
+    if world > 1:
+        t = torch.tensor([elapsed, e2e_wall], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        elapsed, e2e_wall = float(t[0]), float(t[1])
+        s = torch.tensor([d_hops, d_steps, d_events, e2e_hops, launches], dtype=torch.int64, device="cuda")
+        dist.all_reduce(s, op=dist.ReduceOp.SUM)
+        d_hops, d_steps, d_events, e2e_hops, launches = (int(x) for x in s)
+
+    if rank == 0:
+        peak, peak_src = measured_peak_gbs()
+        # dominant kernel: k_advance, one launch per step; algorithmic bytes of THIS rank's launch
+        my_hops_per_launch = (hops1 - hops0) / K
+        kern_s = (sum(step_ms) / K) / 1000.0
+        achieved = my_hops_per_launch * b_hop / kern_s / 1e9
+        line = {"metric": METRIC, "value": d_hops / elapsed, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
+                "ms_per_step": 1000.0 * elapsed / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+                "dtype": "int64", "data": "synthetic", "config": config_dict(args, world),
+                "env_steps_per_s": d_steps / elapsed, "sim_events_per_s": d_events / elapsed,
+                "packet_hops_per_step": d_hops / K,
+                "clocks": clocks,
+                "e2e": {"value": e2e_hops / e2e_wall, "unit": UNIT, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                        "what": "prb_set_policy(host table) + prb_run + prb_counters_host per step, wall clock"},
+                "gpu_launches": launches,
+                "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                             "traffic": recorded_traffic(args), "peak_source": peak_src, "kernel": "k_advance",
+                             "bytes_per_packet_hop": b_hop, "packet_hops_per_launch": my_hops_per_launch,
+                             "kernel_ms": kern_s * 1000.0,
+                             "note": "event-serial simulator: issue/latency bound, not HBM bound (DESIGN.md)"}}
+        if world == 1 and not args.no_cpu_baseline:
+            cores = os.cpu_count() or 1
+            hc, sc_, dt, kind = ref_sample(args.cpu_sim_time, cores)
+            line["cpu_baseline"] = {"value": hc / dt, "unit": UNIT, "cores": cores, "kind": kind,
+                                    "env_steps_per_s": sc_ / dt,
+                                    "sample": "%d processes (one per core) x 1 env x %g simulated s of the same workload, "
+                                              "sp table agent in-process, %.1f s wall" % (cores, args.cpu_sim_time, dt)}
+        print(json.dumps(line), flush=True)
+    env.close()
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

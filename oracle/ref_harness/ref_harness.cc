@@ -69,6 +69,7 @@ size_t g_actionPos = 0;
 uint64_t g_rng = 0;
 uint64_t g_nDecisions = 0, g_nSteps = 0;
 bool g_summaryDone = false;
+unsigned long g_nHops = 0, g_nDataHops = 0;   /* Receive() on switch<->switch devices, tagged packets */
 
 struct LastRx
 {
@@ -156,6 +157,11 @@ void OnMacRx (std::string ctx, Ptr<const Packet> p)
   g_lastRx.src = has ? t.GetSource () : 0; g_lastRx.dst = has ? t.GetFinalDestination () : 0;
   g_lastRx.lastHop = has ? t.GetLastHop () : 0; g_lastRx.nextHop = has ? t.GetNextHop () : 0;
   g_lastRx.valable = has ? t.GetTrafficValable () : 0;
+  if (dev >= 2 && has && t.GetSimpleValue () <= 4)
+    {
+      g_nHops++;
+      if (t.GetSimpleValue () == 0) g_nDataHops++;
+    }
   LogEvent (dev >= 2 ? "RCV" : "ARR", ctx, p, false);
 }
 
@@ -217,6 +223,8 @@ WriteSummary ()
   fprintf (f, "end_ns %ld\n", (long) Simulator::Now ().GetNanoSeconds ());
   fprintf (f, "decisions %lu\n", (unsigned long) g_nDecisions);
   fprintf (f, "env_steps %lu\n", (unsigned long) g_nSteps);
+  fprintf (f, "packet_hops %lu\n", g_nHops);
+  fprintf (f, "data_hops %lu\n", g_nDataHops);
   fprintf (f, "overlay_injected %d\n", cs.getGlobalOverlayPacketsInjected ());
   fprintf (f, "overlay_arrived %d\n", cs.getGlobalOverlayPacketsArrived ());
   fprintf (f, "overlay_lost %d\n", cs.getGlobalOverlayPacketsLost ());
