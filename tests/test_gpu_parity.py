@@ -28,7 +28,7 @@ def test_cuda_replays_reference_golden(name, lanes):
     env = make_env(g.cfg, arrays=g.arrays, lanes_per_env=lanes)
     inj, policy, table, seed = common.replay_inputs(g)
     env.set_inject_trace(*inj)
-    env.enable_log(len(g.events) + 16, len(g.dec["t"]) + 16)
+    env.enable_log(2 * len(g.events), 2 * len(g.dec["t"]))   # envs 1, 2 of a random agent draw other actions
     env.reset()
     env.set_policy(policy, table, seed=seed)
     env.run()
@@ -195,7 +195,7 @@ def test_full_batch_properties_config2():
     assert (c["data_hops"] <= c["packet_hops"]).all() and (c["decisions"] <= c["env_steps"]).all()
     assert (c["env_steps"] == c["decisions"] + c["overlay_arrived"]).all()
     assert (c["vanished"] == 0).all()
-    assert 1500 < c["overlay_injected"].mean() < 1650      # 860 pkt/s * 0.9 * 2 s
+    assert 1100 < c["overlay_injected"].mean() < 1230      # 860 pkt/s * 0.9 * (2 s - mean start offset 0.5 s)
     for e in (0, 1777, 4095):
         osim = common.oracle_run(cfg, arrays, oracle, policy="table", table=table, env_id=e)
         common.assert_counters_equal(osim.counters(), c[e])
