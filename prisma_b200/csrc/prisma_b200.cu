@@ -94,8 +94,8 @@ scan_slots (const int64_t *t_ts, const uint32_t *t_seq, int first, int last, int
 
 /* Advance every environment: run mode until `until_ns`, gym mode until the next valid Notify().
  * SMEM: the env blob lives in shared memory during the launch. */
-template <int G, bool LOG, bool SMEM>
-__global__ void __launch_bounds__ (128)
+template <int G, bool LOG, bool GYM, bool SMEM>
+__global__ void __launch_bounds__ (128, LOG ? 4 : 7)
 k_advance (const __grid_constant__ Static st, const LaunchArgs a)
 {
   extern __shared__ __align__ (16) char smem[];
@@ -126,15 +126,15 @@ k_advance (const __grid_constant__ Static st, const LaunchArgs a)
   d.ev_log = LOG && a.ev_logs ? a.ev_logs + (size_t) (active ? env : 0) * st.ev_cap : nullptr;
   d.st_log = LOG && a.st_logs ? a.st_logs + (size_t) (active ? env : 0) * st.st_cap : nullptr;
   Scal *sc = d.sc;
-  __shared__ prb_step_rec scratch_rec[128 / G];
-  prb_step_rec *rec = (st.mode == MODE_GYM && a.out) ? &a.out[active ? env : 0] : &scratch_rec[group_in_block];
-  Sim<LOG> sim (st, d, env, rec);
+  __shared__ prb_step_rec scratch_rec[(LOG && !GYM) ? 128 / G : 1];
+  prb_step_rec *rec = GYM ? &a.out[active ? env : 0] : (LOG ? &scratch_rec[group_in_block] : nullptr);
+  Sim<LOG, GYM> sim (st, d, env, rec);
   const int64_t stop = st.sim_time_ns;
   const int64_t until = a.until_ns;
 
   if (active && gl == 0)
     {
-      if (st.mode == MODE_GYM) rec->valid = 0;
+      if (GYM) rec->valid = 0;
       if (sc->finished)
         active = false;
       else
@@ -337,7 +337,7 @@ upload_tables (prb_env *env)
   return PRB_OK;
 }
 
-template <int G, bool LOG>
+template <int G, bool LOG, bool GYM>
 static int
 launch_advance_g (prb_env *env, const LaunchArgs &a)
 {
@@ -348,15 +348,15 @@ launch_advance_g (prb_env *env, const LaunchArgs &a)
   size_t smem = (size_t) envs_per_block * st.blob_bytes;
   /* shared-memory staging pays when the launch executes many events per env (run mode) and the blobs of
    * a block fit; gym-mode launches execute a handful of events and work on the blob in place */
-  bool use_smem = st.mode == MODE_RUN && smem + sizeof (prb_step_rec) * envs_per_block + 1024 <= (size_t) env->max_smem;
+  bool use_smem = !GYM && smem + sizeof (prb_step_rec) * envs_per_block + 1024 <= (size_t) env->max_smem;
   if (use_smem)
     {
-      auto k = k_advance<G, LOG, true>;
+      auto k = k_advance<G, LOG, GYM, true>;
       CUDA_TRY (cudaFuncSetAttribute (k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
       k<<<blocks, threads, smem, env->stream>>> (st, a);
     }
   else
-    k_advance<G, LOG, false><<<blocks, threads, 0, env->stream>>> (st, a);
+    k_advance<G, LOG, GYM, false><<<blocks, threads, 0, env->stream>>> (st, a);
   CUDA_TRY (cudaGetLastError ());
   env->launches++;
   return PRB_OK;
@@ -366,13 +366,18 @@ static int
 launch_advance (prb_env *env, const LaunchArgs &a)
 {
   bool log = env->log_on;
+  bool gym = env->dst.mode == MODE_GYM;
+#define PRB_DISPATCH(G_)                                                                              \
+  if (gym) return log ? launch_advance_g<G_, true, true> (env, a) : launch_advance_g<G_, false, true> (env, a); \
+  return log ? launch_advance_g<G_, true, false> (env, a) : launch_advance_g<G_, false, false> (env, a);
   switch (env->G)
     {
-    case 32: return log ? launch_advance_g<32, true> (env, a) : launch_advance_g<32, false> (env, a);
-    case 16: return log ? launch_advance_g<16, true> (env, a) : launch_advance_g<16, false> (env, a);
-    case 8: return log ? launch_advance_g<8, true> (env, a) : launch_advance_g<8, false> (env, a);
+    case 32: PRB_DISPATCH (32)
+    case 16: PRB_DISPATCH (16)
+    case 8: PRB_DISPATCH (8)
     default: return fail (PRB_EINVAL, "lanes_per_env must be 8, 16 or 32");
     }
+#undef PRB_DISPATCH
 }
 
 extern "C" {

@@ -403,9 +403,11 @@ neglog (double u)
 /* ---------------------------------------------------------------------------------------------
  * The simulator of one environment.  Every method is executed by the group leader only.
  * ------------------------------------------------------------------------------------------- */
-template <bool LOG>
+template <bool LOG, bool GYM>
 struct Sim
 {
+  /* the Gym step record is assembled only when somebody reads it: the parity log or prb_step */
+  static constexpr bool REC = LOG || GYM;
   const Static &st;
   Dyn &d;
   Scal *sc;
@@ -852,27 +854,41 @@ struct Sim
       }
     sc->c.env_steps++;
     int data = type == PRB_DATA;
-    int consult = data && !rec->done;
-    if (st.mode == MODE_GYM)
+    int done = data ? (p_dst (p) == x) : (d.last_dst[m] == x);
+    int consult = data && !done;
+    if (GYM)
       {
         rec->need_action = consult;
         rec->action = -1;
         rec->valid = 1;
         sc->pending = 1;
         sc->pend_link = l; sc->pend_pkt = pi; sc->pend_m = m; sc->pend_consult = consult;
-        sc->pend_done = rec->done; sc->pend_data = data;
+        sc->pend_done = done; sc->pend_data = data;
         return ST_PAUSE;
       }
     int32_t action = 0;
-    if (consult) action = policy_action (m, rec->obs, st.agent_k[m]);
-    rec->action = consult ? action : -1;
-    rec->need_action = 0;
-    rec->valid = 1;
-    if (LOG && st.st_cap > 0)
+    if (consult)
       {
-        if (sc->st_n < st.st_cap) d.st_log[sc->st_n++] = *rec; else sc->c.errors |= PRB_ERR_LOG;
+        if (REC)
+          action = policy_action (m, rec->obs, st.agent_k[m]);
+        else
+          {
+            /* fused run without a reader of the record: the table agent needs obs[0] only */
+            int32_t obs0 = st.map_overlay[p_dst (p)];
+            action = policy_action (m, &obs0, st.agent_k[m]);
+          }
       }
-    finish_step (l, pi, p, m, data, consult, rec->done, action);
+    if (REC)
+      {
+        rec->action = consult ? action : -1;
+        rec->need_action = 0;
+        rec->valid = 1;
+        if (LOG && st.st_cap > 0)
+          {
+            if (sc->st_n < st.st_cap) d.st_log[sc->st_n++] = *rec; else sc->c.errors |= PRB_ERR_LOG;
+          }
+      }
+    finish_step (l, pi, p, m, data, consult, done, action);
     return ST_CONTINUE;
   }
 
@@ -890,6 +906,11 @@ struct Sim
   PRB_HD void
   fill_data_step (int m, int x, const Pkt &p)
   {
+    if (!REC)
+      {
+        d.n_lost[m] = 0;      /* the lost list is flushed by every data step (data-packet-manager.cc:229-237) */
+        return;
+      }
     prb_step_rec *r = rec;
     r->t_ns = sc->now; r->node = x; r->overlay = m; r->uid = (int64_t) p.uid; r->ptype = PRB_DATA;
     r->nobs = build_obs (m, p, r->obs);
@@ -916,6 +937,7 @@ struct Sim
   PRB_HD void
   fill_control_step (int m, int x, const Pkt &p)
   {
+    if (!REC) return;
     prb_step_rec *r = rec;
     r->t_ns = sc->now; r->node = x; r->overlay = m;
     r->uid = p_type (p) == PRB_SMALL_SIGN ? (int64_t) p.uid : -1;
@@ -1153,15 +1175,15 @@ finalize_counters (prb_counters &c)
 /* ---------------------------------------------------------------------------------------------
  * Serial driver (G = 1): used by the host test harness and as the reference for the group version.
  * ------------------------------------------------------------------------------------------- */
-template <bool LOG>
+template <bool LOG, bool GYM>
 PRB_HDN inline void
 run_env_serial (const Static &st, Dyn &d, int env, int64_t until_ns, int32_t action, prb_step_rec *out)
 {
   Scal *sc = d.sc;
   prb_step_rec local;
-  prb_step_rec *rec = (st.mode == MODE_GYM && out) ? out : &local;
-  Sim<LOG> sim (st, d, env, rec);
-  if (st.mode == MODE_GYM) rec->valid = 0;
+  prb_step_rec *rec = (GYM && out) ? out : &local;
+  Sim<LOG, GYM> sim (st, d, env, rec);
+  if (GYM) rec->valid = 0;
   if (sc->finished) return;
   if (!sc->started) sim.start ();
   if (sc->pending) sim.resume (action);

@@ -83,7 +83,7 @@ void
 hs_run (hs_sim *s, int64_t until_ns)
 {
   s->hm.st.mode = MODE_RUN;
-  run_env_serial<true> (s->hm.st, s->d, s->env_index, until_ns, 0, nullptr);
+  run_env_serial<true, false> (s->hm.st, s->d, s->env_index, until_ns, 0, nullptr);
 }
 
 /* Gym mode: one Notify() per call; `action` answers the previous record */
@@ -91,7 +91,15 @@ void
 hs_step (hs_sim *s, int32_t action, prb_step_rec *out)
 {
   s->hm.st.mode = MODE_GYM;
-  run_env_serial<true> (s->hm.st, s->d, s->env_index, s->hm.st.sim_time_ns, action, out);
+  run_env_serial<true, true> (s->hm.st, s->d, s->env_index, s->hm.st.sim_time_ns, action, out);
+}
+
+/* the record-free fast path of fused runs (no log): counters only */
+void
+hs_run_nolog (hs_sim *s, int64_t until_ns)
+{
+  s->hm.st.mode = MODE_RUN;
+  run_env_serial<false, false> (s->hm.st, s->d, s->env_index, until_ns, 0, nullptr);
 }
 
 void

@@ -36,6 +36,7 @@ def lib():
                                           C.POINTER(C.c_uint8), C.POINTER(C.c_uint8)]
         L.hs_set_policy.argtypes = [vp, C.c_int, C.POINTER(i32), i64, C.c_uint64]
         L.hs_run.argtypes = [vp, i64]
+        L.hs_run_nolog.argtypes = [vp, i64]
         L.hs_step.argtypes = [vp, i32, C.POINTER(_abi.PrbStepRec)]
         L.hs_counters.argtypes = [vp, C.POINTER(_abi.PrbCounters)]
         L.hs_num_events.restype = i64
@@ -95,6 +96,9 @@ class HostSim:
 
     def run(self, until_ns=None):
         lib().hs_run(self.h, int(until_ns if until_ns is not None else self.cfg.sim_time_ns))
+
+    def run_nolog(self, until_ns=None):
+        lib().hs_run_nolog(self.h, int(until_ns if until_ns is not None else self.cfg.sim_time_ns))
 
     def step(self, action=0):
         r = _abi.PrbStepRec()

@@ -145,3 +145,21 @@ def test_global_routes_match_oracle(topo):
     host_sim.lib().hs_global_routes(n, arrays.phys_adj.ctypes.data_as(host_sim.C.POINTER(host_sim.C.c_uint8)),
                                     out.ctypes.data_as(host_sim.C.POINTER(host_sim.C.c_int32)))
     assert np.array_equal(out, oracle.global_routes(arrays.phys_adj))
+
+
+def test_core_record_free_fast_path_equals_logged_run():
+    """Fused runs that nobody logs skip the Gym step record (sim_core.cuh Sim::REC == false): counters,
+    queues and clock must not change."""
+    for policy in ("table", "random"):
+        cfg = common.env_config("abilene", simTime=2, load_factor=1.4, max_out_buffer_size=3000, pingAsObs=1,
+                                activateUnderlayTraffic=1, train=1, signaling_type="NN", agent_type="dqn_buffer")
+        arrays = cfg.load()
+        table = common.sp_table(arrays)
+        a = host_sim.HostSim(cfg.abi_params(arrays))
+        a.set_policy(policy, table, seed=5)
+        a.run()
+        b = host_sim.HostSim(cfg.abi_params(arrays))
+        b.set_policy(policy, table, seed=5)
+        b.run_nolog()
+        assert a.counters() == b.counters()
+        assert np.array_equal(a.queue_bytes(), b.queue_bytes())
