@@ -308,6 +308,8 @@ build_model (const prb_config &c, HostModel &hm)
 
   st.E = c.num_envs; st.N = N; st.M = M; st.L = L; st.LA = LA; st.F = F; st.K = K;
   st.S = 2 * LA + M + F;
+  st.NK = 2 * LA + M;
+  st.NKP = align_up (st.NK, 32);
   st.MA = (int32_t) std::max<uint32_t> (c.moving_average_size, 1);
   st.ma_size = c.moving_average_size;
   st.n_szc = n_szc; st.n_rc = (int32_t) rates.size ();
@@ -318,6 +320,11 @@ build_model (const prb_config &c, HostModel &hm)
   st.loss_penalty = (float) c.loss_penalty;
   st.seed = c.seed; st.env_id_base = c.env_id_base; st.policy_seed = 1;
   host_invert_1e9 (&st.inv1e9_hi, &st.inv1e9_lo);
+  if (st.inv1e9_hi != INV1E9_HI || st.inv1e9_lo != INV1E9_LO)
+    {
+      hm.error = "int64x64 inverse of 1e9 differs from the constant compiled into the kernels";
+      return false;
+    }
   /* packet pool: what the byte-limited queues can hold as data packets, plus the wires and slack */
   int P = c.pool_capacity;
   if (P <= 0)
@@ -338,6 +345,7 @@ build_model (const prb_config &c, HostModel &hm)
   st.off_scal = o; o += align_up ((int32_t) sizeof (Scal), 8);
   st.off_t_ts = o; o += 8 * st.S;
   st.off_sent_mask = o; o += 8 * M * K;
+  st.off_t_key = o; o += 4 * st.NKP;
   st.off_t_seq = o; o += 4 * st.S;
   st.off_q_bytes = o; o += 4 * LA;
   st.off_f_pos = o; o += 4 * std::max (F, 1);
@@ -359,6 +367,7 @@ build_model (const prb_config &c, HostModel &hm)
   Dyn d;
   bind_state (st, hm.blob0.data (), d);
   for (int s = 0; s < st.S; s++) d.t_ts[s] = T_IDLE;
+  for (int s = 0; s < st.NKP; s++) d.t_key[s] = KEY_IDLE;
   for (int l = 0; l < LA; l++) d.q_head[l] = d.q_tail[l] = d.w_head[l] = d.w_tail[l] = NIL;
   for (int m = 0; m < M; m++) d.last_dst[m] = -1;
   d.sc->free_head = 0;

@@ -57,39 +57,22 @@ struct LaunchArgs
   int64_t until_ns;
 };
 
-/* minimum (ts, seq) over the lanes of a group; every lane of the group gets the winner's slot */
+/* minimum (key, uid) over the lanes of a group; every lane gets the winning slot (or -1) and its key */
 template <int G>
 __device__ __forceinline__ void
-group_min (unsigned gmask, int64_t ts, uint32_t seq, int slot, int64_t &mts, uint32_t &mseq, int &mslot)
+group_min (unsigned gmask, const uint32_t *t_seq, uint32_t key, int slot, uint32_t &mkey, int &mslot)
 {
-  uint32_t hi = (uint32_t) ((uint64_t) ts >> 32), lo = (uint32_t) (uint64_t) ts;
-  uint32_t mhi = __reduce_min_sync (gmask, hi);
-  uint32_t mlo = __reduce_min_sync (gmask, hi == mhi ? lo : 0xFFFFFFFFu);
-  bool cand = hi == mhi && lo == mlo;
-  uint32_t ms = __reduce_min_sync (gmask, cand ? seq : 0xFFFFFFFFu);
-  unsigned b = __ballot_sync (gmask, cand && seq == ms);
-  int src = __ffs (b) - 1;
-  mslot = __shfl_sync (gmask, slot, src);
-  mts = (int64_t) (((uint64_t) mhi << 32) | mlo);
-  mseq = ms;
-}
-
-/* per-lane scan of timer slots first, first+G, ... < last: keeps the (ts, seq) minimum */
-template <int G>
-__device__ __forceinline__ void
-scan_slots (const int64_t *t_ts, const uint32_t *t_seq, int first, int last, int64_t &bts, uint32_t &bseq, int &bslot)
-{
-  for (int s = first; s < last; s += G)
+  mkey = __reduce_min_sync (gmask, key);
+  bool cand = key == mkey;
+  unsigned b = __ballot_sync (gmask, cand);
+  if (mkey != KEY_IDLE && (b & (b - 1)))
     {
-      int64_t t = t_ts[s];
-      if (t > bts) continue;
-      if (t == T_IDLE) continue;
-      uint32_t q = t_seq[s];
-      if (t < bts || q < bseq)
-        {
-          bts = t; bseq = q; bslot = s;
-        }
+      /* several lanes hold the same timestamp: the scheduler uid decides */
+      uint32_t q = cand ? t_seq[slot] : 0xFFFFFFFFu;
+      uint32_t mq = __reduce_min_sync (gmask, q);
+      b = __ballot_sync (gmask, cand && q == mq);
     }
+  mslot = __shfl_sync (gmask, slot, __ffs (b) - 1);
 }
 
 /* Advance every environment: run mode until `until_ns`, gym mode until the next valid Notify().
@@ -99,13 +82,12 @@ __global__ void __launch_bounds__ (128, LOG ? 4 : 7)
 k_advance (const __grid_constant__ Static st, const LaunchArgs a)
 {
   extern __shared__ __align__ (16) char smem[];
-  constexpr int GROUPS_PER_WARP = 32 / G;
   const int lane = threadIdx.x & 31;
   const int gl = lane % G;                                   /* lane inside the group */
+  const int leader = (lane / G) * G;
   const int group_in_block = threadIdx.x / G;
   const int env = blockIdx.x * (blockDim.x / G) + group_in_block;
-  const unsigned gmask = G == 32 ? 0xFFFFFFFFu : (((1u << G) - 1u) << ((lane / G) * G));
-  (void) GROUPS_PER_WARP;
+  const unsigned gmask = G == 32 ? 0xFFFFFFFFu : (((1u << G) - 1u) << leader);
   bool active = env < st.E;
   char *gblob = a.blobs + (size_t) (active ? env : 0) * st.blob_bytes;
   char *blob = gblob;
@@ -132,6 +114,7 @@ k_advance (const __grid_constant__ Static st, const LaunchArgs a)
   const int64_t stop = st.sim_time_ns;
   const int64_t until = a.until_ns;
 
+  int active_resume = 0;      /* gym mode: the first thing to run is the rest of the suspended Receive */
   if (active && gl == 0)
     {
       if (GYM) rec->valid = 0;
@@ -140,56 +123,60 @@ k_advance (const __grid_constant__ Static st, const LaunchArgs a)
       else
         {
           if (!sc->started) sim.start ();
-          if (sc->pending) sim.resume (a.actions ? a.actions[env] : 0);
+          if (sc->pending) active_resume = 1;
         }
     }
-  active = __shfl_sync (gmask, active ? 1 : 0, (lane / G) * G) != 0;
+  active = __shfl_sync (gmask, active ? 1 : 0, leader) != 0;
+  active_resume = __shfl_sync (gmask, active_resume, leader);
   __syncwarp (gmask);
 
   /* flows are scanned lazily: a lane rescans its flow slots only after one of them fired */
-  const int flow0 = 2 * st.LA + st.M;
   int64_t fts = T_IDLE; uint32_t fseq = 0xFFFFFFFFu; int fslot = -1;
-  if (active) scan_slots<G> (d.t_ts, d.t_seq, flow0 + gl, st.S, fts, fseq, fslot);
+  if (active) scan_flows (st, d, gl, G, fts, fseq, fslot);
 
   while (__any_sync (gmask, active))
     {
-      int64_t bts = fts; uint32_t bseq = fseq; int bslot = fslot;
-      if (active) scan_slots<G> (d.t_ts, d.t_seq, gl, flow0, bts, bseq, bslot);
-      int64_t mts; uint32_t mseq; int mslot;
-      group_min<G> (gmask, bts, bseq, bslot, mts, mseq, mslot);
-      if (!active) continue;
-      int status = ST_CONTINUE;
-      bool stop_now = false;
-      if (mts == T_IDLE)
+      uint32_t bk = KEY_IDLE;
+      int bslot = -1;
+      if (active && !active_resume)
         {
-          if (gl == 0) sc->finished = 1;
-          stop_now = true;
+          scan_keys (st, d, gl, G, bk, bslot);
+          uint32_t fk = flow_key (sc, fts);
+          if (fk < bk || (fk == bk && fk != KEY_IDLE && fseq < d.t_seq[bslot]))
+            {
+              bk = fk;
+              bslot = fslot;
+            }
         }
-      else if (mts > stop || (mts == stop && mseq > sc->stop_seq))
+      uint32_t mkey; int mslot;
+      group_min<G> (gmask, d.t_seq, bk, bslot, mkey, mslot);
+      if (!active) continue;
+      int32_t action = 0;
+      if (active_resume)
         {
+          mslot = SLOT_RESUME;
+          mkey = 0;
+          action = a.actions ? a.actions[env] : 0;
+          active_resume = 0;
+        }
+      if (mkey == KEY_FAR)
+        {
+          /* every armed timer is beyond the key range (rare): new epoch, exact search by the leader */
           if (gl == 0)
             {
-              sc->now = stop;
-              sc->finished = 1;
+              sim.rebase (sc->now);
+              mslot = slow_min (st, d);
             }
-          stop_now = true;
+          __syncwarp (gmask);
+          mslot = __shfl_sync (gmask, mslot, leader);
         }
-      else if (mts >= until && until < stop)
-        stop_now = true;
-      if (stop_now)
-        {
-          active = false;
-          continue;
-        }
-      if (gl == 0) status = sim.handle (mslot, mts);
+      int status = ST_CONTINUE;
+      int go = 1;
+      if (gl == 0) go = step_or_stop (st, sim, mslot, until, action, status) ? 1 : 0;
       __syncwarp (gmask);
-      status = __shfl_sync (gmask, status, (lane / G) * G);
-      if (mslot >= flow0 && mslot == fslot)
-        {
-          fts = T_IDLE; fseq = 0xFFFFFFFFu; fslot = -1;
-          scan_slots<G> (d.t_ts, d.t_seq, flow0 + gl, st.S, fts, fseq, fslot);
-        }
-      if (status == ST_PAUSE) active = false;
+      go = __shfl_sync (gmask, go, leader);
+      if (mslot == fslot && mslot >= 0) scan_flows (st, d, gl, G, fts, fseq, fslot);
+      if (!go) active = false;
     }
   __syncwarp (gmask);
   if (env < st.E && gl == 0)
@@ -243,9 +230,10 @@ k_counters (const __grid_constant__ Static st, const char *blobs, prb_counters *
 {
   int e = blockIdx.x * blockDim.x + threadIdx.x;
   if (e >= st.E) return;
-  const Scal *sc = (const Scal *) (blobs + (size_t) e * st.blob_bytes + st.off_scal);
-  prb_counters c = sc->c;
-  finalize_counters (c);
+  Dyn d;
+  bind_state (st, const_cast<char *> (blobs) + (size_t) e * st.blob_bytes, d);
+  prb_counters c;
+  finalize_counters (st, d, c);
   out[e] = c;
 }
 

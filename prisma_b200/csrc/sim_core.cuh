@@ -42,10 +42,13 @@ namespace prb {
 
 constexpr int64_t T_IDLE = INT64_MAX;
 constexpr uint16_t NIL = 0xFFFF;
+constexpr uint32_t KEY_IDLE = 0xFFFFFFFFu;   /* scan key of an unarmed slot */
+constexpr uint32_t KEY_FAR = 0xFFFFFFFEu;    /* saturated: at least 2^32-2 ns after the epoch */
 constexpr int NODE_NONE = 255;         /* packed stand-in for lastHop = 1000 / prev_node = -1 */
 
 enum { MODE_RUN = 0, MODE_GYM = 1 };
 enum { ST_CONTINUE = 0, ST_PAUSE = 1 };
+enum { SLOT_NONE = -1, SLOT_RESUME = -2 };   /* SLOT_RESUME: finish the suspended Receive of gym mode */
 
 /* size classes of packets on the wire */
 enum { SZC_DATA_INJ = 0, SZC_DATA_FWD = 1, SZC_PING = 2, SZC_SIGN0 = 3, MAX_SZC = 16 };
@@ -91,6 +94,7 @@ PRB_FIELD (p_prev_node, 56, 8)
 struct Static
 {
   int32_t E, N, M, L, LA, F, K, S, P, MA;
+  int32_t NK, NKP;                     /* non-flow timer slots (2*LA + M) and their count padded to 32 */
   int32_t n_szc, n_rc;
   int64_t link_delay_ns, sim_time_ns, ping_interval_ns;
   uint32_t max_out_buffer, ma_size;
@@ -121,7 +125,7 @@ struct Static
   const int32_t *tr_next;              /* next injection of the same flow or -1 */
   const int32_t *flow_first;           /* [F] first trace index or -1 */
   /* state blob layout (byte offsets inside one env's blob) */
-  int32_t off_scal, off_t_ts, off_sent_mask, off_t_seq, off_q_bytes, off_f_pos, off_ping_index, off_win,
+  int32_t off_scal, off_t_ts, off_sent_mask, off_t_key, off_t_seq, off_q_bytes, off_f_pos, off_ping_index, off_win,
       off_lost, off_n_lost, off_q_pkts, off_q_head, off_q_tail, off_w_head, off_w_tail, off_last_dst, off_n_win,
       off_sent_old;
   int32_t blob_bytes;
@@ -131,11 +135,14 @@ struct Static
 struct Scal
 {
   int64_t now;
+  int64_t epoch;            /* scan keys are (ts - epoch) in 32 bits */
+  int64_t front_ts;         /* scheduler frontier: events with (ts, seq) below it have executed */
   uint64_t pol_rng;
   int64_t pol_pos;
   int64_t ev_n, st_n;
   uint32_t seq, stop_seq;
   uint32_t next_uid;
+  uint32_t front_seq, pend_seq;
   int32_t started, finished;
   int32_t pending;          /* gym mode: 1 = a step record is out and its Receive is suspended */
   int32_t pend_link, pend_pkt, pend_m, pend_consult, pend_done, pend_data;
@@ -150,6 +157,7 @@ struct Dyn
   Scal *sc;
   int64_t *t_ts;
   uint32_t *t_seq;
+  uint32_t *t_key;
   uint64_t *sent_mask;
   uint32_t *q_bytes, *f_pos, *ping_index, *lost, *n_lost;
   float *win;
@@ -168,6 +176,7 @@ bind_state (const Static &st, char *blob, Dyn &d)
   d.t_ts = (int64_t *) (blob + st.off_t_ts);
   d.sent_mask = (uint64_t *) (blob + st.off_sent_mask);
   d.t_seq = (uint32_t *) (blob + st.off_t_seq);
+  d.t_key = (uint32_t *) (blob + st.off_t_key);
   d.q_bytes = (uint32_t *) (blob + st.off_q_bytes);
   d.f_pos = (uint32_t *) (blob + st.off_f_pos);
   d.ping_index = (uint32_t *) (blob + st.off_ping_index);
@@ -185,7 +194,11 @@ bind_state (const Static &st, char *blob, Dyn &d)
 }
 
 /* timer slots: [0,LA) TransmitComplete of link l; [LA,2LA) head-of-wire Receive of link l;
- * [2LA,2LA+M) ping timer of overlay node m; [2LA+M, 2LA+M+F) next injection of flow f */
+ * [2LA,2LA+M) ping timer of overlay node m; [2LA+M, 2LA+M+F) next injection of flow f.
+ * The first NK = 2LA+M slots also carry a 32-bit scan key (t_key) that the group scans per event.  A
+ * TransmitComplete whose queue is empty does nothing but mark the device idle, so its slot stays unarmed
+ * (key idle) and the event is elided: Send compares its (ts, uid) with the running event's instead, and
+ * the slot is armed only once a packet waits behind the one on the wire. */
 PRB_HD int slot_txc (const Static &st, int l) { (void) st; return l; }
 PRB_HD int slot_rcv (const Static &st, int l) { return st.LA + l; }
 PRB_HD int slot_ping (const Static &st, int m) { return 2 * st.LA + m; }
@@ -241,13 +254,23 @@ pow2_ (int e)   /* 2^e, -1022 <= e <= 1023 */
  * int64x64-128.cc:191-214), GetDouble adds the two words as long double and narrows to double
  * (int64x64-128.h:203-213).  The x87 sum rounds to a 64-bit significand, the narrowing to 53 bits:
  * both roundings are reproduced here with integers. */
-PRB_HD double
-ns_to_seconds (const Static &st, int64_t ns)
+/* int64x64_t::Invert (1e9) = floor (2^128 / 1e9) (+0: the round trip gives 1); model.h recomputes it and
+ * refuses to build a model if it differs */
+constexpr uint64_t INV1E9_HI = 18446744073ull;
+constexpr uint64_t INV1E9_LO = 13088917067439035464ull;
+
+#if defined(__CUDACC__)
+__host__ __device__ __noinline__
+#else
+inline
+#endif
+double
+ns_to_seconds_ (int64_t ns)
 {
   uint64_t a = (uint64_t) ns;
   /* q = a*inv_hi + ((a*inv_lo) >> 64), a 128-bit Q64.64 value */
-  uint64_t lo1 = a * st.inv1e9_hi, hi1 = umul64hi_ (a, st.inv1e9_hi);
-  uint64_t add = umul64hi_ (a, st.inv1e9_lo);
+  uint64_t lo1 = a * INV1E9_HI, hi1 = umul64hi_ (a, INV1E9_HI);
+  uint64_t add = umul64hi_ (a, INV1E9_LO);
   uint64_t q_lo = lo1 + add;
   uint64_t q_hi = hi1 + (q_lo < lo1 ? 1 : 0);
   if (q_hi == 0)
@@ -268,6 +291,13 @@ ns_to_seconds (const Static &st, int64_t ns)
         }
     }
   return u64_to_double_rn (m) * pow2_ (s - 64);
+}
+
+PRB_HD double
+ns_to_seconds (const Static &st, int64_t ns)
+{
+  (void) st;
+  return ns_to_seconds_ (ns);
 }
 
 PRB_HD double dmul_ (double a, double b)
@@ -412,31 +442,52 @@ struct Sim
   Dyn &d;
   Scal *sc;
   int env;
-  uint32_t dirty;        /* bit (slot & 31): timer slots written by the current event */
+  uint32_t cur_seq;      /* scheduler uid of the running event */
+  /* Sends requested by the running event are executed after its handler, in order, by ONE inlined copy of
+   * Send/TransmitStart (flush_sends): the first waits in registers, further ones are chained through the
+   * pool (link id parked in rcv_seq).  post_kind: what the event schedules after its sends. */
+  int ps_n, ps_l0, ps_pi0;
+  Pkt ps_q0;
+  uint16_t ps_head, ps_tail;
+  int post_kind, post_arg;
   prb_step_rec *rec;     /* where the current Gym step is assembled */
 
-  PRB_HD Sim (const Static &st_, Dyn &d_, int env_, prb_step_rec *rec_) : st (st_), d (d_), sc (d_.sc), env (env_), dirty (0), rec (rec_) {}
+  PRB_HD Sim (const Static &st_, Dyn &d_, int env_, prb_step_rec *rec_) : st (st_), d (d_), sc (d_.sc), env (env_), cur_seq (0), ps_n (0), ps_l0 (0), ps_pi0 (0), ps_head (NIL), ps_tail (NIL), post_kind (0), post_arg (0), rec (rec_) {}
 
   /* ---- timers ---- */
+  PRB_HD uint32_t
+  mk_key (int64_t ts) const
+  {
+    uint64_t dlt = (uint64_t) (ts - sc->epoch);
+    return dlt < (uint64_t) KEY_FAR ? (uint32_t) dlt : KEY_FAR;
+  }
   PRB_HD void
   set_timer (int slot, int64_t ts)
   {
     d.t_ts[slot] = ts;
     d.t_seq[slot] = sc->seq++;
-    dirty |= 1u << (slot & 31);
+    if (slot < st.NK) d.t_key[slot] = mk_key (ts);
   }
   PRB_HD void
   put_timer (int slot, int64_t ts, uint32_t seq)
   {
     d.t_ts[slot] = ts;
     d.t_seq[slot] = seq;
-    dirty |= 1u << (slot & 31);
+    if (slot < st.NK) d.t_key[slot] = mk_key (ts);
   }
   PRB_HD void
   clear_timer (int slot)
   {
     d.t_ts[slot] = T_IDLE;
-    dirty |= 1u << (slot & 31);
+    if (slot < st.NK) d.t_key[slot] = KEY_IDLE;
+  }
+  /* new epoch: every armed key is rewritten from the 64-bit truth */
+  PRB_HD void
+  rebase (int64_t epoch)
+  {
+    sc->epoch = epoch;
+    for (int s2 = 0; s2 < st.NK; s2++)
+      if (d.t_key[s2] != KEY_IDLE) d.t_key[s2] = mk_key (d.t_ts[s2]);
   }
 
   /* ---- packet pool ---- */
@@ -510,7 +561,10 @@ struct Sim
     if (l < st.L) log_event (PRB_EV_TXB, st.link_from[l], l, p, (int) d.q_bytes[l]);
     int64_t tx = st.tx_ns[st.link_rc[l] * MAX_SZC + p_szc (p)];
     int64_t delay = l < st.L ? st.link_delay_ns : 0;
-    set_timer (slot_txc (st, l), sc->now + tx);
+    /* TransmitComplete: scheduled (it takes a scheduler uid) but armed only while a packet waits */
+    d.t_ts[l] = sc->now + tx;
+    d.t_seq[l] = sc->seq++;
+    d.t_key[l] = d.q_head[l] != NIL ? mk_key (sc->now + tx) : KEY_IDLE;
     p.rcv_ts = sc->now + tx + delay;
     p.rcv_seq = sc->seq++;
     p.next = NIL;
@@ -572,12 +626,22 @@ struct Sim
         return;
       }
     if (l < st.L) log_event (PRB_EV_ENQ, node, l, p, (int) (qb + size));
-    if (d.t_ts[slot_txc (st, l)] == T_IDLE)
+    int64_t tc = d.t_ts[l];
+    bool busy = tc != T_IDLE;
+    if (busy && d.t_key[l] == KEY_IDLE && (tc < sc->now || (tc == sc->now && d.t_seq[l] < cur_seq)))
+      {
+        /* the elided TransmitComplete lies before the running event in scheduler order: it has happened */
+        sc->c.events++;
+        d.t_ts[l] = T_IDLE;
+        busy = false;
+      }
+    if (!busy)
       {
         /* READY: the packet goes through the (empty) queue straight to the wire */
         transmit_start (l, pi, p);
         return;
       }
+    if (d.t_key[l] == KEY_IDLE) d.t_key[l] = mk_key (tc);   /* a packet waits: the completion becomes a real event */
     p.next = NIL;
     d.pool[pi] = p;
     uint16_t t = d.q_tail[l];
@@ -585,6 +649,46 @@ struct Sim
     d.q_tail[l] = (uint16_t) pi;
     d.q_bytes[l] = qb + size;
     d.q_pkts[l] = (uint16_t) (qp + 1);
+  }
+
+  PRB_HD void
+  post_send (int l, int pi, const Pkt &p)
+  {
+    if (ps_n == 0)
+      {
+        ps_l0 = l; ps_pi0 = pi; ps_q0 = p;
+      }
+    else
+      {
+        Pkt q = p;
+        q.rcv_seq = (uint32_t) l;
+        q.next = NIL;
+        d.pool[pi] = q;
+        if (ps_tail == NIL) ps_head = (uint16_t) pi; else d.pool[ps_tail].next = (uint16_t) pi;
+        ps_tail = (uint16_t) pi;
+      }
+    ps_n++;
+  }
+
+  PRB_HD void
+  flush_sends ()
+  {
+    while (ps_n > 0)
+      {
+        int l = ps_l0, pi = ps_pi0;
+        Pkt p = ps_q0;
+        ps_n--;
+        if (ps_n > 0)
+          {
+            /* next request comes out of the chain */
+            ps_pi0 = ps_head;
+            ps_q0 = d.pool[ps_head];
+            ps_l0 = (int) ps_q0.rcv_seq;
+            ps_head = ps_q0.next;
+            if (ps_head == NIL) ps_tail = NIL;
+          }
+        dev_send (l, pi, p);
+      }
   }
 
   /* PointToPointNetDevice::TransmitComplete */
@@ -697,7 +801,7 @@ struct Sim
     set_p_prev_node (q, NODE_NONE);
     set_p_szc (q, st.agent_sign_szc[m]);
     q.uid = p.uid; q.aux = 0;
-    dev_send (in_link ^ 1, qi, q);
+    post_send (in_link ^ 1, qi, q);
   }
 
   /* PingForwardPacketManager::receivePacket / sendPingBackPacket */
@@ -722,7 +826,7 @@ struct Sim
 #else
     memcpy (&q.aux, &delay, 4);
 #endif
-    dev_send (in_link ^ 1, qi, q);
+    post_send (in_link ^ 1, qi, q);
   }
 
   /* PingBackPacketManager::receivePacket */
@@ -786,9 +890,9 @@ struct Sim
         set_p_szc (q, SZC_PING);
         set_p_tunnel (q, t);
         q.uid = idx; q.aux = ms;
-        dev_send (st.route[node * st.N + nb], qi, q);
+        post_send (st.route[node * st.N + nb], qi, q);
       }
-    set_timer (slot_ping (st, m), sc->now + st.ping_interval_ns);
+    post_kind = 2; post_arg = m;     /* the timer is rescheduled after the sends (data-packet-manager.cc:349-357) */
   }
 
   /* ---- Receive: part A (up to the agent's observation) ---- */
@@ -864,6 +968,8 @@ struct Sim
         sc->pending = 1;
         sc->pend_link = l; sc->pend_pkt = pi; sc->pend_m = m; sc->pend_consult = consult;
         sc->pend_done = done; sc->pend_data = data;
+        sc->pend_seq = cur_seq;
+        sc->front_ts = sc->now; sc->front_seq = cur_seq;
         return ST_PAUSE;
       }
     int32_t action = 0;
@@ -899,6 +1005,7 @@ struct Sim
     int l = sc->pend_link, pi = sc->pend_pkt;
     Pkt p = d.pool[pi];
     sc->pending = 0;
+    cur_seq = sc->pend_seq;
     finish_step (l, pi, p, sc->pend_m, sc->pend_data, sc->pend_consult, sc->pend_done, sc->pend_consult ? action : 0);
   }
 
@@ -974,7 +1081,7 @@ struct Sim
                     set_p_szc (q, SZC_DATA_FWD);
                     set_p_tracked (q, 1); set_p_prev_node (q, node);
                     q.prev_t = sc->now;
-                    dev_send (st.route[node * st.N + nb], qi, q);
+                    post_send (st.route[node * st.N + nb], qi, q);
                   }
               }
             else
@@ -1006,7 +1113,7 @@ struct Sim
     else
       {
         forwarded = true;
-        dev_send (st.route[x * st.N + p_ipdst (p)], pi, p);
+        post_send (st.route[x * st.N + p_ipdst (p)], pi, p);
       }
     if (data && p_dst (o) == x)
       {
@@ -1098,20 +1205,26 @@ struct Sim
       }
     else
       {
-        uint64_t eid = st.env_id_base + (uint64_t) env;
-        uint32_t r[4];
-        philox4x32 ((uint32_t) eid, (uint32_t) (eid >> 32), (uint32_t) (src * st.N + dst), d.f_pos[f] - 1,
-                    (uint32_t) st.seed, (uint32_t) (st.seed >> 32), r);
-        double u = dmul_ (dadd_ ((double) r[2], 0.5), 1.0 / 4294967296.0);
         p.uid = sc->next_uid++;
         set_p_valable (p, both ? 1 : 0);
         double prej = (st.opt_agent && st.opt_rejected) ? st.opt_rejected[src * st.N + dst] : 0.0;
-        set_p_rejected (p, u < prej ? 1 : 0);
+        int rej = 0;
+        if (prej > 0.0)
+          {
+            /* u in (0,1) < prej can only hold for prej > 0: the draw is skipped otherwise */
+            uint64_t eid = st.env_id_base + (uint64_t) env;
+            uint32_t r[4];
+            philox4x32 ((uint32_t) eid, (uint32_t) (eid >> 32), (uint32_t) (src * st.N + dst), d.f_pos[f] - 1,
+                        (uint32_t) st.seed, (uint32_t) (st.seed >> 32), r);
+            double u = dmul_ (dadd_ ((double) r[2], 0.5), 1.0 / 4294967296.0);
+            rej = u < prej ? 1 : 0;
+          }
+        set_p_rejected (p, rej);
       }
     set_p_first_hop (p, p_valable (p));
     set_p_ipdst (p, dst);
-    if (pi >= 0) dev_send (st.L + src, pi, p);
-    schedule_flow (f, false);
+    if (pi >= 0) post_send (st.L + src, pi, p);
+    post_kind = 1; post_arg = f;     /* ScheduleNextTx after the send (poisson-application.cc:357) */
   }
 
   /* ping timers are scheduled while the envs are built, Simulator::Stop right before Run
@@ -1125,46 +1238,138 @@ struct Sim
     for (int f = 0; f < st.F; f++) schedule_flow (f, true);
   }
 
-  /* executes the event in timer slot `slot` (the group's minimum) */
+  /* executes the event in timer slot `slot` (the group's minimum), or resumes the suspended one */
   PRB_HD int
-  handle (int slot, int64_t ts)
+  handle (int slot, int64_t ts, uint32_t seq, int32_t action)
   {
-    sc->now = ts;
-    sc->c.events++;
-    if (slot < st.LA)
+    int status = ST_CONTINUE;
+    ps_n = 0; ps_head = NIL; ps_tail = NIL; post_kind = 0;
+    if (slot == SLOT_RESUME)
+      resume (action);
+    else
       {
-        transmit_complete (slot);
-        return ST_CONTINUE;
-      }
-    if (slot < 2 * st.LA)
-      {
-        int l = slot - st.LA;
-        uint16_t h = d.w_head[l];
-        uint16_t nx = d.pool[h].next;
-        d.w_head[l] = nx;
-        if (nx == NIL)
+        sc->now = ts;
+        cur_seq = seq;
+        sc->c.events++;
+        if (ts - sc->epoch > (1ll << 31)) rebase (ts);
+        if (slot < st.LA)
+          transmit_complete (slot);
+        else if (slot < 2 * st.LA)
           {
-            d.w_tail[l] = NIL;
-            clear_timer (slot);
+            int l = slot - st.LA;
+            uint16_t h = d.w_head[l];
+            uint16_t nx = d.pool[h].next;
+            d.w_head[l] = nx;
+            if (nx == NIL)
+              {
+                d.w_tail[l] = NIL;
+                clear_timer (slot);
+              }
+            else
+              put_timer (slot, d.pool[nx].rcv_ts, d.pool[nx].rcv_seq);
+            status = receive (l, h);
           }
+        else if (slot < 2 * st.LA + st.M)
+          ping_timer (slot - 2 * st.LA);
         else
-          put_timer (slot, d.pool[nx].rcv_ts, d.pool[nx].rcv_seq);
-        return receive (l, h);
+          inject (slot - 2 * st.LA - st.M);
       }
-    if (slot < 2 * st.LA + st.M)
-      {
-        ping_timer (slot - 2 * st.LA);
-        return ST_CONTINUE;
-      }
-    inject (slot - 2 * st.LA - st.M);
-    return ST_CONTINUE;
+    flush_sends ();
+    if (post_kind == 1)
+      schedule_flow (post_arg, false);
+    else if (post_kind == 2)
+      set_timer (slot_ping (st, post_arg), sc->now + st.ping_interval_ns);
+    return status;
   }
 };
 
+/* ---------------------------------------------------------------------------------------------
+ * Next-event search.  Per event every lane of the group looks at its share of the 32-bit scan keys
+ * (slots gl, gl+G, ...) and at its cached flow minimum; the group then reduces (key, uid).
+ * ------------------------------------------------------------------------------------------- */
+
+/* one lane's share of the key scan; (bk, bslot) start as (KEY_IDLE, -1) */
+PRB_HD void
+scan_keys (const Static &st, const Dyn &d, int gl, int G, uint32_t &bk, int &bslot)
+{
+  for (int s = gl; s < st.NKP; s += G)
+    {
+      uint32_t k = d.t_key[s];
+      if (k < bk || (k == bk && k != KEY_IDLE && d.t_seq[s] < d.t_seq[bslot]))
+        {
+          bk = k;
+          bslot = s;
+        }
+    }
+}
+
+/* one lane's share of the flow timers (exact 64-bit): slots NK+gl, NK+gl+G, ... */
+PRB_HD void
+scan_flows (const Static &st, const Dyn &d, int gl, int G, int64_t &fts, uint32_t &fseq, int &fslot)
+{
+  fts = T_IDLE; fseq = 0xFFFFFFFFu; fslot = -1;
+  for (int s = st.NK + gl; s < st.S; s += G)
+    {
+      int64_t t = d.t_ts[s];
+      if (t == T_IDLE || t > fts) continue;
+      uint32_t q = d.t_seq[s];
+      if (t < fts || q < fseq)
+        {
+          fts = t; fseq = q; fslot = s;
+        }
+    }
+}
+
+PRB_HD uint32_t
+flow_key (const Scal *sc, int64_t fts)
+{
+  if (fts == T_IDLE) return KEY_IDLE;
+  uint64_t dlt = (uint64_t) (fts - sc->epoch);
+  return dlt < (uint64_t) KEY_FAR ? (uint32_t) dlt : KEY_FAR;
+}
+
+/* exact search over the 64-bit truth: only used when every armed timer is farther than the key range */
+PRB_HD int
+slow_min (const Static &st, const Dyn &d)
+{
+  int best = -1;
+  int64_t bts = T_IDLE;
+  uint32_t bseq = 0;
+  for (int s = 0; s < st.S; s++)
+    {
+      if (s < st.NK && d.t_key[s] == KEY_IDLE) continue;
+      int64_t t = d.t_ts[s];
+      if (t == T_IDLE) continue;
+      uint32_t q = d.t_seq[s];
+      if (best < 0 || t < bts || (t == bts && q < bseq))
+        {
+          best = s; bts = t; bseq = q;
+        }
+    }
+  return best;
+}
+
+/* TransmitComplete events that were elided and lie before the scheduler frontier: they count as executed */
+PRB_HD int64_t
+elided_before_frontier (const Static &st, const Dyn &d)
+{
+  const Scal *sc = d.sc;
+  int64_t n = 0;
+  for (int l = 0; l < st.LA; l++)
+    {
+      int64_t tc = d.t_ts[l];
+      if (tc != T_IDLE && d.t_key[l] == KEY_IDLE && (tc < sc->front_ts || (tc == sc->front_ts && d.t_seq[l] < sc->front_seq)))
+        n++;
+    }
+  return n;
+}
+
 /* ComputeStats::getAverage / getSignalingOverhead at read-out (compute-stats-v2.cc:87-97,263-266) */
 PRB_HD void
-finalize_counters (prb_counters &c)
+finalize_counters (const Static &st, const Dyn &d, prb_counters &c)
 {
+  c = d.sc->c;
+  c.events += elided_before_frontier (st, d);
   c.avg_e2e = c.n_e2e ? c.sum_e2e / (float) c.n_e2e : 0.0f;
   c.avg_cost = c.n_cost ? c.sum_cost / (float) c.n_cost : 0.0f;
   c.avg_underlay_e2e = c.n_underlay_e2e ? c.sum_underlay_e2e / (float) c.n_underlay_e2e : 0.0f;
@@ -1172,8 +1377,46 @@ finalize_counters (prb_counters &c)
   c.signaling_overhead = c.bytes_data ? (float) (int32_t) c.bytes_signaling / (float) (int32_t) c.bytes_data : 0.0f;
 }
 
+/* what the loop does once the next event (slot, ts, seq) is known; returns false when the env stops here */
+template <bool LOG, bool GYM>
+PRB_HD bool
+step_or_stop (const Static &st, Sim<LOG, GYM> &sim, int slot, int64_t until_ns, int32_t action, int &status)
+{
+  Scal *sc = sim.sc;
+  const int64_t stop = st.sim_time_ns;
+  status = ST_CONTINUE;
+  if (slot == SLOT_RESUME)
+    {
+      status = sim.handle (SLOT_RESUME, 0, 0, action);
+      return status != ST_PAUSE;
+    }
+  if (slot < 0)
+    {
+      sc->finished = 1;
+      sc->front_ts = stop; sc->front_seq = sc->stop_seq;
+      return false;
+    }
+  int64_t ts = sim.d.t_ts[slot];
+  uint32_t seq = sim.d.t_seq[slot];
+  if (ts > stop || (ts == stop && seq > sc->stop_seq))
+    {
+      sc->now = stop;
+      sc->finished = 1;
+      sc->front_ts = stop; sc->front_seq = sc->stop_seq;
+      return false;
+    }
+  if (ts >= until_ns && until_ns < stop)
+    {
+      sc->front_ts = until_ns; sc->front_seq = 0;
+      return false;
+    }
+  status = sim.handle (slot, ts, seq, 0);
+  return status != ST_PAUSE;
+}
+
 /* ---------------------------------------------------------------------------------------------
- * Serial driver (G = 1): used by the host test harness and as the reference for the group version.
+ * Serial driver (a group of one lane): the host test harness runs this; the kernels run the same
+ * scan/handle functions with G lanes and warp reductions (prisma_b200.cu).
  * ------------------------------------------------------------------------------------------- */
 template <bool LOG, bool GYM>
 PRB_HDN inline void
@@ -1186,38 +1429,40 @@ run_env_serial (const Static &st, Dyn &d, int env, int64_t until_ns, int32_t act
   if (GYM) rec->valid = 0;
   if (sc->finished) return;
   if (!sc->started) sim.start ();
-  if (sc->pending) sim.resume (action);
-  int64_t stop = st.sim_time_ns;
+  bool resume_first = sc->pending != 0;
+  const int64_t stop = st.sim_time_ns;
+  int64_t fts; uint32_t fseq; int fslot;
+  scan_flows (st, d, 0, 1, fts, fseq, fslot);
   for (;;)
     {
-      int best = -1;
-      int64_t bts = T_IDLE;
-      uint32_t bseq = 0;
-      for (int s = 0; s < st.S; s++)
+      uint32_t bk = KEY_IDLE;
+      int bslot = -1;
+      if (resume_first)
         {
-          int64_t t = d.t_ts[s];
-          if (t == T_IDLE) continue;
-          uint32_t q = d.t_seq[s];
-          if (best < 0 || t < bts || (t == bts && q < bseq))
-            {
-              best = s; bts = t; bseq = q;
-            }
+          int status;
+          resume_first = false;
+          if (!step_or_stop (st, sim, SLOT_RESUME, until_ns, action, status)) break;
+          continue;
         }
-      if (best < 0)
+      scan_keys (st, d, 0, 1, bk, bslot);
+      uint32_t fk = flow_key (sc, fts);
+      if (fk < bk || (fk == bk && fk != KEY_IDLE && fseq < d.t_seq[bslot]))
         {
-          sc->finished = 1;
-          break;
+          bk = fk;
+          bslot = fslot;
         }
-      if (bts > stop || (bts == stop && bseq > sc->stop_seq))
+      if (bk == KEY_FAR)
         {
-          sc->now = stop;
-          sc->finished = 1;
-          break;
+          /* everything armed is far away: move the epoch up to the clock, then fall back to the exact search */
+          sim.rebase (sc->now);
+          bslot = slow_min (st, d);
         }
-      if (bts >= until_ns && until_ns < stop) break;
-      if (sim.handle (best, bts) == ST_PAUSE) break;
+      int status;
+      bool fired_flow = bslot >= st.NK;
+      if (!step_or_stop (st, sim, bslot, until_ns, 0, status)) break;
+      if (fired_flow) scan_flows (st, d, 0, 1, fts, fseq, fslot);
     }
-  if (!sc->pending && until_ns < stop && sc->now < until_ns) sc->now = until_ns;
+  if (!sc->pending && until_ns < stop && sc->now < until_ns && !sc->finished) sc->now = until_ns;
   sc->c.end_ns = sc->now;
 }
 

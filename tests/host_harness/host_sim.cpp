@@ -105,8 +105,7 @@ hs_run_nolog (hs_sim *s, int64_t until_ns)
 void
 hs_counters (hs_sim *s, prb_counters *out)
 {
-  *out = s->d.sc->c;
-  finalize_counters (*out);
+  finalize_counters (s->hm.st, s->d, *out);
 }
 
 int64_t hs_num_events (hs_sim *s) { return s->d.sc->ev_n; }

@@ -163,3 +163,22 @@ def test_core_record_free_fast_path_equals_logged_run():
         b.run_nolog()
         assert a.counters() == b.counters()
         assert np.array_equal(a.queue_bytes(), b.queue_bytes())
+
+
+def test_core_sparse_timers_beyond_key_range():
+    """Scan keys are 32-bit offsets from an epoch (4.29 s range).  With a 7 s ping interval and a trickle of
+    traffic every armed timer is regularly farther away than that: the exact 64-bit fallback must agree
+    with the restatement event by event."""
+    cfg = common.env_config("overlay_full_mesh_3n_abilene", simTime=60, load_factor=0.004, pingAsObs=1,
+                            activateUnderlayTraffic=1, pingPacketIntervalTime=7.0)
+    arrays = cfg.load()
+    table = common.sp_table(arrays)
+    osim = common.oracle_run(cfg, arrays, oracle, policy="table", table=table, env_id=2)
+    hs = host_sim.HostSim(cfg.abi_params(arrays), env_index=2)
+    hs.set_policy("table", table)
+    hs.run()
+    oe = osim.events()
+    assert 50 < len(oe) < 3000
+    assert common.first_event_mismatch(oe, hs.events()) is None
+    common.assert_steps_equal(osim.decisions(), hs.steps())
+    common.assert_counters_equal(osim.counters(), hs.counters())

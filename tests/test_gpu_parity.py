@@ -224,6 +224,26 @@ def test_drop_heavy_small_buffers():
     env.close()
 
 
+def test_sparse_timers_beyond_key_range():
+    """32-bit scan keys saturate when every timer is > 4.29 s away: exact fallback on the device."""
+    cfg = common.env_config("overlay_full_mesh_3n_abilene", num_envs=33, simTime=60, load_factor=0.004, pingAsObs=1,
+                            activateUnderlayTraffic=1, pingPacketIntervalTime=7.0)
+    arrays = cfg.load()
+    table = common.sp_table(arrays)
+    env = make_env(cfg, arrays=arrays)
+    env.enable_log(5000, 2000)
+    env.reset()
+    env.set_policy("table", table)
+    env.run()
+    cs = env.counters()
+    for e in (0, 32):
+        osim = common.oracle_run(cfg, arrays, oracle, policy="table", table=table, env_id=e)
+        assert common.first_event_mismatch(osim.events(), env.events(e)) is None
+        common.assert_steps_equal(osim.decisions(), env.steps(e))
+        common.assert_counters_equal(osim.counters(), cs[e])
+    env.close()
+
+
 def test_compat_per_node_view():
     """Ns3EnvCompat: the reference's per-node reset/step surface over env 0, driven the way
     prisma/main.py:117-127 does — one thread per overlay node running a Forwarder-style loop."""
