@@ -10,7 +10,7 @@ import os
 import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libprisma_b200.so")
+LIB_PATH = os.environ.get("PRB_LIB") or os.path.join(HERE, "libprisma_b200.so")   # PRB_LIB: kernel experiments
 
 PRB_MAX_K = 16
 PRB_MAX_LOST = 8
