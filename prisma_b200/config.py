@@ -142,6 +142,24 @@ class EnvConfig:
     num_envs: int = 1
     device: int = 0
 
+    @classmethod
+    def from_params(cls, params: dict, **over) -> "EnvConfig":
+        """Builds the configuration from the reference's `params` dict (the output of
+        prisma/source/argument_parser.py:11-164): same keys, unknown keys ignored."""
+        names = {f.name for f in dataclasses.fields(cls)}
+        kw = {k: v for k, v in params.items() if k in names and v is not None}
+        kw.update(over)
+        return cls(**kw)
+
+    def shard(self, rank: int, world: int) -> "tuple[int, int]":
+        """(first env id, env count) of rank `rank` when `num_envs` environments are sharded over `world`
+        ranks: contiguous ranges, remainder to the low ranks.  Environments are independent, so this is the
+        whole multi-GPU story of the step loop (no collective)."""
+        base, rem = divmod(int(self.num_envs), int(world))
+        n = base + (1 if rank < rem else 0)
+        first = rank * base + min(rank, rem)
+        return first, n
+
     # ---- derived ----
     def load(self) -> "EnvArrays":
         adj = self.physical_adjacency_matrix
