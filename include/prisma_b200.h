@@ -48,10 +48,12 @@ enum { PRB_DATA = 0, PRB_BIG_SIGN = 1, PRB_SMALL_SIGN = 2, PRB_PING_FWD = 3, PRB
 /* event-log record kinds */
 enum { PRB_EV_INJ = 0, PRB_EV_ARR = 1, PRB_EV_ENQ = 2, PRB_EV_DRP = 3, PRB_EV_TXB = 4, PRB_EV_RCV = 5 };
 /* agent hooks evaluated on the device (prb_run) */
-enum { PRB_POLICY_ZERO = 0, PRB_POLICY_TABLE = 1, PRB_POLICY_TRACE = 2, PRB_POLICY_RANDOM = 3 };
+enum { PRB_POLICY_ZERO = 0, PRB_POLICY_TABLE = 1, PRB_POLICY_TRACE = 2, PRB_POLICY_RANDOM = 3, PRB_POLICY_NODE_TRACE = 4 };
+/* which engine advances the environments in prb_run (prb_set_engine) */
+enum { PRB_ENGINE_AUTO = 0, PRB_ENGINE_SERIAL = 1, PRB_ENGINE_PARALLEL = 2 };
 enum { PRB_INJECT_TRACE = 0, PRB_INJECT_PHILOX = 1 };
 /* env error bits (prb_errors) */
-enum { PRB_ERR_POOL = 1, PRB_ERR_LOG = 2, PRB_ERR_PING_WINDOW = 4, PRB_ERR_TRACE = 8, PRB_ERR_SEQ = 16 };
+enum { PRB_ERR_POOL = 1, PRB_ERR_LOG = 2, PRB_ERR_PING_WINDOW = 4, PRB_ERR_TRACE = 8, PRB_ERR_SEQ = 16, PRB_ERR_TIE = 32 };
 
 typedef struct prb_config
 {

@@ -18,7 +18,8 @@ PRB_LASTHOP_NONE = 1000
 
 PRB_DATA, PRB_BIG_SIGN, PRB_SMALL_SIGN, PRB_PING_FWD, PRB_PING_BACK = range(5)
 EV_KINDS = ["INJ", "ARR", "ENQ", "DRP", "TXB", "RCV"]
-POLICY = {"zero": 0, "table": 1, "trace": 2, "random": 3}
+POLICY = {"zero": 0, "table": 1, "trace": 2, "random": 3, "node_trace": 4}
+ENGINE = {"auto": 0, "serial": 1, "parallel": 2}
 SIGNALING = {"ideal": 0, "NN": 1, "target": 2, "digital_twin": 3}
 ERR_BITS = {1: "packet pool exhausted", 2: "log capacity exceeded", 4: "ping window too short",
             8: "action trace exhausted", 16: "scheduler uid overflow"}

@@ -11,6 +11,7 @@
 #include <vector>
 
 #include "sim_core.cuh"
+#include "par_core.cuh"
 
 namespace prb {
 
@@ -389,7 +390,7 @@ struct HostTrace
   std::vector<int64_t> t;
   std::vector<uint32_t> uid;
   std::vector<uint8_t> flags;
-  std::vector<int32_t> next;
+  std::vector<int32_t> next, prev;
 };
 
 inline bool
@@ -398,7 +399,7 @@ build_trace (HostModel &hm, int64_t n, const int64_t *t_ns, const int32_t *src, 
 {
   const int N = hm.st.N;
   tr.t.assign (t_ns, t_ns + n);
-  tr.uid.resize (n); tr.flags.resize (n); tr.next.assign (n, -1);
+  tr.uid.resize (n); tr.flags.resize (n); tr.next.assign (n, -1); tr.prev.assign (n, -1);
   std::fill (hm.flow_first.begin (), hm.flow_first.end (), -1);
   std::vector<int32_t> last (hm.flow_src.size (), -1);
   for (int64_t i = 0; i < n; i++)
@@ -409,8 +410,174 @@ build_trace (HostModel &hm, int64_t n, const int64_t *t_ns, const int32_t *src, 
       tr.uid[i] = (uint32_t) uid[i];
       tr.flags[i] = (uint8_t) ((valable[i] ? 1 : 0) | (rejected && rejected[i] ? 2 : 0));
       if (last[f] >= 0) tr.next[last[f]] = (int32_t) i; else hm.flow_first[f] = (int32_t) i;
+      tr.prev[i] = last[f];
       last[f] = (int32_t) i;
     }
+  return true;
+}
+
+/* ---- node-parallel engine (par_core.cuh): tables, ring sizes, state layout ------------------------------ */
+
+struct PModel
+{
+  PStatic ps;                      /* table pointers are HOST pointers into the vectors below */
+  std::vector<int16_t> in_links, out_links;
+  std::vector<int32_t> ring_off, flow_begin, pol_off;
+  std::vector<uint16_t> ring_mask, dcode_rcv, dcode_txc;
+  std::vector<char> pblob0;
+  bool supported = false;
+  std::string why;                 /* why the configuration has to run on the serial engine */
+};
+
+inline int32_t
+pow2_ceil (int64_t v)
+{
+  int32_t p = 1;
+  while (p < v) p <<= 1;
+  return p;
+}
+
+inline bool
+build_pmodel (const prb_config &c, const HostModel &hm, PModel &pm)
+{
+  const Static &st = hm.st;
+  PStatic &ps = pm.ps;
+  memset (&ps, 0, sizeof (ps));
+  const int N = st.N, M = st.M, L = st.L, LA = st.LA, F = st.F;
+  pm.supported = false;
+  /* lookahead: the smallest packet that can be put on a switch link */
+  int64_t tx_min = INT64_MAX;
+  for (int k = 0; k < st.n_szc; k++) tx_min = std::min (tx_min, hm.tx_ns[k]);
+  if (tx_min <= 0 || st.link_delay_ns < 0)
+    {
+      pm.why = "zero transmission time";
+      return false;
+    }
+  ps.la_ns = st.link_delay_ns + tx_min;
+  /* packets between TransmitStart and the peer's Receive, as seen by a sender that runs up to one lookahead
+   * ahead of the receiver: 3 + 2*delay/tx_min */
+  int64_t w = 3 + (2 * st.link_delay_ns + tx_min - 1) / tx_min;
+  ps.W = pow2_ceil (w);
+  if (ps.W > 16)
+    {
+      pm.why = "link_delay is many minimum transmission times: the wire rings would not fit";
+      return false;
+    }
+  if (N > 4096)
+    {
+      pm.why = "too many nodes";
+      return false;
+    }
+  int deg = 1;
+  std::vector<std::vector<int>> in (N), out (N);
+  for (int l = 0; l < L; l++)
+    {
+      out[hm.link_from[l]].push_back (l);
+      in[hm.link_to[l]].push_back (l);
+    }
+  for (int x = 0; x < N; x++) deg = std::max<int> (deg, (int) std::max (in[x].size (), out[x].size ()));
+  ps.DEG = deg;
+  pm.in_links.assign ((size_t) N * deg, -1);
+  pm.out_links.assign ((size_t) N * deg, -1);
+  for (int x = 0; x < N; x++)
+    {
+      for (size_t j = 0; j < in[x].size (); j++) pm.in_links[(size_t) x * deg + j] = (int16_t) in[x][j];
+      for (size_t j = 0; j < out[x].size (); j++) pm.out_links[(size_t) x * deg + j] = (int16_t) out[x][j];
+    }
+  /* rings: what the byte-limited queue holds as data packets, the wire, and slack for small packets */
+  int64_t per = c.max_out_buffer_size / std::max<int> (hm.szc_bytes[SZC_DATA_FWD], 38) + 2 + ps.W;
+  if (c.train) per *= 2;
+  int32_t rc = std::min (std::max (pow2_ceil (per), 8), 4096);
+  pm.ring_off.assign (LA, 0);
+  pm.ring_mask.assign (LA, 0);
+  int32_t off = 0;
+  for (int l = 0; l < LA; l++)
+    {
+      int32_t cap = l < L ? rc : 8;
+      pm.ring_off[l] = off;
+      pm.ring_mask[l] = (uint16_t) (cap - 1);
+      off += cap;
+    }
+  ps.ring_records = off;
+  pm.flow_begin.assign (N + 1, 0);
+  for (int f = 0; f < F; f++) pm.flow_begin[hm.flow_src[f] + 1]++;
+  for (int x = 0; x < N; x++) pm.flow_begin[x + 1] += pm.flow_begin[x];
+  for (int f = 1; f < F; f++)
+    if (hm.flow_src[f] < hm.flow_src[f - 1])
+      {
+        pm.why = "flows are not grouped by source";
+        return false;
+      }
+  pm.pol_off.assign (M + 1, 0);
+  /* distance codes: every value ts(event) - ts(parent) that a Receive, a TransmitComplete or a ping timer
+   * can have, ranked largest first (par_core.cuh, POrd) */
+  {
+    std::vector<int64_t> dist;
+    const int nrc = st.n_rc;
+    for (int r = 0; r < nrc; r++)
+      for (int k = 0; k < st.n_szc; k++)
+        {
+          dist.push_back (hm.tx_ns[(size_t) r * MAX_SZC + k]);
+          dist.push_back (hm.tx_ns[(size_t) r * MAX_SZC + k] + (r == 0 ? st.link_delay_ns : 0));
+        }
+    dist.push_back (st.ping_interval_ns);
+    std::sort (dist.begin (), dist.end (), [] (int64_t a, int64_t b) { return a > b; });
+    dist.erase (std::unique (dist.begin (), dist.end ()), dist.end ());
+    if (dist.size () >= P_CODE_FLOW)
+      {
+        pm.why = "too many distinct transmission times";
+        return false;
+      }
+    auto code = [&] (int64_t v) { return (uint16_t) (std::find (dist.begin (), dist.end (), v) - dist.begin ()); };
+    pm.dcode_rcv.assign ((size_t) nrc * MAX_SZC, 0);
+    pm.dcode_txc.assign ((size_t) nrc * MAX_SZC, 0);
+    for (int r = 0; r < nrc; r++)
+      for (int k = 0; k < st.n_szc; k++)
+        {
+          pm.dcode_txc[(size_t) r * MAX_SZC + k] = code (hm.tx_ns[(size_t) r * MAX_SZC + k]);
+          pm.dcode_rcv[(size_t) r * MAX_SZC + k] = code (hm.tx_ns[(size_t) r * MAX_SZC + k] + (r == 0 ? st.link_delay_ns : 0));
+        }
+    ps.dcode_ping = code (st.ping_interval_ns);
+  }
+  /* state layout */
+  int32_t o = 0;
+  ps.off_scal = o; o += align_up ((int32_t) sizeof (PScal), 8);
+  ps.off_t_next = o; o += 8 * N;
+  ps.off_t_ping = o; o += 8 * M;
+  ps.off_fmin_ts = o; o += 8 * N;
+  ps.off_f_ts = o; o += 8 * std::max (F, 1);
+  ps.off_busy = o; o += 8 * LA;
+  ps.off_w_ts = o; o += 8 * LA * ps.W;
+  ps.off_sring = o; o += (int32_t) sizeof (PStat) * N * P_SR;
+  ps.off_fly_ord = o; o += (int32_t) sizeof (POrd) * LA;
+  ps.off_q_bytes = o; o += 4 * LA;
+  ps.off_f_pos = o; o += 4 * std::max (F, 1);
+  ps.off_ping_index = o; o += 4 * M;
+  ps.off_pol_pos = o; o += 4 * M;
+  ps.off_fmin_f = o; o += 4 * N;
+  ps.off_head = o; o += 2 * LA;
+  ps.off_mid = o; o += 2 * LA;
+  ps.off_tail = o; o += 2 * LA;
+  ps.off_s_head = o; o += N;
+  ps.off_s_tail = o; o += N;
+  ps.off_fly_szc = o; o += LA;
+  ps.pblob_bytes = align_up (o, 16);
+  pm.pblob0.assign (ps.pblob_bytes, 0);
+  PDyn d;
+  p_bind_state (ps, pm.pblob0.data (), d);
+  for (int x = 0; x < N; x++)
+    {
+      d.t_next[x] = P_FAR;
+      d.fmin_ts[x] = P_FAR;
+      d.fmin_f[x] = -1;
+    }
+  for (int m = 0; m < M; m++) d.t_ping[m] = P_FAR;
+  for (int f = 0; f < std::max (F, 1); f++) d.f_ts[f] = P_FAR;
+  ps.in_links = pm.in_links.data (); ps.out_links = pm.out_links.data ();
+  ps.ring_off = pm.ring_off.data (); ps.ring_mask = pm.ring_mask.data ();
+  ps.flow_begin = pm.flow_begin.data (); ps.tr_prev = nullptr; ps.pol_off = pm.pol_off.data ();
+  ps.dcode_rcv = pm.dcode_rcv.data (); ps.dcode_txc = pm.dcode_txc.data ();
+  pm.supported = true;
   return true;
 }
 

@@ -1,0 +1,1028 @@
+/* prisma_b200 — node-parallel engine: one lane per network node, conservative lookahead inside an env.
+ *
+ * The serial engine (sim_core.cuh) executes one event of an environment at a time in ns-3's global
+ * (timestamp, scheduler uid) order.  This engine advances the NODES of one environment concurrently
+ * (a team of T lanes, lane x owns node x, its traffic node N+x, every device of both and the flows that
+ * start at x) and is used by prb_run for the agents that are a function of the packet alone (next-hop
+ * table).  Same physics, same reference citations as sim_core.cuh; what changes is the order in which
+ * independent events are executed.
+ *
+ * Why that is allowed.  A node is only ever influenced from outside through packets that arrive on its
+ * in-links, and a packet whose transmission starts at time s on link y->x arrives at s + tx + delay >=
+ * s + LA, LA = link_delay + tx(smallest packet) (point-to-point-net-device.cc:272-302,
+ * point-to-point-channel.cc:86-107).  With t_next[y] the timestamp of the earliest pending event of node
+ * y and gmin their minimum, node x may execute its earliest event e iff
+ *     ts(e) <  max(busy_until[y->x], t_next[y]) + LA   for every in-link, and   ts(e) < gmin + 2 LA
+ * (strictly: an arrival with the same timestamp could still be ordered before e).  The node that holds
+ * gmin always qualifies, so every round makes progress.
+ *
+ * Order of simultaneous events of ONE node.  ns-3 orders equal timestamps by scheduler uid, i.e. by the
+ * order in which they were scheduled (scheduler.h:153-169).  That order is reproduced from local
+ * information: first the time at which each event was scheduled (the transmission start of an arrival or
+ * of a TransmitComplete, the previous injection of a flow, the previous ping round); when those agree too,
+ * by the rules that cover the systematic cases (ping rounds: every ping timer fires at the same instant,
+ * in overlay-index order, and sends tunnel by tunnel, data-packet-manager.cc:349-357; TransmitComplete is
+ * scheduled before the peer's Receive, point-to-point-net-device.cc:295-296).  A tie that none of these
+ * decides sets PRB_ERR_TIE: the run is then not claimed to be in ns-3's order (it never happened in the
+ * test-suite; two unrelated events would have to coincide to the nanosecond twice in a row).
+ *
+ * float32 statistics.  The reference re-sums float vectors front to back (compute-stats-v2.cc:87-97), so
+ * the sums depend on the global order of deliveries and drops.  Nodes append (ts, value) records to a small
+ * ring; every round the records older than gmin are folded into the sums in timestamp order by one lane
+ * at a time.  Deliveries at DIFFERENT nodes in the same nanosecond are folded in node order.
+ *
+ * Like sim_core.cuh this header also compiles with g++ for tests/host_harness, where the lanes of a team
+ * are emulated one after the other (in a shuffled order, to show that a round does not depend on it).
+ */
+#pragma once
+
+#include "sim_core.cuh"
+
+#ifndef PRB_UNLIKELY
+#define PRB_UNLIKELY(x) __builtin_expect (!!(x), 0)
+#endif
+
+namespace prb {
+
+constexpr int P_SR = 8;                  /* statistics-ring records per node */
+constexpr int64_t P_FAR = INT64_MAX;
+constexpr uint32_t P_NONE16 = 0xFFFFu;
+constexpr uint32_t P_CODE_FLOW = 510;      /* scheduled by a source: the distance to its parent is arbitrary */
+
+/* Scheduling history of an event, for the order of simultaneous events (tie_before).
+ * An event's scheduler uid is the order of its Schedule call, i.e. (timestamp of the parent event, uid of
+ * the parent, position inside the parent's handler), recursively.  The distance ts(e) - ts(parent(e)) of
+ * almost every event is one of a few values (a transmission time, plus the link delay for a Receive, or
+ * the ping interval); the host ranks those values (largest first) and an event carries the ranks of its
+ * ancestors, most recent first, run-length coded: six 16-bit entries (code << 7 | run), then the creation
+ * rank of the setup event the chain started from (0xFFFF once history has been shed) and the position of the
+ * chain among the transmissions of one ping round.  Comparing two histories entry by entry is comparing
+ * the ancestors' timestamps generation by generation, which is how ns-3's uids compare. */
+struct POrd
+{
+  uint64_t a;        /* e0 (bits 48..63) e1 e2 e3 */
+  uint64_t b;        /* e4 e5 root branch */
+};
+
+enum { PK_NONE = 0, PK_RCV = 1, PK_TXC = 2, PK_FLOW = 3, PK_PING = 4 };
+enum { PS_OVERLAY_ARRIVED = 0, PS_UNDERLAY_ARRIVED = 1, PS_OVERLAY_DROP = 2, PS_UNDERLAY_DROP = 3 };
+
+/* packet record inside a link ring — 32 bytes */
+struct PRec
+{
+  uint64_t w0;       /* same packing as Pkt::w0 */
+  int64_t prev_t;
+  uint32_t uid;
+  uint32_t aux;
+  POrd ord;          /* history of the transmission that carries the packet (tie_before) */
+  uint64_t pad;
+};
+
+struct PStat
+{
+  int64_t ts;
+  uint32_t code;
+  float v;
+};
+
+struct PStatic
+{
+  int32_t W;                 /* wire-ring slots per link (power of two) */
+  int32_t DEG;               /* row length of in_links / out_links */
+  int32_t ring_records;      /* PRec per environment */
+  int32_t pad0;
+  int64_t la_ns;             /* smallest (tx + delay) of a switch<->switch link */
+  const int16_t *in_links;   /* [N*DEG] switch links that end at x, -1 padded */
+  const int16_t *out_links;  /* [N*DEG] switch links that start at x, -1 padded */
+  const int32_t *ring_off;   /* [LA] first record of the ring of link l */
+  const uint16_t *ring_mask; /* [LA] ring capacity - 1 */
+  const int32_t *flow_begin; /* [N+1] flows with source x: [flow_begin[x], flow_begin[x+1]) */
+  const int32_t *tr_prev;    /* trace mode: previous injection of the same flow, -1 for the first */
+  const int32_t *pol_off;    /* per-node action trace: [M+1] offsets into pol_data */
+  const uint16_t *dcode_rcv; /* [n_rc*MAX_SZC] rank of tx + delay of a Receive on a link of that rate class */
+  const uint16_t *dcode_txc; /* [n_rc*MAX_SZC] rank of tx */
+  int32_t dcode_ping, pad1;
+  int32_t off_scal, off_t_next, off_t_ping, off_fmin_ts, off_f_ts, off_busy, off_w_ts, off_sring, off_q_bytes, off_f_pos,
+      off_ping_index, off_pol_pos, off_fmin_f, off_head, off_mid, off_tail, off_s_head, off_s_tail, off_fly_szc, off_fly_ord;
+  int32_t pblob_bytes;
+};
+
+struct PScal
+{
+  int64_t front_ts;          /* every event with ts < front_ts has executed */
+  int64_t ev_n;
+  int64_t tx_started;        /* TransmitStart calls so far (each schedules one TransmitComplete) */
+  int64_t ev_real;           /* Receive / injection / ping-timer events executed */
+  int32_t started, finished;
+  prb_counters c;
+};
+
+struct PDyn
+{
+  PScal *sc;
+  int64_t *t_next, *t_ping, *fmin_ts, *f_ts, *busy, *w_ts;
+  PStat *sring;
+  uint32_t *q_bytes, *f_pos, *ping_index, *pol_pos;
+  int32_t *fmin_f;
+  uint16_t *head, *mid, *tail;
+  POrd *fly_ord;
+  uint8_t *s_head, *s_tail, *fly_szc;
+  PRec *rings;
+  prb_event *ev_log;
+};
+
+PRB_HD void
+p_bind_state (const PStatic &ps, char *blob, PDyn &d)
+{
+  d.sc = (PScal *) (blob + ps.off_scal);
+  d.t_next = (int64_t *) (blob + ps.off_t_next);
+  d.t_ping = (int64_t *) (blob + ps.off_t_ping);
+  d.fmin_ts = (int64_t *) (blob + ps.off_fmin_ts);
+  d.f_ts = (int64_t *) (blob + ps.off_f_ts);
+  d.busy = (int64_t *) (blob + ps.off_busy);
+  d.w_ts = (int64_t *) (blob + ps.off_w_ts);
+  d.sring = (PStat *) (blob + ps.off_sring);
+  d.q_bytes = (uint32_t *) (blob + ps.off_q_bytes);
+  d.f_pos = (uint32_t *) (blob + ps.off_f_pos);
+  d.ping_index = (uint32_t *) (blob + ps.off_ping_index);
+  d.pol_pos = (uint32_t *) (blob + ps.off_pol_pos);
+  d.fmin_f = (int32_t *) (blob + ps.off_fmin_f);
+  d.head = (uint16_t *) (blob + ps.off_head);
+  d.mid = (uint16_t *) (blob + ps.off_mid);
+  d.tail = (uint16_t *) (blob + ps.off_tail);
+  d.s_head = (uint8_t *) (blob + ps.off_s_head);
+  d.s_tail = (uint8_t *) (blob + ps.off_s_tail);
+  d.fly_szc = (uint8_t *) (blob + ps.off_fly_szc);
+  d.fly_ord = (POrd *) (blob + ps.off_fly_ord);
+}
+
+/* per-lane counters of one launch (registers on the device) */
+struct PAcc
+{
+  uint32_t overlay_injected, overlay_arrived, overlay_lost, underlay_injected, underlay_arrived, underlay_lost;
+  uint32_t bytes_data, bytes_signaling, packet_hops, data_hops, env_steps, decisions, vanished, ev_real, tx_started;
+  uint32_t errors;
+};
+
+struct PCand
+{
+  int64_t ts;
+  int32_t kind;
+  int32_t idx;      /* link (RCV, TXC), flow, overlay index */
+};
+
+PRB_HD int64_t
+sat_add (int64_t a, int64_t b)
+{
+  return a > P_FAR - b ? P_FAR : a + b;
+}
+
+/* ---- scheduling histories ---- */
+PRB_HD POrd
+ord_empty (uint32_t root, uint32_t branch)
+{
+  POrd o;
+  o.a = 0;
+  o.b = ((uint64_t) (root & 0xFFFFu) << 16) | (uint64_t) (branch & 0xFFFFu);
+  return o;
+}
+
+/* history of a child of an event with history o whose own distance code is `code` */
+PRB_HD POrd
+ord_push (POrd o, uint32_t code)
+{
+  uint32_t e0 = (uint32_t) (o.a >> 48);
+  if ((e0 >> 7) == code && (e0 & 127u) != 0 && (e0 & 127u) < 127u)
+    {
+      o.a += 1ull << 48;
+      return o;
+    }
+  uint32_t e3 = (uint32_t) (o.a & 0xFFFFu), e4 = (uint32_t) (o.b >> 48), e5 = (uint32_t) ((o.b >> 32) & 0xFFFFu);
+  uint64_t tail = o.b & 0xFFFFFFFFull;
+  if (e5 & 127u) tail |= 0xFFFF0000ull;          /* an entry falls off the end: the root is no longer known */
+  o.b = ((uint64_t) e3 << 48) | ((uint64_t) e4 << 32) | tail;
+  o.a = (o.a >> 16) | ((uint64_t) ((code << 7) | 1u) << 48);
+  return o;
+}
+
+PRB_HD uint32_t
+ord_entry (const POrd &o, int i)
+{
+  return i < 4 ? (uint32_t) ((o.a >> (48 - 16 * i)) & 0xFFFFu) : (uint32_t) ((o.b >> (48 - 16 * (i - 4))) & 0xFFFFu);
+}
+
+/* -1: x was scheduled first, +1: y, 0: the histories do not tell */
+PRB_HDN inline int
+ord_compare (const POrd &x, const POrd &y)
+{
+  int ix = 0, iy = 0;
+  uint32_t ex = ord_entry (x, 0), ey = ord_entry (y, 0);
+  uint32_t rx = ex & 127u, ry = ey & 127u;
+  for (;;)
+    {
+      if (rx == 0 || ry == 0)
+        {
+          if (rx != 0 || ry != 0) return 0;
+          /* both histories end here: at setup, unless entries have been shed */
+          uint32_t rootx = (uint32_t) ((x.b >> 16) & 0xFFFFu), rooty = (uint32_t) ((y.b >> 16) & 0xFFFFu);
+          if (rootx == P_NONE16 || rooty == P_NONE16) return 0;
+          if (rootx != rooty) return rootx < rooty ? -1 : 1;
+          uint32_t bx = (uint32_t) (x.b & 0xFFFFu), by = (uint32_t) (y.b & 0xFFFFu);
+          if (bx != by) return bx < by ? -1 : 1;
+          return 0;
+        }
+      uint32_t cx = ex >> 7, cy = ey >> 7;
+      if (cx == P_CODE_FLOW || cy == P_CODE_FLOW) return 0;
+      if (cx != cy) return cx < cy ? -1 : 1;    /* the larger distance (smaller code) was scheduled earlier */
+      uint32_t m = rx < ry ? rx : ry;
+      rx -= m; ry -= m;
+      if (rx == 0)
+        {
+          if (++ix == 6) return 0;
+          ex = ord_entry (x, ix); rx = ex & 127u;
+        }
+      if (ry == 0)
+        {
+          if (++iy == 6) return 0;
+          ey = ord_entry (y, iy); ry = ey & 127u;
+        }
+    }
+}
+
+/* the running event as a parent: when it was scheduled, its history, and its own distance code */
+struct PCtx
+{
+  int64_t sched;
+  POrd ord;
+  uint32_t code;
+};
+
+template <bool LOG>
+struct PSim
+{
+  const Static &st;
+  const PStatic &ps;
+  PDyn &d;
+  PAcc &acc;
+  int env;
+
+  PRB_HD PSim (const Static &st_, const PStatic &ps_, PDyn &d_, PAcc &acc_, int env_) : st (st_), ps (ps_), d (d_), acc (acc_), env (env_) {}
+
+  PRB_HD static void
+  to_pkt (const PRec &r, Pkt &p)
+  {
+    p.w0 = r.w0; p.prev_t = r.prev_t; p.uid = r.uid; p.aux = r.aux; p.rcv_ts = 0; p.rcv_seq = 0; p.next = NIL; p.pad = 0;
+  }
+  PRB_HD static void
+  to_rec (const Pkt &p, PRec &r)
+  {
+    r.w0 = p.w0; r.prev_t = p.prev_t; r.uid = p.uid; r.aux = p.aux; r.ord.a = 0; r.ord.b = 0; r.pad = 0;
+  }
+
+  PRB_HD void
+  log_event (int64_t now, int kind, int node, int link, const Pkt &p, int qbytes)
+  {
+    if (!LOG) return;
+    int64_t i;
+#if defined(__CUDA_ARCH__)
+    i = (int64_t) atomicAdd ((unsigned long long *) &d.sc->ev_n, 1ull);
+#else
+    i = d.sc->ev_n++;
+#endif
+    if (i >= st.ev_cap)
+      {
+        if (st.ev_cap > 0) acc.errors |= PRB_ERR_LOG;
+        return;
+      }
+    prb_event *e = &d.ev_log[i];
+    int data = p_type (p) == PRB_DATA;
+    e->t_ns = now; e->kind = kind; e->node = node; e->link = link; e->pad_ = 0;
+    e->uid = data ? (int64_t) p.uid : -1;
+    e->size = st.szc_bytes[p_szc (p)]; e->type = p_type (p); e->src = p_src (p); e->dst = p_dst (p);
+    e->last_hop = p_last_hop (p) == NODE_NONE ? PRB_LASTHOP_NONE : p_last_hop (p);
+    e->next_hop = p_next_hop (p); e->valable = data ? p_valable (p) : -1;
+    e->qbytes = qbytes;
+  }
+
+  /* ---- float statistics: appended here, folded in timestamp order by the team ---- */
+  PRB_HD void
+  stat_push (int x, int64_t ts, uint32_t code, float v)
+  {
+    uint8_t t = d.s_tail[x];
+    PStat &s = d.sring[x * P_SR + (t & (P_SR - 1))];
+    s.ts = ts; s.code = code; s.v = v;
+    d.s_tail[x] = (uint8_t) (t + 1);
+  }
+  PRB_HD int
+  stat_room (int x) const
+  {
+    return P_SR - (int) (uint8_t) (d.s_tail[x] - d.s_head[x]);
+  }
+
+  PRB_HD void
+  count_drop (int x, int64_t now, bool overlay_side)
+  {
+    if (overlay_side)
+      {
+        acc.overlay_lost++;
+        stat_push (x, now, PS_OVERLAY_DROP, st.loss_penalty);
+      }
+    else
+      {
+        acc.underlay_lost++;
+        stat_push (x, now, PS_UNDERLAY_DROP, st.loss_penalty);
+      }
+  }
+
+  /* PointToPointNetDevice::TransmitStart + PointToPointChannel::TransmitStart: the record is already in the
+   * ring at position mid; o is the history shared by the TransmitComplete and the Receive it schedules */
+  PRB_HD void
+  transmit_start (int l, int64_t now, const Pkt &p, const POrd &o)
+  {
+    if (l < st.L) log_event (now, PRB_EV_TXB, st.link_from[l], l, p, (int) d.q_bytes[l]);
+    int szc = p_szc (p);
+    int64_t tx = st.tx_ns[st.link_rc[l] * MAX_SZC + szc];
+    int64_t delay = l < st.L ? st.link_delay_ns : 0;
+    d.busy[l] = now + tx;
+    d.fly_szc[l] = (uint8_t) szc;
+    d.fly_ord[l] = o;
+    uint16_t m = d.mid[l];
+    if ((uint16_t) (m - d.head[l]) >= (uint16_t) ps.W) acc.errors |= PRB_ERR_POOL;
+    d.w_ts[l * ps.W + (m & (ps.W - 1))] = now + tx + delay;
+    d.mid[l] = (uint16_t) (m + 1);
+    acc.tx_started++;
+  }
+
+  PRB_HD PCtx
+  txc_ctx (int l, int64_t ts) const
+  {
+    PCtx c;
+    int k = st.link_rc[l] * MAX_SZC + d.fly_szc[l];
+    c.sched = ts - st.tx_ns[k];
+    c.ord = d.fly_ord[l];
+    c.code = ps.dcode_txc[k];
+    return c;
+  }
+
+  /* PointToPointNetDevice::Send + Queue::DoEnqueue, executed by the lane that owns the sending node.
+   * cur: the running event; branch: position among the transmissions of a ping round (or 0xFFFF: inherit) */
+  PRB_HD void
+  dev_send (int x, int l, int64_t now, const Pkt &p, const PCtx &cur, uint32_t branch)
+  {
+    int node = st.link_from[l];
+    int data = p_type (p) == PRB_DATA;
+    if (PRB_UNLIKELY (data && p_rejected (p) && node < 23))
+      {
+        count_drop (x, now, p_valable (p));
+        return;
+      }
+    if (l >= st.L) log_event (now, PRB_EV_INJ, node, l, p, -1);
+    uint32_t size = st.szc_bytes[p_szc (p)];
+    uint32_t qb = d.q_bytes[l];
+    uint16_t h = d.head[l], m = d.mid[l], t = d.tail[l];
+    bool fits = l < st.L ? (qb + size <= st.max_out_buffer) : ((uint32_t) (uint16_t) (t - m) + 1 <= 1000u);
+    if (PRB_UNLIKELY (!fits))
+      {
+        if (l < st.L) log_event (now, PRB_EV_DRP, node, l, p, (int) qb);
+        if (data) count_drop (x, now, p_valable (p) && p_dst (p) != node);
+        return;
+      }
+    if (l < st.L) log_event (now, PRB_EV_ENQ, node, l, p, (int) (qb + size));
+    uint16_t mask = ps.ring_mask[l];
+    if (PRB_UNLIKELY ((uint16_t) (t - h) > mask))
+      {
+        acc.errors |= PRB_ERR_POOL;
+        return;
+      }
+    /* a TransmitComplete with nothing waiting only marks the device idle: it is not an event here, the
+     * device is READY as soon as the clock reaches busy_until */
+    bool busy = m != t || d.busy[l] > now;
+    if (PRB_UNLIKELY (!busy && d.busy[l] == now && now != 0))
+      {
+        /* the device completes in this very nanosecond.  If that TransmitComplete comes after the running
+         * event in scheduler order the device is still BUSY: the packet is queued and the completion, now a
+         * real event of this node at the same timestamp, starts it */
+        PCtx tc = txc_ctx (l, now);
+        int r = tc.sched != cur.sched ? (tc.sched < cur.sched ? -1 : 1) : ord_compare (tc.ord, cur.ord);
+        if (r == 0) acc.errors |= PRB_ERR_TIE;
+        if (r >= 0) busy = true;
+      }
+    PRec r;
+    to_rec (p, r);
+    POrd o;
+    o.a = 0; o.b = 0;
+    if (!busy)
+      {
+        o = ord_push (cur.ord, cur.code);
+        if (branch != P_NONE16) o.b = (o.b & ~0xFFFFull) | branch;
+        r.ord = o;
+      }
+    d.rings[ps.ring_off[l] + (t & mask)] = r;
+    d.tail[l] = (uint16_t) (t + 1);
+    if (!busy)
+      transmit_start (l, now, p, o);
+    else
+      d.q_bytes[l] = qb + size;
+  }
+
+  /* PointToPointNetDevice::TransmitComplete with a packet waiting */
+  PRB_HD void
+  transmit_complete (int l, int64_t now)
+  {
+    PCtx cur = txc_ctx (l, now);
+    uint16_t m = d.mid[l];
+    PRec *rp = &d.rings[ps.ring_off[l] + (m & ps.ring_mask[l])];
+    PRec r = *rp;
+    Pkt p;
+    to_pkt (r, p);
+    POrd o = ord_push (cur.ord, cur.code);
+    rp->ord = o;
+    d.q_bytes[l] -= st.szc_bytes[p_szc (p)];
+    transmit_start (l, now, p, o);
+  }
+
+  PRB_HD int32_t
+  policy_action (int m, const Pkt &p)
+  {
+    if (st.policy == PRB_POLICY_TABLE) return st.pol_data[m * st.M + st.map_overlay[p_dst (p)]];
+    if (st.policy == PRB_POLICY_NODE_TRACE)
+      {
+        uint32_t i = d.pol_pos[m];
+        if ((int64_t) ps.pol_off[m] + i >= (int64_t) ps.pol_off[m + 1])
+          {
+            acc.errors |= PRB_ERR_TRACE;
+            return 0;
+          }
+        d.pol_pos[m] = i + 1;
+        return st.pol_data[ps.pol_off[m] + i];
+      }
+    return 0;
+  }
+
+  PRB_HD static void
+  blank (Pkt &q)
+  {
+    q.w0 = 0; q.prev_t = 0; q.rcv_ts = 0; q.rcv_seq = 0; q.pad = 0; q.next = NIL; q.uid = 0; q.aux = 0;
+  }
+
+  PRB_HD PCtx
+  rcv_ctx (int l, int64_t ts, const PRec &r) const
+  {
+    PCtx c;
+    int k = st.link_rc[l] * MAX_SZC + (int) ((r.w0 >> 7) & 15);
+    c.sched = ts - st.tx_ns[k] - (l < st.L ? st.link_delay_ns : 0);
+    c.ord = r.ord;
+    c.code = ps.dcode_rcv[k];
+    return c;
+  }
+
+  /* PointToPointNetDevice::Receive (+ agent hook, ExecuteActions, IP forward, statistics) */
+  PRB_HD void
+  receive (int x, int l, int64_t now)
+  {
+    uint16_t h = d.head[l];
+    PRec r = d.rings[ps.ring_off[l] + (h & ps.ring_mask[l])];
+    d.head[l] = (uint16_t) (h + 1);
+    Pkt p;
+    to_pkt (r, p);
+    const PCtx cur = rcv_ctx (l, now, r);
+    bool access = l >= st.L;
+    int type = p_type (p);
+    acc.ev_real++;
+    if (PRB_UNLIKELY (type == PRB_DATA && p_rejected (p) && x < 23)) return;
+    log_event (now, access ? PRB_EV_ARR : PRB_EV_RCV, x, l, p, -1);
+    if (!access)
+      {
+        acc.packet_hops++;
+        if (type == PRB_DATA) acc.data_hops++;
+      }
+    int m = st.map_overlay[x];
+    bool notify = false;
+    if (m >= 0)
+      {
+        switch (type)
+          {
+          case PRB_DATA:
+            notify = p_next_hop (p) == x && p_valable (p);
+            break;
+          case PRB_BIG_SIGN:
+            notify = p_src (p) != x && p_dst (p) == x && p_next_hop (p) == x;
+            break;
+          case PRB_SMALL_SIGN:
+            notify = p_dst (p) == x && p_next_hop (p) == x;
+            break;
+          case PRB_PING_FWD:
+            {
+              /* PingForwardPacketManager::sendPingBackPacket */
+              float delay = d2f_ (dsub_ (ns_to_seconds_ (now), dmul_ ((double) p.aux, 0.001)));
+              Pkt q;
+              blank (q);
+              set_p_type (q, PRB_PING_BACK);
+              int lh = p_last_hop (p);
+              set_p_dst (q, lh); set_p_next_hop (q, lh); set_p_last_hop (q, x); set_p_src (q, x); set_p_ipdst (q, lh);
+              set_p_prev_node (q, NODE_NONE);
+              set_p_szc (q, SZC_PING);
+              set_p_tunnel (q, p_tunnel (p));
+              q.uid = p.uid;
+#if defined(__CUDA_ARCH__)
+              q.aux = __float_as_uint (delay);
+#else
+              memcpy (&q.aux, &delay, 4);
+#endif
+              dev_send (x, l ^ 1, now, q, cur, P_NONE16);
+            }
+            break;
+          default:
+            break;   /* PING_BACK: the delay windows only feed observations, which this engine does not build */
+          }
+      }
+    if (notify)
+      {
+        acc.env_steps++;
+        int data = type == PRB_DATA;
+        if (data)
+          {
+            int done = p_dst (p) == x;
+            if (!done) acc.decisions++;
+            if (st.train && p_src (p) != x)
+              {
+                /* DataPacketManager::sendSmallSignalingPacket */
+                Pkt q;
+                blank (q);
+                set_p_type (q, PRB_SMALL_SIGN);
+                int lh = p_last_hop (p);
+                set_p_dst (q, lh); set_p_next_hop (q, lh); set_p_last_hop (q, x); set_p_src (q, x); set_p_ipdst (q, lh);
+                set_p_prev_node (q, NODE_NONE);
+                set_p_szc (q, st.agent_sign_szc[m]);
+                q.uid = p.uid;
+                dev_send (x, l ^ 1, now, q, cur, P_NONE16);
+              }
+            if (!done)
+              {
+                int32_t action = policy_action (m, p);
+                int k = st.agent_k[m];
+                if (action >= 0 && action < k)
+                  {
+                    Pkt q = p;
+                    int nb = st.agent_nbr[m * st.K + action];
+                    set_p_last_hop (q, x); set_p_next_hop (q, nb); set_p_ipdst (q, nb);
+                    set_p_first_hop (q, 0);
+                    set_p_szc (q, SZC_DATA_FWD);
+                    set_p_tracked (q, 1); set_p_prev_node (q, x);
+                    q.prev_t = now;
+                    dev_send (x, st.route[x * st.N + nb], now, q, cur, P_NONE16);
+                  }
+                else
+                  acc.vanished++;
+              }
+          }
+      }
+    /* the IP forward inside m_rxCallback and the statistics after it (point-to-point-net-device.cc:432-463) */
+    int data = type == PRB_DATA;
+    if (p_first_hop (p))
+      {
+      }
+    else if (p_ipdst (p) == x)
+      {
+        if (data && p_last_hop (p) == NODE_NONE && !p_valable (p) && !(p_rejected (p) && st.N + x < 23))
+          acc.underlay_injected++;
+      }
+    else
+      dev_send (x, st.route[x * st.N + p_ipdst (p)], now, p, cur, P_NONE16);
+    if (data && p_dst (p) == x)
+      {
+        float dly = d2f_ (dsub_ (ns_to_seconds_ (now), (double) p.aux));
+        if (p_valable (p))
+          {
+            if (p_next_hop (p) == p_dst (p))
+              {
+                acc.overlay_arrived++;
+                stat_push (x, now, PS_OVERLAY_ARRIVED, dly);
+              }
+          }
+        else
+          {
+            acc.underlay_arrived++;
+            stat_push (x, now, PS_UNDERLAY_ARRIVED, dly);
+          }
+      }
+    if (type > 0 && p_dst (p) == x) acc.bytes_signaling += st.szc_bytes[p_szc (p)] - 2;
+    if (data && p_last_hop (p) == NODE_NONE)
+      {
+        if (p_valable (p))
+          {
+            acc.overlay_injected++;
+            acc.bytes_data += st.szc_bytes[p_szc (p)] - 2;
+          }
+        else
+          acc.underlay_injected++;
+      }
+  }
+
+  /* history of the pending firing of ping timer m: idx earlier firings, one ping interval apart */
+  PRB_HD PCtx
+  ping_ctx (int m, int64_t ts) const
+  {
+    PCtx c;
+    uint32_t n = d.ping_index[m];
+    c.sched = n == 0 ? -1 : ts - st.ping_interval_ns;
+    c.code = (uint32_t) ps.dcode_ping;
+    uint32_t e[6] = { 0, 0, 0, 0, 0, 0 };
+    uint32_t left = n;
+    for (int i = 0; i < 6 && left > 0; i++)
+      {
+        uint32_t r = left < 127u ? left : 127u;
+        e[i] = (c.code << 7) | r;
+        left -= r;
+      }
+    POrd o;
+    o.a = ((uint64_t) e[0] << 48) | ((uint64_t) e[1] << 32) | ((uint64_t) e[2] << 16) | (uint64_t) e[3];
+    o.b = ((uint64_t) e[4] << 48) | ((uint64_t) e[5] << 32) | ((uint64_t) (left > 0 ? P_NONE16 : (uint32_t) m) << 16) | P_NONE16;
+    c.ord = o;
+    return c;
+  }
+
+  /* DataPacketManager::sendPingPackets */
+  PRB_HD void
+  ping_timer (int x, int m, int64_t now)
+  {
+    acc.ev_real++;
+    const PCtx cur = ping_ctx (m, now);
+    int k = st.agent_k[m];
+    uint32_t idx = d.ping_index[m];
+    uint32_t ms = (uint32_t) (now / 1000000);
+    d.ping_index[m] = idx + 1;
+    for (int t = 0; t < k; t++)
+      {
+        int nb = st.agent_nbr[m * st.K + t];
+        Pkt q;
+        blank (q);
+        set_p_type (q, PRB_PING_FWD);
+        set_p_dst (q, nb); set_p_next_hop (q, nb); set_p_last_hop (q, x); set_p_src (q, x); set_p_ipdst (q, nb);
+        set_p_prev_node (q, NODE_NONE);
+        set_p_szc (q, SZC_PING);
+        set_p_tunnel (q, t);
+        q.uid = idx; q.aux = ms;
+        dev_send (x, st.route[x * st.N + nb], now, q, cur, (uint32_t) t);
+      }
+    d.t_ping[m] = now + st.ping_interval_ns;
+  }
+
+  /* ---- sources ---- */
+  PRB_HD int64_t
+  philox_gap (int f, uint32_t nd) const
+  {
+    uint64_t eid = st.env_id_base + (uint64_t) env;
+    uint32_t fkey = (uint32_t) (st.flow_src[f] * st.N + st.flow_dst[f]);
+    uint32_t r[4];
+    philox4x32 ((uint32_t) eid, (uint32_t) (eid >> 32), fkey, nd, (uint32_t) st.seed, (uint32_t) (st.seed >> 32), r);
+    double u = u01_53 (r[0], r[1]);
+    double delay = dmul_ (st.flow_mean_s[f], neglog (u));
+    return (int64_t) dmul_ (delay, 1e9);
+  }
+
+  PRB_HD void
+  schedule_flow (int f, bool first, int64_t now)
+  {
+    if (st.inject_mode == PRB_INJECT_TRACE)
+      {
+        int32_t i = first ? st.flow_first[f] : st.tr_next[(int32_t) d.f_pos[f]];
+        d.f_pos[f] = (uint32_t) i;
+        d.f_ts[f] = i >= 0 ? st.tr_t[i] : P_FAR;
+        return;
+      }
+    int64_t base = now;
+    uint32_t nd = d.f_pos[f];
+    if (first)
+      {
+        uint64_t eid = st.env_id_base + (uint64_t) env;
+        uint32_t fkey = (uint32_t) (st.flow_src[f] * st.N + st.flow_dst[f]);
+        uint32_t r[4];
+        philox4x32 ((uint32_t) eid, (uint32_t) (eid >> 32), fkey, 0u, (uint32_t) st.seed, (uint32_t) (st.seed >> 32), r);
+        base = 100000 + (int64_t) dmul_ (u01_53 (r[0], r[1]), 1e9);
+        nd = 1;
+      }
+    d.f_pos[f] = nd + 1;
+    d.f_ts[f] = base + philox_gap (f, nd);
+  }
+
+  /* when was the pending injection of flow f scheduled: the flow's previous injection (or setup) */
+  PRB_HD int64_t
+  flow_sched_time (int f) const
+  {
+    if (st.inject_mode == PRB_INJECT_TRACE)
+      {
+        int32_t i = (int32_t) d.f_pos[f];
+        int32_t pv = i >= 0 ? ps.tr_prev[i] : -1;
+        return pv >= 0 ? st.tr_t[pv] : -1;
+      }
+    uint32_t nd = d.f_pos[f] - 1;       /* ordinal of the gap that produced f_ts */
+    if (nd <= 1) return -1;
+    return d.f_ts[f] - philox_gap (f, nd);
+  }
+
+  PRB_HD PCtx
+  flow_ctx (int f) const
+  {
+    PCtx c;
+    c.sched = flow_sched_time (f);
+    c.code = P_CODE_FLOW;
+    c.ord = ord_empty (c.sched < 0 ? (uint32_t) (st.M + f) : P_NONE16, P_NONE16);
+    if (c.sched >= 0) c.ord.a = (uint64_t) ((P_CODE_FLOW << 7) | 1u) << 48;
+    return c;
+  }
+
+  /* earliest injection among the flows of node x; equal times: the one scheduled first */
+  PRB_HD void
+  rescan_flows (int x)
+  {
+    int64_t bt = P_FAR;
+    int bf = -1;
+    for (int f = ps.flow_begin[x]; f < ps.flow_begin[x + 1]; f++)
+      {
+        int64_t t = d.f_ts[f];
+        if (t < bt)
+          {
+            bt = t; bf = f;
+          }
+        else if (PRB_UNLIKELY (t == bt && t != P_FAR))
+          {
+            int64_t a = flow_sched_time (bf), b = flow_sched_time (f);
+            if (a == b && a >= 0) acc.errors |= PRB_ERR_TIE;
+            if (b < a) bf = f;      /* same setup time (-1): creation order, i.e. the lower index stays */
+          }
+      }
+    d.fmin_ts[x] = bt;
+    d.fmin_f[x] = bf;
+  }
+
+  /* PoissonGeneratorApplication::SendPacket */
+  PRB_HD void
+  inject (int x, int f, int64_t now)
+  {
+    acc.ev_real++;
+    const PCtx cur = flow_ctx (f);
+    int src = st.flow_src[f], dst = st.flow_dst[f];
+    Pkt p;
+    blank (p);
+    set_p_type (p, PRB_DATA);
+    set_p_dst (p, dst); set_p_src (p, src); set_p_next_hop (p, src); set_p_last_hop (p, NODE_NONE);
+    set_p_prev_node (p, NODE_NONE);
+    set_p_szc (p, SZC_DATA_INJ);
+    p.aux = (uint32_t) (uint64_t) ns_to_seconds_ (now);
+    int both = st.map_overlay[src] >= 0 && st.map_overlay[dst] >= 0;
+    if (st.inject_mode == PRB_INJECT_TRACE)
+      {
+        int32_t i = (int32_t) d.f_pos[f];
+        p.uid = st.tr_uid[i];
+        set_p_valable (p, st.tr_flags[i] & 1);
+        set_p_rejected (p, (st.tr_flags[i] >> 1) & 1);
+      }
+    else
+      {
+        /* packet uids of synthetic traffic: (ordinal of the packet inside its flow) * F + flow */
+        p.uid = (d.f_pos[f] - 1) * (uint32_t) st.F + (uint32_t) f;
+        set_p_valable (p, both ? 1 : 0);
+        double prej = (st.opt_agent && st.opt_rejected) ? st.opt_rejected[src * st.N + dst] : 0.0;
+        int rej = 0;
+        if (prej > 0.0)
+          {
+            uint64_t eid = st.env_id_base + (uint64_t) env;
+            uint32_t r[4];
+            philox4x32 ((uint32_t) eid, (uint32_t) (eid >> 32), (uint32_t) (src * st.N + dst), d.f_pos[f] - 1,
+                        (uint32_t) st.seed, (uint32_t) (st.seed >> 32), r);
+            double u = dmul_ (dadd_ ((double) r[2], 0.5), 1.0 / 4294967296.0);
+            rej = u < prej ? 1 : 0;
+          }
+        set_p_rejected (p, rej);
+      }
+    set_p_first_hop (p, p_valable (p));
+    set_p_ipdst (p, dst);
+    dev_send (x, st.L + src, now, p, cur, P_NONE16);
+    schedule_flow (f, false, now);
+    rescan_flows (x);
+  }
+
+  /* ---- order of two simultaneous events of one node ---- */
+  PRB_HD PCtx
+  cand_ctx (const PCand &c) const
+  {
+    switch (c.kind)
+      {
+      case PK_RCV:
+        return rcv_ctx (c.idx, c.ts, d.rings[ps.ring_off[c.idx] + (d.head[c.idx] & ps.ring_mask[c.idx])]);
+      case PK_TXC:
+        return txc_ctx (c.idx, c.ts);
+      case PK_FLOW:
+        return flow_ctx (c.idx);
+      default:
+        return ping_ctx (c.idx, c.ts);
+      }
+  }
+
+  /* true when a runs before b (same timestamp, same node).
+   * 1. the event that was scheduled earlier has the smaller scheduler uid;
+   * 2. TransmitStart schedules its TransmitComplete before the peer's Receive (zero-delay access link);
+   * 3. scheduled at the same instant: the parents ran at the same instant, and so on back — the histories
+   *    (POrd) are compared generation by generation, down to the creation order of the setup events (ping
+   *    timers in overlay-index order before the sources, sim.cc:519-560,599-632) and the tunnel order inside
+   *    one ping round (data-packet-manager.cc:349-357);
+   * 4. histories that do not tell (shed entries, a source among the ancestors) set PRB_ERR_TIE unless the
+   *    two events cannot influence each other (TransmitComplete of two different devices). */
+  PRB_HDN bool
+  tie_before (const PCand &a, const PCand &b)
+  {
+    PCtx ca = cand_ctx (a), cb = cand_ctx (b);
+    if (ca.sched != cb.sched) return ca.sched < cb.sched;
+    if (a.kind == PK_TXC && b.kind == PK_RCV && a.idx == b.idx) return true;
+    if (a.kind == PK_RCV && b.kind == PK_TXC && a.idx == b.idx) return false;
+    int r = ord_compare (ca.ord, cb.ord);
+    if (r != 0) return r < 0;
+    if (!(a.kind == PK_TXC && b.kind == PK_TXC))
+      {
+#if defined(PRB_DEBUG_TIES) && !defined(__CUDA_ARCH__)
+        fprintf (stderr, "tie: ts=%lld sched=%lld a=(%d,%d) b=(%d,%d) ord=%016llx.%016llx / %016llx.%016llx\n", (long long) a.ts,
+                 (long long) ca.sched, a.kind, a.idx, b.kind, b.idx, (unsigned long long) ca.ord.a, (unsigned long long) ca.ord.b,
+                 (unsigned long long) cb.ord.a, (unsigned long long) cb.ord.b);
+#endif
+        acc.errors |= PRB_ERR_TIE;
+      }
+    return a.kind != b.kind ? a.kind < b.kind : a.idx < b.idx;
+  }
+
+  PRB_HD void
+  offer (PCand &best, int64_t ts, int kind, int idx)
+  {
+    if (ts < best.ts)
+      {
+        best.ts = ts; best.kind = kind; best.idx = idx;
+      }
+    else if (PRB_UNLIKELY (ts == best.ts && ts != P_FAR))
+      {
+        PCand c;
+        c.ts = ts; c.kind = kind; c.idx = idx;
+        if (tie_before (c, best)) best = c;
+      }
+  }
+
+  /* earliest pending event of node x */
+  PRB_HD PCand
+  select (int x)
+  {
+    PCand b;
+    b.ts = P_FAR; b.kind = PK_NONE; b.idx = -1;
+    const int W = ps.W;
+    for (int j = 0; j < ps.DEG; j++)
+      {
+        int l = ps.in_links[x * ps.DEG + j];
+        if (l < 0) break;
+        uint16_t h = d.head[l];
+        if (h != d.mid[l]) offer (b, d.w_ts[l * W + (h & (W - 1))], PK_RCV, l);
+      }
+    for (int j = 0; j < ps.DEG; j++)
+      {
+        int l = ps.out_links[x * ps.DEG + j];
+        if (l < 0) break;
+        if (d.mid[l] != d.tail[l]) offer (b, d.busy[l], PK_TXC, l);
+      }
+    {
+      int l = st.L + x;
+      uint16_t h = d.head[l], m = d.mid[l];
+      if (m != d.tail[l]) offer (b, d.busy[l], PK_TXC, l);
+      if (h != m) offer (b, d.w_ts[l * W + (h & (W - 1))], PK_RCV, l);
+    }
+    int m = st.map_overlay[x];
+    if (m >= 0) offer (b, d.t_ping[m], PK_PING, m);
+    if (d.fmin_f[x] >= 0) offer (b, d.fmin_ts[x], PK_FLOW, d.fmin_f[x]);
+    return b;
+  }
+
+  /* does c lie before the end of this run (until_ns) and of the simulation? */
+  PRB_HD bool
+  in_time (const PCand &c, int64_t until_ns) const
+  {
+    if (c.kind == PK_NONE) return false;
+    const int64_t stop = st.sim_time_ns;
+    if (c.ts < until_ns && c.ts < stop) return true;
+    /* Simulator::Stop is scheduled after the first ping timers: a first ping at exactly simTime still runs */
+    return c.ts == stop && until_ns >= stop && c.kind == PK_PING && d.ping_index[c.idx] == 0;
+  }
+
+  /* may node x execute c now?  (t_next[] of every node is published, gmin is their minimum) */
+  PRB_HD bool
+  safe (int x, const PCand &c, int64_t gmin, int64_t until_ns) const
+  {
+    if (!in_time (c, until_ns)) return false;
+    if (stat_room (x) < 2) return false;
+    if (c.ts >= sat_add (gmin, 2 * ps.la_ns)) return false;
+    for (int j = 0; j < ps.DEG; j++)
+      {
+        int l = ps.in_links[x * ps.DEG + j];
+        if (l < 0) break;
+        int64_t tn = d.t_next[st.link_from[l]];
+        int64_t b = d.busy[l];
+        if (c.ts >= sat_add (b > tn ? b : tn, ps.la_ns)) return false;
+      }
+    return true;
+  }
+
+  PRB_HD void
+  execute (int x, const PCand &c)
+  {
+    switch (c.kind)
+      {
+      case PK_RCV: receive (x, c.idx, c.ts); break;
+      case PK_TXC: transmit_complete (c.idx, c.ts); break;
+      case PK_FLOW: inject (x, c.idx, c.ts); break;
+      case PK_PING: ping_timer (x, c.idx, c.ts); break;
+      default: break;
+      }
+  }
+
+  /* what sim.cc schedules before Simulator::Run, for the nodes of this lane */
+  PRB_HD void
+  start_node (int x)
+  {
+    int m = st.map_overlay[x];
+    if (m >= 0) d.t_ping[m] = st.ping_interval_ns;
+    for (int f = ps.flow_begin[x]; f < ps.flow_begin[x + 1]; f++) schedule_flow (f, true, 0);
+    rescan_flows (x);
+  }
+};
+
+/* fold one statistics record into the float32 sums (ComputeStats push order) */
+PRB_HD void
+p_apply_stat (prb_counters &c, const PStat &s)
+{
+  switch (s.code)
+    {
+    case PS_OVERLAY_ARRIVED:
+      c.sum_cost = fadd_ (c.sum_cost, s.v); c.n_cost++;
+      c.sum_e2e = fadd_ (c.sum_e2e, s.v); c.n_e2e++;
+      break;
+    case PS_UNDERLAY_ARRIVED:
+      c.sum_underlay_cost = fadd_ (c.sum_underlay_cost, s.v); c.n_underlay_cost++;
+      c.sum_underlay_e2e = fadd_ (c.sum_underlay_e2e, s.v); c.n_underlay_e2e++;
+      break;
+    case PS_OVERLAY_DROP:
+      c.sum_cost = fadd_ (c.sum_cost, s.v); c.n_cost++;
+      break;
+    default:
+      c.sum_underlay_cost = fadd_ (c.sum_underlay_cost, s.v); c.n_underlay_cost++;
+      break;
+    }
+}
+
+/* add a lane's counters to the environment's totals (device: shared/global atomics) */
+PRB_HD void
+p_add_u64 (int64_t *dst, uint32_t v)
+{
+  if (v == 0) return;
+#if defined(__CUDA_ARCH__)
+  atomicAdd ((unsigned long long *) dst, (unsigned long long) v);
+#else
+  *dst += v;
+#endif
+}
+
+PRB_HD void
+p_flush_acc (PScal *sc, const PAcc &a)
+{
+  prb_counters &c = sc->c;
+  p_add_u64 (&c.overlay_injected, a.overlay_injected); p_add_u64 (&c.overlay_arrived, a.overlay_arrived);
+  p_add_u64 (&c.overlay_lost, a.overlay_lost); p_add_u64 (&c.underlay_injected, a.underlay_injected);
+  p_add_u64 (&c.underlay_arrived, a.underlay_arrived); p_add_u64 (&c.underlay_lost, a.underlay_lost);
+  p_add_u64 (&c.bytes_data, a.bytes_data); p_add_u64 (&c.bytes_signaling, a.bytes_signaling);
+  p_add_u64 (&c.packet_hops, a.packet_hops); p_add_u64 (&c.data_hops, a.data_hops);
+  p_add_u64 (&c.env_steps, a.env_steps); p_add_u64 (&c.decisions, a.decisions); p_add_u64 (&c.vanished, a.vanished);
+  p_add_u64 (&sc->ev_real, a.ev_real); p_add_u64 (&sc->tx_started, a.tx_started);
+  if (a.errors)
+    {
+#if defined(__CUDA_ARCH__)
+      atomicOr ((int *) &c.errors, (int) a.errors);
+#else
+      c.errors |= (int32_t) a.errors;
+#endif
+    }
+}
+
+/* read-out: same fields as the serial engine's finalize_counters */
+PRB_HD void
+p_finalize_counters (const Static &st, const PDyn &d, prb_counters &c)
+{
+  const PScal *sc = d.sc;
+  c = sc->c;
+  /* events = Receive + injections + ping timers + every TransmitComplete that lies before the frontier */
+  int64_t pending = 0;
+  for (int l = 0; l < st.LA; l++)
+    if (d.busy[l] >= sc->front_ts && d.busy[l] != 0) pending++;
+  c.events = sc->ev_real + sc->tx_started - pending;
+  c.end_ns = sc->front_ts;
+  c.avg_e2e = c.n_e2e ? c.sum_e2e / (float) c.n_e2e : 0.0f;
+  c.avg_cost = c.n_cost ? c.sum_cost / (float) c.n_cost : 0.0f;
+  c.avg_underlay_e2e = c.n_underlay_e2e ? c.sum_underlay_e2e / (float) c.n_underlay_e2e : 0.0f;
+  c.avg_underlay_cost = c.n_underlay_cost ? c.sum_underlay_cost / (float) c.n_underlay_cost : 0.0f;
+  c.signaling_overhead = c.bytes_data ? (float) (int32_t) c.bytes_signaling / (float) (int32_t) c.bytes_data : 0.0f;
+}
+
+}  // namespace prb

@@ -57,8 +57,39 @@ def lib():
         L.hs_tx_time_ns.argtypes = [C.c_uint32, C.c_uint64]
         L.hs_invert_1e9.argtypes = [C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
         L.hs_global_routes.argtypes = [i32, C.POINTER(C.c_uint8), C.POINTER(i32)]
+        L.hp_create.restype = vp
+        L.hp_create.argtypes = [C.POINTER(_abi.PrbConfig), C.c_int, i64, C.c_int]
+        L.hp_destroy.argtypes = [vp]
+        L.hp_set_inject_trace.argtypes = L.hs_set_inject_trace.argtypes
+        L.hp_set_policy.argtypes = [vp, C.c_int, C.POINTER(i32), i64]
+        L.hp_run.argtypes = [vp, i64, C.c_int]
+        L.hp_counters.argtypes = [vp, C.POINTER(_abi.PrbCounters)]
+        for f in ("hp_num_events", "hp_rounds", "hp_executed", "hp_lookahead_ns"):
+            getattr(L, f).restype = i64
+            getattr(L, f).argtypes = [vp]
+        L.hp_events.restype = vp
+        L.hp_events.argtypes = [vp]
+        L.hp_num_links.argtypes = [vp]
+        L.hp_queue_bytes.argtypes = [vp, i32]
+        L.hp_wire_slots.argtypes = [vp]
+        L.hp_state_bytes.argtypes = [vp]
         _lib = L
     return _lib
+
+
+def node_trace(decisions_node, decisions_action, o2u):
+    """Per-node action lists for PRB_POLICY_NODE_TRACE from a global decision log: [M+1 offsets][actions].
+    Only the steps where the agent was consulted (action >= 0) consume an action."""
+    m = len(o2u)
+    u2o = {int(u): i for i, u in enumerate(o2u)}
+    per = [[] for _ in range(m)]
+    for n, a in zip(decisions_node, decisions_action):
+        if a >= 0:
+            per[u2o[int(n)]].append(int(a))
+    off = np.zeros(m + 1, dtype=np.int32)
+    off[1:] = np.cumsum([len(x) for x in per])
+    flat = np.array([a for x in per for a in x], dtype=np.int32)
+    return np.concatenate([off, flat]).astype(np.int32)
 
 
 class HostSim:
@@ -127,3 +158,66 @@ class HostSim:
     def queue_bytes(self):
         nl = lib().hs_num_links(self.h)
         return np.array([lib().hs_queue_bytes(self.h, l) for l in range(nl)], dtype=np.int32)
+
+
+class HostParSim:
+    """The node-parallel engine (prisma_b200/csrc/par_core.cuh) with the lanes of a team emulated in turn."""
+
+    def __init__(self, params, env_index=0, ev_cap=1 << 21, team=32):
+        self._keep = []
+        self.cfg = _abi.fill_config(_abi.PrbConfig(), self._keep, params)
+        self.h = lib().hp_create(C.byref(self.cfg), env_index, ev_cap, team)
+        if not self.h:
+            raise ValueError("hp_create failed (configuration not supported by the parallel engine?)")
+
+    def close(self):
+        if self.h:
+            lib().hp_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def set_inject_trace(self, t_ns, src, dst, uid, valable, rejected):
+        a = [np.ascontiguousarray(t_ns, dtype=np.int64), np.ascontiguousarray(src, dtype=np.int32),
+             np.ascontiguousarray(dst, dtype=np.int32), np.ascontiguousarray(uid, dtype=np.int64),
+             np.ascontiguousarray(valable, dtype=np.uint8), np.ascontiguousarray(rejected, dtype=np.uint8)]
+        rc = lib().hp_set_inject_trace(self.h, len(a[0]), _abi.ptr(a[0], C.c_int64), _abi.ptr(a[1], C.c_int32),
+                                       _abi.ptr(a[2], C.c_int32), _abi.ptr(a[3], C.c_int64),
+                                       _abi.ptr(a[4], C.c_uint8), _abi.ptr(a[5], C.c_uint8))
+        if rc != 0:
+            raise ValueError("bad injection trace")
+
+    def set_policy(self, kind, data=None):
+        d = np.ascontiguousarray(data if data is not None else [], dtype=np.int32).ravel()
+        lib().hp_set_policy(self.h, _abi.POLICY[kind], _abi.ptr(d, C.c_int32), d.size)
+
+    def run(self, until_ns=None, log=True):
+        lib().hp_run(self.h, int(until_ns if until_ns is not None else self.cfg.sim_time_ns), 1 if log else 0)
+
+    def counters(self):
+        c = _abi.PrbCounters()
+        lib().hp_counters(self.h, C.byref(c))
+        return {n: getattr(c, n) for n, _ in c._fields_}
+
+    def events(self):
+        n = lib().hp_num_events(self.h)
+        if n == 0:
+            return np.zeros(0, dtype=_abi.EVENT_DTYPE)
+        buf = (C.c_char * (n * 64)).from_address(lib().hp_events(self.h))
+        return np.frombuffer(buf, dtype=_abi.EVENT_DTYPE).copy()
+
+    def queue_bytes(self):
+        nl = lib().hp_num_links(self.h)
+        return np.array([lib().hp_queue_bytes(self.h, l) for l in range(nl)], dtype=np.int32)
+
+    @property
+    def rounds(self):
+        return lib().hp_rounds(self.h)
+
+    @property
+    def executed(self):
+        return lib().hp_executed(self.h)
