@@ -159,6 +159,14 @@ int32_t prb_global_routes (int32_t n, const uint8_t *adj, int32_t *route_out);
 int prb_create (const prb_config *cfg, int device, void *cuda_stream, prb_env **out);
 int prb_destroy (prb_env *env);
 int prb_reset (prb_env *env);
+/* engine of prb_run: PRB_ENGINE_AUTO picks the node-parallel engine (one lane per network node, conservative
+ * lookahead inside an environment) for table / per-node-trace agents without ordered logs, the event-serial
+ * one otherwise (prb_step, trace and random agents, prb_enable_log).  team: lanes per environment of the
+ * parallel engine, 0 = from the node count.  prb_engine: the engine that has advanced the environments
+ * since the last reset (0 none).  prb_round_stats: rounds and events of the parallel engine so far. */
+int prb_set_engine (prb_env *env, int mode, int team);
+int prb_engine (prb_env *env);
+int prb_round_stats (prb_env *env, int64_t *rounds, int64_t *executed);
 int prb_num_links (prb_env *env);        /* L (switch<->switch, directed) */
 int prb_state_bytes (prb_env *env, int64_t *blob_bytes, int64_t *pool_bytes);
 
@@ -166,8 +174,8 @@ int prb_state_bytes (prb_env *env, int64_t *blob_bytes, int64_t *pool_bytes);
 int prb_set_inject_trace (prb_env *env, int64_t n, const int64_t *t_ns, const int32_t *src, const int32_t *dst,
                           const int64_t *uid, const uint8_t *valable, const uint8_t *rejected);
 /* agent hook evaluated on the device: TABLE data[M*M] (row = stepping overlay node, column = obs[0]);
- * TRACE data[n] actions in decision order; RANDOM uses seed (+ env index); data_dev != 0: data is a DEVICE
- * pointer that stays owned by the caller */
+ * TRACE data[n] actions in decision order; RANDOM uses seed (+ env index); NODE_TRACE data = [M+1 offsets]
+ * [actions of overlay node 0][of node 1]...: every node replays its own decisions (parallel engine) */
 int prb_set_policy (prb_env *env, int kind, const int32_t *data, int64_t n, uint64_t seed);
 
 /* parity logs: per-env capacities (records); 0 disables */

@@ -22,7 +22,8 @@ POLICY = {"zero": 0, "table": 1, "trace": 2, "random": 3, "node_trace": 4}
 ENGINE = {"auto": 0, "serial": 1, "parallel": 2}
 SIGNALING = {"ideal": 0, "NN": 1, "target": 2, "digital_twin": 3}
 ERR_BITS = {1: "packet pool exhausted", 2: "log capacity exceeded", 4: "ping window too short",
-            8: "action trace exhausted", 16: "scheduler uid overflow"}
+            8: "action trace exhausted", 16: "scheduler uid overflow",
+            32: "order of simultaneous events not determined (parallel engine)"}
 
 
 class PrbConfig(C.Structure):
@@ -159,6 +160,9 @@ def lib():
         "prb_queue_bytes": (C.c_int, [vp, i32, C.POINTER(i32)]),
         "prb_sync": (C.c_int, [vp]),
         "prb_launch_count": (i64, [vp]),
+        "prb_set_engine": (C.c_int, [vp, C.c_int, C.c_int]),
+        "prb_engine": (C.c_int, [vp]),
+        "prb_round_stats": (C.c_int, [vp, C.POINTER(i64), C.POINTER(i64)]),
     }
     for name, (res, args) in sig.items():
         f = getattr(L, name)   # raises AttributeError if the library does not export a declared symbol
@@ -172,7 +176,7 @@ EXPORTS = ["prb_last_error", "prb_version", "prb_seconds_to_ns", "prb_ns_to_seco
            "prb_build_links", "prb_global_routes", "prb_create", "prb_destroy", "prb_reset", "prb_num_links",
            "prb_state_bytes", "prb_set_inject_trace", "prb_set_policy", "prb_enable_log", "prb_read_events",
            "prb_read_steps", "prb_run", "prb_step", "prb_step_host", "prb_counters_host", "prb_counters_dev",
-           "prb_queue_bytes", "prb_sync", "prb_launch_count"]
+           "prb_queue_bytes", "prb_sync", "prb_launch_count", "prb_set_engine", "prb_engine", "prb_round_stats"]
 
 
 class PrbError(RuntimeError):

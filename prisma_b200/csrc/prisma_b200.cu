@@ -196,6 +196,202 @@ k_advance (const __grid_constant__ Static st, const LaunchArgs a)
     }
 }
 
+
+/* ------------------------------------------------------------------------------------------------
+ * Node-parallel engine (par_core.cuh): a team of T lanes per environment, lane g owns the nodes g, g+T, ...
+ * One round = every lane finds the earliest pending event of its nodes and publishes its timestamp, the
+ * team reduces the minimum, folds the float statistics that have become final, and every lane whose event
+ * is inside the lookahead of its neighbours executes it.  The environment's state lives in shared memory
+ * for the whole launch; packet records move through per-link rings in HBM.
+ * ---------------------------------------------------------------------------------------------- */
+struct ParArgs
+{
+  char *pblobs;           /* [E * pblob_bytes] */
+  PRec *rings;            /* [E * ring_records] */
+  prb_event *ev_logs;     /* [E * ev_cap] or null */
+  int64_t until_ns;
+  unsigned long long *round_stats;   /* optional: [0] rounds, [1] events executed (diagnostics) */
+};
+
+template <int T, bool LOG, bool SMEM>
+__global__ void __launch_bounds__ (128)
+k_run_par (const __grid_constant__ Static st, const __grid_constant__ PStatic ps, const ParArgs a)
+{
+  extern __shared__ __align__ (16) char smem[];
+  const int lane = threadIdx.x & 31;
+  const int gl = lane % T;
+  const int leader = (lane / T) * T;
+  const int team_in_block = threadIdx.x / T;
+  const int env = blockIdx.x * (blockDim.x / T) + team_in_block;
+  const unsigned tmask = T == 32 ? 0xFFFFFFFFu : (((1u << T) - 1u) << leader);
+  if (env >= st.E) return;             /* whole teams leave together: every sync below names tmask only */
+  char *gblob = a.pblobs + (size_t) env * ps.pblob_bytes;
+  char *blob = gblob;
+  if (SMEM)
+    {
+      blob = smem + (size_t) team_in_block * ps.pblob_bytes;
+      const uint4 *src = (const uint4 *) gblob;
+      uint4 *dst = (uint4 *) blob;
+      for (int i = gl; i < ps.pblob_bytes / 16; i += T) dst[i] = src[i];
+      __syncwarp (tmask);
+    }
+  PDyn d;
+  p_bind_state (ps, blob, d);
+  d.rings = a.rings + (size_t) env * ps.ring_records;
+  d.ev_log = LOG && a.ev_logs ? a.ev_logs + (size_t) env * st.ev_cap : nullptr;
+  PScal *sc = d.sc;
+  PAcc acc;
+  memset (&acc, 0, sizeof (acc));
+  PSim<LOG> sim (st, ps, d, acc, env);
+  const int N = st.N;
+  const int64_t stop = st.sim_time_ns;
+  const int64_t until = a.until_ns;
+  const int64_t base = sc->front_ts;          /* timestamps of this launch are reduced as 32-bit offsets */
+  const bool finished = sc->finished != 0;
+  unsigned rounds = 0, executed = 0;
+
+  if (!finished && !sc->started)
+    for (int x = gl; x < N; x += T) sim.start_node (x);
+  __syncwarp (tmask);
+
+  /* every statistics record older than `bound`, in timestamp order; one lane applies at a time */
+  auto fold = [&] (int64_t bound) {
+    for (;;)
+      {
+        int64_t ft = P_FAR;
+        int fx = -1;
+        for (int x = gl; x < N; x += T)
+          if (d.s_head[x] != d.s_tail[x])
+            {
+              int64_t ts = d.sring[x * P_SR + (d.s_head[x] & (P_SR - 1))].ts;
+              if (ts < bound && ts < ft)
+                {
+                  ft = ts; fx = x;
+                }
+            }
+        uint32_t rel = fx < 0 ? 0xFFFFFFFFu : (uint32_t) (ft - base);
+        uint32_t m = __reduce_min_sync (tmask, rel);
+        if (m == 0xFFFFFFFFu) break;
+        unsigned b = __ballot_sync (tmask, rel == m);
+        if (lane == __ffs (b) - 1)
+          {
+            p_apply_stat (sc->c, d.sring[fx * P_SR + (d.s_head[fx] & (P_SR - 1))]);
+            d.s_head[fx] = (uint8_t) (d.s_head[fx] + 1);
+          }
+        __syncwarp (tmask);
+      }
+  };
+
+  while (!finished)
+    {
+      /* phase 1: earliest pending event of my nodes */
+      PCand c0;
+      c0.ts = P_FAR; c0.kind = PK_NONE; c0.idx = -1;
+      int64_t mt = P_FAR;
+      bool mine_in_time = false;
+      for (int x = gl, i = 0; x < N; x += T, i++)
+        {
+          PCand c = sim.select (x);
+          d.t_next[x] = c.ts;
+          if (i == 0) c0 = c;
+          mt = c.ts < mt ? c.ts : mt;
+          mine_in_time = mine_in_time || sim.in_time (c, until);
+        }
+      __syncwarp (tmask);
+      if (!__any_sync (tmask, mine_in_time)) break;
+      uint64_t off = (uint64_t) (mt - base);
+      uint32_t rel = mt == P_FAR || off > 0xFFFFFFFEull ? 0xFFFFFFFEu : (uint32_t) off;
+      const int64_t gmin = base + (int64_t) __reduce_min_sync (tmask, rel);
+      fold (gmin);
+      /* phase 2: the earliest of my events that nothing can precede any more */
+      PCand my;
+      my.ts = P_FAR; my.kind = PK_NONE; my.idx = -1;
+      int myx = -1;
+      for (int x = gl, i = 0; x < N; x += T, i++)
+        {
+          PCand c = i == 0 ? c0 : sim.select (x);
+          if (c.ts < my.ts && sim.safe (x, c, gmin, until))
+            {
+              my = c; myx = x;
+            }
+        }
+      unsigned go = __ballot_sync (tmask, myx >= 0);     /* also orders the reads above before the handlers */
+      if (go == 0)
+        {
+          acc.errors |= PRB_ERR_SEQ;                       /* cannot happen: the node that holds gmin is safe */
+          break;
+        }
+      if (myx >= 0) sim.execute (myx, my);
+      __syncwarp (tmask);
+      rounds++;
+      executed += __popc (go);
+    }
+  __syncwarp (tmask);
+  if (!finished)
+    {
+      fold (P_FAR);
+      p_flush_acc (sc, acc);
+      __syncwarp (tmask);
+      if (gl == 0)
+        {
+          sc->started = 1;
+          sc->front_ts = until < stop ? until : stop;
+          if (until >= stop) sc->finished = 1;
+          if (a.round_stats)
+            {
+              atomicAdd (&a.round_stats[0], (unsigned long long) rounds);
+              atomicAdd (&a.round_stats[1], (unsigned long long) executed);
+            }
+        }
+    }
+  if (SMEM)
+    {
+      __syncwarp (tmask);
+      const uint4 *src = (const uint4 *) blob;
+      uint4 *dst = (uint4 *) gblob;
+      for (int i = gl; i < ps.pblob_bytes / 16; i += T) dst[i] = src[i];
+    }
+}
+
+__global__ void
+k_reset_par (const __grid_constant__ Static st, const __grid_constant__ PStatic ps, char *pblobs, const char *pblob0)
+{
+  const int64_t words = ps.pblob_bytes / 16;
+  const int64_t total = words * st.E;
+  const int64_t stride = (int64_t) gridDim.x * blockDim.x;
+  for (int64_t i = (int64_t) blockIdx.x * blockDim.x + threadIdx.x; i < total; i += stride)
+    ((uint4 *) pblobs)[i] = ((const uint4 *) pblob0)[i % words];
+}
+
+__global__ void
+k_counters_par (const __grid_constant__ Static st, const __grid_constant__ PStatic ps, const char *pblobs, prb_counters *out)
+{
+  int e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= st.E) return;
+  PDyn d;
+  p_bind_state (ps, const_cast<char *> (pblobs) + (size_t) e * ps.pblob_bytes, d);
+  prb_counters c;
+  p_finalize_counters (st, d, c);
+  out[e] = c;
+}
+
+__global__ void
+k_queue_bytes_par (const __grid_constant__ Static st, const __grid_constant__ PStatic ps, const char *pblobs, int e, int32_t *out)
+{
+  int l = blockIdx.x * blockDim.x + threadIdx.x;
+  if (l >= st.L) return;
+  const uint32_t *q = (const uint32_t *) (pblobs + (size_t) e * ps.pblob_bytes + ps.off_q_bytes);
+  out[l] = (int32_t) q[l];
+}
+
+__global__ void
+k_log_counts_par (const __grid_constant__ PStatic ps, const char *pblobs, int e, int64_t *out)
+{
+  const PScal *sc = (const PScal *) (pblobs + (size_t) e * ps.pblob_bytes + ps.off_scal);
+  out[0] = sc->ev_n;
+  out[1] = 0;
+}
+
 /* reset: every env gets the initial blob, its policy RNG, and a fully linked free list */
 __global__ void
 k_reset (const __grid_constant__ Static st, char *blobs, Pkt *pools, const char *blob0)
@@ -282,6 +478,20 @@ struct prb_env
   int64_t *d_scratch = nullptr;
   int64_t launches = 0;
   bool log_on = false;
+  /* node-parallel engine */
+  PModel pm;
+  PStatic dps;                /* PStatic with DEVICE table pointers */
+  char *d_ptables = nullptr;
+  char *d_pblob0 = nullptr;
+  char *d_pblobs = nullptr;   /* allocated on first use */
+  PRec *d_rings = nullptr;
+  int32_t *d_tr_prev = nullptr;
+  unsigned long long *d_round_stats = nullptr;
+  int engine_mode = PRB_ENGINE_AUTO;
+  int engine_active = 0;      /* engine that has advanced the environments since the last reset (0: none) */
+  int team = 0;
+  int64_t par_front_ns = 0;
+  bool pol_node_trace = false;
 };
 
 template <typename T>
@@ -322,6 +532,110 @@ upload_tables (prb_env *env)
   s.opt_rejected = hm.opt_rejected.empty () ? nullptr : (const double *) (b + o[14]);
   s.pol_data = nullptr; s.pol_n = 0;
   s.tr_t = nullptr; s.tr_uid = nullptr; s.tr_flags = nullptr; s.tr_next = nullptr; s.flow_first = nullptr;
+  return PRB_OK;
+}
+
+static int
+upload_ptables (prb_env *env)
+{
+  PModel &pm = env->pm;
+  env->dps = pm.ps;
+  if (!pm.supported) return PRB_OK;
+  std::vector<char> buf;
+  size_t o[8];
+  place (buf, pm.in_links, o[0]); place (buf, pm.out_links, o[1]); place (buf, pm.ring_off, o[2]);
+  place (buf, pm.ring_mask, o[3]); place (buf, pm.flow_begin, o[4]); place (buf, pm.dcode_rcv, o[5]);
+  place (buf, pm.dcode_txc, o[6]);
+  CUDA_TRY (cudaMalloc (&env->d_ptables, buf.size ()));
+  CUDA_TRY (cudaMemcpyAsync (env->d_ptables, buf.data (), buf.size (), cudaMemcpyHostToDevice, env->stream));
+  CUDA_TRY (cudaMalloc (&env->d_pblob0, pm.ps.pblob_bytes));
+  CUDA_TRY (cudaMemcpyAsync (env->d_pblob0, pm.pblob0.data (), pm.ps.pblob_bytes, cudaMemcpyHostToDevice, env->stream));
+  CUDA_TRY (cudaMalloc (&env->d_round_stats, 16));
+  CUDA_TRY (cudaMemsetAsync (env->d_round_stats, 0, 16, env->stream));
+  CUDA_TRY (cudaStreamSynchronize (env->stream));
+  PStatic &s = env->dps;
+  char *b = env->d_ptables;
+  s.in_links = (const int16_t *) (b + o[0]); s.out_links = (const int16_t *) (b + o[1]);
+  s.ring_off = (const int32_t *) (b + o[2]); s.ring_mask = (const uint16_t *) (b + o[3]);
+  s.flow_begin = (const int32_t *) (b + o[4]); s.dcode_rcv = (const uint16_t *) (b + o[5]);
+  s.dcode_txc = (const uint16_t *) (b + o[6]);
+  s.tr_prev = nullptr; s.pol_off = nullptr;
+  return PRB_OK;
+}
+
+/* the parallel engine's state is allocated when it is first used */
+static int
+ensure_par_state (prb_env *env)
+{
+  if (env->d_pblobs) return PRB_OK;
+  const Static &st = env->dst;
+  const PStatic &ps = env->dps;
+  cudaError_t e = cudaMalloc (&env->d_pblobs, (size_t) ps.pblob_bytes * st.E);
+  if (e == cudaSuccess) e = cudaMalloc (&env->d_rings, sizeof (PRec) * (size_t) ps.ring_records * st.E);
+  if (e != cudaSuccess) return fail (PRB_ENOMEM, std::string ("cudaMalloc (parallel engine state): ") + cudaGetErrorString (e));
+  int64_t work = (int64_t) ps.pblob_bytes / 16 * st.E;
+  int blocks = (int) std::min<int64_t> ((work + 255) / 256, 148 * 16);
+  k_reset_par<<<blocks, 256, 0, env->stream>>> (st, ps, env->d_pblobs, env->d_pblob0);
+  CUDA_TRY (cudaGetLastError ());
+  env->launches++;
+  return PRB_OK;
+}
+
+template <int T, bool LOG>
+static int
+launch_par_t (prb_env *env, const ParArgs &a)
+{
+  const Static &st = env->dst;
+  const PStatic &ps = env->dps;
+  const int threads = 128;
+  const int teams = threads / T;
+  const int blocks = (st.E + teams - 1) / teams;
+  size_t smem = (size_t) teams * ps.pblob_bytes;
+  if (smem + 1024 <= (size_t) env->max_smem)
+    {
+      auto k = k_run_par<T, LOG, true>;
+      CUDA_TRY (cudaFuncSetAttribute (k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
+      k<<<blocks, threads, smem, env->stream>>> (st, ps, a);
+    }
+  else
+    k_run_par<T, LOG, false><<<blocks, threads, 0, env->stream>>> (st, ps, a);
+  CUDA_TRY (cudaGetLastError ());
+  env->launches++;
+  return PRB_OK;
+}
+
+static int
+launch_par (prb_env *env, const ParArgs &a)
+{
+  bool log = env->log_on;
+  switch (env->team)
+    {
+    case 8: return log ? launch_par_t<8, true> (env, a) : launch_par_t<8, false> (env, a);
+    case 16: return log ? launch_par_t<16, true> (env, a) : launch_par_t<16, false> (env, a);
+    case 32: return log ? launch_par_t<32, true> (env, a) : launch_par_t<32, false> (env, a);
+    default: return fail (PRB_EINVAL, "team size must be 8, 16 or 32");
+    }
+}
+
+/* prb_run on the parallel engine; launches cover at most 4 simulated seconds each (32-bit time offsets) */
+static int
+run_parallel (prb_env *env, int64_t until_ns)
+{
+  int rc = ensure_par_state (env);
+  if (rc != PRB_OK) return rc;
+  const int64_t stop = env->dst.sim_time_ns;
+  int64_t target = std::min (until_ns, stop);
+  ParArgs a;
+  a.pblobs = env->d_pblobs; a.rings = env->d_rings; a.ev_logs = env->d_ev; a.round_stats = env->d_round_stats;
+  do
+    {
+      int64_t chunk_end = std::min<int64_t> (target, env->par_front_ns + (int64_t) 4000000000ll);
+      a.until_ns = chunk_end >= stop ? std::max<int64_t> (until_ns, stop) : chunk_end;
+      if ((rc = launch_par (env, a)) != PRB_OK) return rc;
+      env->par_front_ns = chunk_end;
+    }
+  while (env->par_front_ns < target);
+  env->engine_active = PRB_ENGINE_PARALLEL;
   return PRB_OK;
 }
 
@@ -396,6 +710,8 @@ prb_destroy (prb_env *env)
   cudaFree (env->d_ev); cudaFree (env->d_st); cudaFree (env->d_pol); cudaFree (env->d_trace);
   cudaFree (env->d_flow_first); cudaFree (env->d_counters); cudaFree (env->d_out); cudaFree (env->d_actions);
   cudaFree (env->d_scratch);
+  cudaFree (env->d_ptables); cudaFree (env->d_pblob0); cudaFree (env->d_pblobs); cudaFree (env->d_rings);
+  cudaFree (env->d_tr_prev); cudaFree (env->d_round_stats);
   delete env;
   return PRB_OK;
 }
@@ -429,6 +745,9 @@ prb_create (const prb_config *cfg, int device, void *cuda_stream, prb_env **out)
   if (cudaSetDevice (device) != cudaSuccess) return guard (fail (PRB_ECUDA, "cudaSetDevice failed"));
   cudaDeviceGetAttribute (&env->max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, device);
   if ((rc = upload_tables (env)) != PRB_OK) return guard (rc);
+  build_pmodel (*cfg, env->hm, env->pm);      /* pm.supported says whether prb_run may use the parallel engine */
+  env->team = env->hm.st.N <= 8 ? 8 : (env->hm.st.N <= 16 ? 16 : 32);
+  if ((rc = upload_ptables (env)) != PRB_OK) return guard (rc);
   const Static &st = env->dst;
   auto alloc = [&] (void **p, size_t bytes) -> int {
     cudaError_t e = cudaMalloc (p, bytes);
@@ -470,6 +789,47 @@ prb_reset (prb_env *env)
   k_seed_policy<<<(st.E + 127) / 128, 128, 0, env->stream>>> (st, env->d_blobs);
   CUDA_TRY (cudaGetLastError ());
   env->launches += 2;
+  if (env->d_pblobs)
+    {
+      int64_t pwork = (int64_t) env->dps.pblob_bytes / 16 * st.E;
+      int pblocks = (int) std::min<int64_t> ((pwork + 255) / 256, 148 * 16);
+      k_reset_par<<<pblocks, 256, 0, env->stream>>> (st, env->dps, env->d_pblobs, env->d_pblob0);
+      CUDA_TRY (cudaGetLastError ());
+      env->launches++;
+    }
+  env->engine_active = 0;
+  env->par_front_ns = 0;
+  return PRB_OK;
+}
+
+int
+prb_set_engine (prb_env *env, int mode, int team)
+{
+  if (!env) return fail (PRB_EINVAL, "null handle");
+  if (mode < PRB_ENGINE_AUTO || mode > PRB_ENGINE_PARALLEL) return fail (PRB_EINVAL, "unknown engine");
+  if (team != 0 && team != 8 && team != 16 && team != 32) return fail (PRB_EINVAL, "team size must be 0 (auto), 8, 16 or 32");
+  if (mode == PRB_ENGINE_PARALLEL && !env->pm.supported)
+    return fail (PRB_EINVAL, "the parallel engine does not support this configuration: " + env->pm.why);
+  env->engine_mode = mode;
+  if (team) env->team = team;
+  return PRB_OK;
+}
+
+int prb_engine (prb_env *env) { return env ? env->engine_active : PRB_EINVAL; }
+
+int
+prb_round_stats (prb_env *env, int64_t *rounds, int64_t *executed)
+{
+  if (!env) return fail (PRB_EINVAL, "null handle");
+  unsigned long long h[2] = { 0, 0 };
+  if (env->d_round_stats)
+    {
+      CUDA_TRY (cudaSetDevice (env->device));
+      CUDA_TRY (cudaMemcpyAsync (h, env->d_round_stats, 16, cudaMemcpyDeviceToHost, env->stream));
+      CUDA_TRY (cudaStreamSynchronize (env->stream));
+    }
+  if (rounds) *rounds = (int64_t) h[0];
+  if (executed) *executed = (int64_t) h[1];
   return PRB_OK;
 }
 
@@ -479,8 +839,9 @@ int
 prb_state_bytes (prb_env *env, int64_t *blob_bytes, int64_t *pool_bytes)
 {
   if (!env) return fail (PRB_EINVAL, "null handle");
-  if (blob_bytes) *blob_bytes = env->dst.blob_bytes;
-  if (pool_bytes) *pool_bytes = (int64_t) sizeof (Pkt) * env->dst.P;
+  bool par = env->engine_active == PRB_ENGINE_PARALLEL;
+  if (blob_bytes) *blob_bytes = par ? env->dps.pblob_bytes : env->dst.blob_bytes;
+  if (pool_bytes) *pool_bytes = par ? (int64_t) sizeof (PRec) * env->dps.ring_records : (int64_t) sizeof (Pkt) * env->dst.P;
   return PRB_OK;
 }
 
@@ -511,6 +872,11 @@ prb_set_inject_trace (prb_env *env, int64_t n, const int64_t *t_ns, const int32_
   CUDA_TRY (cudaMemcpyAsync (env->d_flow_first, env->hm.flow_first.data (), sizeof (int32_t) * std::max (st.F, 1),
                              cudaMemcpyHostToDevice, env->stream));
   CUDA_TRY (cudaStreamSynchronize (env->stream));
+  cudaFree (env->d_tr_prev);
+  env->d_tr_prev = nullptr;
+  CUDA_TRY (cudaMalloc (&env->d_tr_prev, 4 * n + 16));
+  CUDA_TRY (cudaMemcpy (env->d_tr_prev, env->tr.prev.data (), 4 * n, cudaMemcpyHostToDevice));
+  env->dps.tr_prev = env->d_tr_prev;
   st.inject_mode = PRB_INJECT_TRACE;
   st.tr_n = n;
   st.tr_t = (const int64_t *) (env->d_trace + o_t);
@@ -527,7 +893,13 @@ prb_set_policy (prb_env *env, int kind, const int32_t *data, int64_t n, uint64_t
   if (!env) return fail (PRB_EINVAL, "null handle");
   CUDA_TRY (cudaSetDevice (env->device));
   Static &st = env->dst;
-  if (kind < PRB_POLICY_ZERO || kind > PRB_POLICY_RANDOM) return fail (PRB_EINVAL, "unknown policy kind");
+  if (kind < PRB_POLICY_ZERO || kind > PRB_POLICY_NODE_TRACE) return fail (PRB_EINVAL, "unknown policy kind");
+  if (kind == PRB_POLICY_NODE_TRACE)
+    {
+      if (!env->pm.supported) return fail (PRB_EINVAL, "per-node action traces need the parallel engine: " + env->pm.why);
+      if (!data || n < (int64_t) st.M + 1) return fail (PRB_EINVAL, "a per-node trace is [M+1 offsets][actions]");
+      if (data[0] != 0 || (int64_t) data[st.M] != n - (st.M + 1)) return fail (PRB_EINVAL, "per-node trace offsets do not match its length");
+    }
   if (kind == PRB_POLICY_TABLE)
     {
       if (!data || n != (int64_t) st.M * st.M) return fail (PRB_EINVAL, "a table policy needs M*M entries");
@@ -549,6 +921,13 @@ prb_set_policy (prb_env *env, int kind, const int32_t *data, int64_t n, uint64_t
   st.policy = kind;
   st.pol_data = env->d_pol;
   st.pol_n = data ? n : 0;
+  env->pol_node_trace = kind == PRB_POLICY_NODE_TRACE;
+  if (env->pol_node_trace)
+    {
+      env->dps.pol_off = env->d_pol;
+      st.pol_data = env->d_pol + (st.M + 1);
+      st.pol_n = n - (st.M + 1);
+    }
   bool reseed = kind == PRB_POLICY_RANDOM || kind == PRB_POLICY_TRACE;
   if (reseed)
     {
@@ -582,7 +961,10 @@ log_counts (prb_env *env, int32_t e, int64_t *ev_n, int64_t *st_n)
 {
   const Static &st = env->dst;
   if (e < 0 || e >= st.E) return fail (PRB_EINVAL, "env index out of range");
-  k_log_counts<<<1, 1, 0, env->stream>>> (st, env->d_blobs, e, env->d_scratch);
+  if (env->engine_active == PRB_ENGINE_PARALLEL)
+    k_log_counts_par<<<1, 1, 0, env->stream>>> (env->dps, env->d_pblobs, e, env->d_scratch);
+  else
+    k_log_counts<<<1, 1, 0, env->stream>>> (st, env->d_blobs, e, env->d_scratch);
   CUDA_TRY (cudaGetLastError ());
   int64_t h[2];
   CUDA_TRY (cudaMemcpyAsync (h, env->d_scratch, 16, cudaMemcpyDeviceToHost, env->stream));
@@ -636,7 +1018,23 @@ prb_run (prb_env *env, int64_t until_ns)
   if (!env) return fail (PRB_EINVAL, "null handle");
   CUDA_TRY (cudaSetDevice (env->device));
   Static &st = env->dst;
+  /* engine: the node-parallel one whenever the agent is a function of the packet alone and nobody asked for
+   * the ordered logs; an episode stays on the engine that started it */
+  bool par_policy = st.policy == PRB_POLICY_ZERO || st.policy == PRB_POLICY_TABLE || st.policy == PRB_POLICY_NODE_TRACE;
+  bool want_par = env->engine_mode == PRB_ENGINE_PARALLEL
+                  || (env->engine_mode == PRB_ENGINE_AUTO && env->pm.supported && par_policy && !env->log_on);
+  if (env->engine_active == PRB_ENGINE_SERIAL) want_par = false;
+  if (env->engine_active == PRB_ENGINE_PARALLEL) want_par = true;
+  if (want_par)
+    {
+      if (!env->pm.supported) return fail (PRB_ESTATE, "the parallel engine does not support this configuration: " + env->pm.why);
+      if (!par_policy) return fail (PRB_ESTATE, "the parallel engine runs table / per-node-trace agents only: prb_reset first");
+      if (env->d_st) return fail (PRB_ESTATE, "the parallel engine keeps no step log");
+      return run_parallel (env, until_ns);
+    }
+  if (st.policy == PRB_POLICY_NODE_TRACE) return fail (PRB_ESTATE, "per-node action traces need the parallel engine");
   st.mode = MODE_RUN;
+  env->engine_active = PRB_ENGINE_SERIAL;
   LaunchArgs a;
   a.blobs = env->d_blobs; a.pools = env->d_pools; a.ev_logs = env->d_ev; a.st_logs = env->d_st;
   a.actions = nullptr; a.out = nullptr; a.until_ns = until_ns;
@@ -649,7 +1047,10 @@ prb_step (prb_env *env, const int32_t *actions_dev, prb_step_rec *out_dev)
   if (!env || !out_dev) return fail (PRB_EINVAL, "null argument");
   CUDA_TRY (cudaSetDevice (env->device));
   Static &st = env->dst;
+  if (env->engine_active == PRB_ENGINE_PARALLEL)
+    return fail (PRB_ESTATE, "this episode runs on the parallel engine (prb_run with a table agent): prb_reset before prb_step");
   st.mode = MODE_GYM;
+  env->engine_active = PRB_ENGINE_SERIAL;
   LaunchArgs a;
   a.blobs = env->d_blobs; a.pools = env->d_pools; a.ev_logs = env->d_ev; a.st_logs = env->d_st;
   a.actions = actions_dev; a.out = out_dev; a.until_ns = st.sim_time_ns;
@@ -677,7 +1078,10 @@ prb_counters_dev (prb_env *env, prb_counters *out_dev)
   if (!env || !out_dev) return fail (PRB_EINVAL, "null argument");
   CUDA_TRY (cudaSetDevice (env->device));
   const Static &st = env->dst;
-  k_counters<<<(st.E + 127) / 128, 128, 0, env->stream>>> (st, env->d_blobs, out_dev);
+  if (env->engine_active == PRB_ENGINE_PARALLEL)
+    k_counters_par<<<(st.E + 127) / 128, 128, 0, env->stream>>> (st, env->dps, env->d_pblobs, out_dev);
+  else
+    k_counters<<<(st.E + 127) / 128, 128, 0, env->stream>>> (st, env->d_blobs, out_dev);
   CUDA_TRY (cudaGetLastError ());
   env->launches++;
   return PRB_OK;
@@ -702,7 +1106,10 @@ prb_queue_bytes (prb_env *env, int32_t e, int32_t *out)
   const Static &st = env->dst;
   if (e < 0 || e >= st.E) return fail (PRB_EINVAL, "env index out of range");
   if (st.L > 1000) return fail (PRB_EINVAL, "too many links for the scratch buffer");
-  k_queue_bytes<<<(st.L + 127) / 128, 128, 0, env->stream>>> (st, env->d_blobs, e, (int32_t *) env->d_scratch);
+  if (env->engine_active == PRB_ENGINE_PARALLEL)
+    k_queue_bytes_par<<<(st.L + 127) / 128, 128, 0, env->stream>>> (st, env->dps, env->d_pblobs, e, (int32_t *) env->d_scratch);
+  else
+    k_queue_bytes<<<(st.L + 127) / 128, 128, 0, env->stream>>> (st, env->d_blobs, e, (int32_t *) env->d_scratch);
   CUDA_TRY (cudaGetLastError ());
   CUDA_TRY (cudaMemcpyAsync (out, env->d_scratch, sizeof (int32_t) * st.L, cudaMemcpyDeviceToHost, env->stream));
   CUDA_TRY (cudaStreamSynchronize (env->stream));

@@ -150,6 +150,23 @@ class BatchedRoutingEnv:
             table = sp_table(self.arrays)
         self.set_policy("table", table)
 
+    def set_engine(self, mode: str = "auto", team: int = 0):
+        """Engine of `run`: "auto" (the node-parallel engine for table / per-node-trace agents without ordered
+        logs, else the event-serial one), "serial" or "parallel"; `team` = lanes per environment (0: auto)."""
+        _abi.check(self.lib.prb_set_engine(self.h, _abi.ENGINE[mode], int(team)))
+
+    @property
+    def engine(self) -> str:
+        """Engine that has advanced the environments since the last reset."""
+        return {0: "none", 1: "serial", 2: "parallel"}[self.lib.prb_engine(self.h)]
+
+    def round_stats(self):
+        """(rounds, events executed) of the node-parallel engine so far: their ratio is the number of events
+        of one environment that ran concurrently."""
+        a, b = C.c_int64(), C.c_int64()
+        _abi.check(self.lib.prb_round_stats(self.h, C.byref(a), C.byref(b)))
+        return a.value, b.value
+
     # ---- stepping ----
     def run(self, until_s: Optional[float] = None, until_ns: Optional[int] = None):
         if until_ns is None:

@@ -1,0 +1,173 @@
+"""The node-parallel engine of prb_run (k_run_par, prisma_b200/csrc/par_core.cuh) on the GPU, through the C
+ABI: against the committed outputs of the reference's ns-3 program, against the CPU restatement, and against
+the event-serial engine at batch sizes.  The engine executes independent events of an environment
+concurrently, so event logs are compared as multisets of complete records; counters, float32 statistics and
+queue occupancies bit for bit."""
+import struct
+
+import numpy as np
+import pytest
+
+from oracle import oracle
+from tests import common, golden_util
+from tests.test_par_host import assert_same_multiset, oracle_uid_map
+
+pytestmark = pytest.mark.gpu
+
+
+def make_env(cfg, **kw):
+    from prisma_b200.env import BatchedRoutingEnv
+    return BatchedRoutingEnv(cfg, **kw)
+
+
+def node_trace(g):
+    from tests.host_harness.host_sim import node_trace as nt
+    return nt(g.dec["node"], g.dec["action"], g.arrays.overlay_to_underlay())
+
+
+@pytest.mark.parametrize("team", [0, 32])
+@pytest.mark.parametrize("name", golden_util.names())
+def test_parallel_engine_replays_reference_golden(name, team):
+    g = golden_util.Golden(name)
+    g.cfg.num_envs = 5
+    env = make_env(g.cfg, arrays=g.arrays)
+    inj, policy, table, seed = common.replay_inputs(g)
+    env.set_inject_trace(*inj)
+    env.set_engine("parallel", team)
+    env.enable_log(2 * len(g.events), 0)
+    env.reset()
+    env.set_policy("node_trace", node_trace(g))
+    env.run()
+    assert env.engine == "parallel"
+    cs = env.counters()
+    assert (cs["errors"] == 0).all()
+    for e in (0, 4):
+        assert_same_multiset(g.events, env.events(e))
+        c = cs[e]
+        for key, v in g.counters.items():
+            assert int(c[key]) == v, key
+        for key, v in g.float_bits.items():
+            assert struct.unpack("I", struct.pack("f", float(c[key])))[0] == v, key
+    env.close()
+
+
+CASES = [
+    ("abilene", dict(simTime=3, load_factor=0.9, pingAsObs=0, activateUnderlayTraffic=1)),
+    ("abilene", dict(simTime=3, load_factor=1.6, max_out_buffer_size=2168, pingAsObs=1, activateUnderlayTraffic=1)),
+    ("overlay_full_mesh_3n_abilene", dict(simTime=8, load_factor=2.5, pingAsObs=1, activateUnderlayTraffic=1, train=1,
+                                          signaling_type="target", agent_type="dqn_buffer", max_out_buffer_size=3000)),
+    ("geant", dict(simTime=1.5, load_factor=1.3, pingAsObs=0, activateUnderlayTraffic=1)),
+]
+
+
+@pytest.mark.parametrize("topo,over", CASES)
+def test_parallel_engine_matches_oracle_synthetic_traffic(topo, over):
+    cfg = common.env_config(topo, num_envs=130, **over)
+    arrays = cfg.load()
+    table = common.sp_table(arrays)
+    env = make_env(cfg, arrays=arrays, env_id_base=1000)
+    env.set_engine("parallel")
+    env.enable_log(400000, 0)
+    env.reset()
+    env.set_policy("table", table)
+    env.run()
+    cs = env.counters()
+    env.check_errors(cs)
+    for e in (0, 37, 129):
+        osim = common.oracle_run(cfg, arrays, oracle, policy="table", table=table, env_id=1000 + e)
+        common.assert_counters_equal(osim.counters(), cs[e])
+        assert np.array_equal(osim.queue_bytes(), env.queue_bytes(e))
+        umap, _ = oracle_uid_map(osim.events(), arrays)
+        assert_same_multiset(osim.events(), env.events(e), umap)
+    rounds, executed = env.round_stats()
+    assert executed > rounds
+    env.close()
+
+
+def test_parallel_and_serial_engines_agree_on_a_batch():
+    """1024 Abilene environments, 2 simulated seconds in two calls: every counter of every environment."""
+    cfg = common.env_config("abilene", num_envs=1024, simTime=2.0, load_factor=0.9, pingAsObs=0, activateUnderlayTraffic=1)
+    arrays = cfg.load()
+    table = common.sp_table(arrays)
+    res = {}
+    for mode in ("serial", "parallel"):
+        env = make_env(cfg, arrays=arrays)
+        env.set_engine(mode)
+        env.set_policy("table", table)
+        env.run(until_s=0.75)
+        env.run()
+        assert env.engine == mode
+        cs = env.counters()
+        env.check_errors(cs)
+        res[mode] = (cs, np.stack([env.queue_bytes(e) for e in (0, 511, 1023)]))
+        env.close()
+    a, b = res["serial"][0], res["parallel"][0]
+    for k in common.COUNTER_INTS:
+        assert np.array_equal(a[k], b[k]), k
+    for k in common.COUNTER_FLOATS:
+        assert np.array_equal(a[k].view(np.uint32), b[k].view(np.uint32)), k
+    assert np.array_equal(res["serial"][1], res["parallel"][1])
+    assert int(a["packet_hops"].sum()) > 3_000_000
+
+
+def test_engine_rules():
+    from prisma_b200 import _abi
+    cfg = common.env_config("abilene", num_envs=8, simTime=0.5, load_factor=0.9, pingAsObs=0, activateUnderlayTraffic=1)
+    arrays = cfg.load()
+    env = make_env(cfg, arrays=arrays)
+    env.set_policy("table", common.sp_table(arrays))
+    env.run(until_s=0.25)
+    assert env.engine == "parallel"                      # auto: table agent, no ordered log
+    with pytest.raises(_abi.PrbError):
+        env.step_host(None)                              # an episode stays on its engine
+    env.reset()
+    assert env.engine == "none"
+    recs = env.step_host(None)
+    assert recs["valid"].all() and env.engine == "serial"
+    env.run()                                            # continues on the serial engine
+    assert env.engine == "serial"
+    env.check_errors()
+    env.reset()
+    env.set_policy("random", seed=3)
+    env.run()
+    assert env.engine == "serial"                        # agents with global state run event by event
+    env.close()
+
+
+def test_drop_heavy_100_nodes_four_nodes_per_lane():
+    """A 100-node random underlay with 4-packet buffers (BASELINE.json configs[4] shape): the parallel engine
+    (4 nodes per lane) and the serial engine give identical counters."""
+    rng = np.random.default_rng(100)
+    n = 100
+    adj = np.zeros((n, n), dtype=np.uint8)
+    for i in range(1, n):
+        j = int(rng.integers(0, i))
+        adj[i, j] = adj[j, i] = 1
+    for _ in range(70):
+        i, j = (int(x) for x in rng.integers(0, n, 2))
+        if i != j:
+            adj[i, j] = adj[j, i] = 1
+    tm = rng.integers(1000, 12000, size=(n, n)).astype(np.uint64)
+    np.fill_diagonal(tm, 0)
+    from prisma_b200.config import EnvConfig
+    cfg = EnvConfig(physical_adjacency_matrix=adj, overlay_adjacency_matrix=adj, map_overlay=np.arange(n),
+                    traffic_matrix_bps=tm, num_envs=16, simTime=1.0, load_factor=1.0, max_out_buffer_size=2168,
+                    pingAsObs=0, activateUnderlayTraffic=1, train=1, signaling_type="target", agent_type="dqn_buffer")
+    arrays = cfg.load()
+    from prisma_b200.env import sp_table
+    table = sp_table(arrays)
+    res = {}
+    for mode in ("serial", "parallel"):
+        env = make_env(cfg, arrays=arrays)
+        env.set_engine(mode)
+        env.set_policy("table", table)
+        env.run()
+        cs = env.counters()
+        env.check_errors(cs)
+        res[mode] = cs
+        env.close()
+    for k in common.COUNTER_INTS:
+        assert np.array_equal(res["serial"][k], res["parallel"][k]), k
+    for k in common.COUNTER_FLOATS:
+        assert np.array_equal(res["serial"][k].view(np.uint32), res["parallel"][k].view(np.uint32)), k
+    assert int(res["parallel"]["overlay_lost"].sum()) > 0
