@@ -114,11 +114,12 @@ def measured_peak_gbs():
         return 6650.0, "fallback (B200_PROFILING.md)"
 
 
-def recorded_traffic(args):
-    """dram bytes per k_advance launch from the committed ncu capture of this exact workload, if any."""
+def recorded_traffic(args, kernel_name):
+    """dram bytes per launch of the dominant kernel from the committed ncu capture of this exact workload."""
     p = os.path.join(ROOT, "profiles", "roofline_traffic.json")
     try:
         j = json.load(open(p))
+        j = j.get(kernel_name, j)
         if j.get("envs") == args.envs and abs(j.get("chunk", -1) - args.chunk) < 1e-12:
             return float(j["dram_bytes_per_launch"])
     except Exception:
@@ -225,7 +226,9 @@ def main():
     ap.add_argument("--impl", default="prisma_b200", choices=["prisma_b200", "reference"])
     ap.add_argument("--envs", type=int, default=4096, help="environments per GPU")
     ap.add_argument("--chunk", type=float, default=1.0, help="simulated seconds per step")
-    ap.add_argument("--lanes", type=int, default=0, help="lanes per environment (0 = library default)")
+    ap.add_argument("--lanes", type=int, default=0, help="serial engine: lanes per environment (0 = library default)")
+    ap.add_argument("--engine", default="auto", choices=["auto", "serial", "parallel"])
+    ap.add_argument("--team", type=int, default=0, help="parallel engine: lanes per environment (0 = from the node count)")
     ap.add_argument("--ref-sim-time", type=float, default=10.0, dest="ref_sim_time")
     ap.add_argument("--cpu-sim-time", type=float, default=30.0, dest="cpu_sim_time")
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -263,6 +266,7 @@ def main():
     kdeg = max(len(x) for x in arrays.overlay_neighbors())
     b_hop = B_HOP_BASE + 4 * (1 + kdeg)
     env = BatchedRoutingEnv(cfg, device=local_rank, arrays=arrays, env_id_base=rank * args.envs, lanes_per_env=args.lanes)
+    env.set_engine(args.engine, args.team)
     env.set_policy("table", table)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
     lib, h = env.lib, env.h
@@ -337,6 +341,7 @@ def main():
     if rank == 0:
         peak, peak_src = measured_peak_gbs()
         # dominant kernel: k_advance, one launch per step; algorithmic bytes of THIS rank's launch
+        kernel_name = "k_run_par" if env.engine == "parallel" else "k_advance"
         my_hops_per_launch = (hops1 - hops0) / K
         kern_s = (sum(step_ms) / K) / 1000.0
         achieved = my_hops_per_launch * b_hop / kern_s / 1e9
@@ -350,10 +355,15 @@ def main():
                         "what": "prb_set_policy(host table) + prb_run + prb_counters_host per step, wall clock"},
                 "gpu_launches": launches,
                 "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                             "traffic": recorded_traffic(args), "peak_source": peak_src, "kernel": "k_advance",
+                             "traffic": recorded_traffic(args, kernel_name), "peak_source": peak_src, "kernel": kernel_name,
                              "bytes_per_packet_hop": b_hop, "packet_hops_per_launch": my_hops_per_launch,
                              "kernel_ms": kern_s * 1000.0,
-                             "note": "event-serial simulator: issue/latency bound, not HBM bound (DESIGN.md)"}}
+                             "note": "discrete-event simulator: issue/latency bound, not HBM bound (DESIGN.md)"}}
+        if env.engine == "parallel":
+            rounds, executed = env.round_stats()
+            line["engine"] = {"name": "node-parallel (k_run_par)", "events_per_round": executed / max(rounds, 1)}
+        else:
+            line["engine"] = {"name": "event-serial (k_advance)"}
         if world == 1 and not args.no_cpu_baseline:
             cores = os.cpu_count() or 1
             hc, sc_, dt, kind = ref_sample(args.cpu_sim_time, cores)

@@ -555,6 +555,7 @@ build_pmodel (const prb_config &c, const HostModel &hm, PModel &pm)
   ps.off_ping_index = o; o += 4 * M;
   ps.off_pol_pos = o; o += 4 * M;
   ps.off_fmin_f = o; o += 4 * N;
+  ps.off_cand = o; o += 4 * N;
   ps.off_head = o; o += 2 * LA;
   ps.off_mid = o; o += 2 * LA;
   ps.off_tail = o; o += 2 * LA;

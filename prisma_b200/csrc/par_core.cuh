@@ -67,15 +67,13 @@ struct POrd
 enum { PK_NONE = 0, PK_RCV = 1, PK_TXC = 2, PK_FLOW = 3, PK_PING = 4 };
 enum { PS_OVERLAY_ARRIVED = 0, PS_UNDERLAY_ARRIVED = 1, PS_OVERLAY_DROP = 2, PS_UNDERLAY_DROP = 3 };
 
-/* packet record inside a link ring — 32 bytes */
+/* packet record inside a link ring — 32 bytes (one sector) */
 struct PRec
 {
   uint64_t w0;       /* same packing as Pkt::w0 */
-  int64_t prev_t;
   uint32_t uid;
   uint32_t aux;
   POrd ord;          /* history of the transmission that carries the packet (tie_before) */
-  uint64_t pad;
 };
 
 struct PStat
@@ -103,7 +101,7 @@ struct PStatic
   const uint16_t *dcode_txc; /* [n_rc*MAX_SZC] rank of tx */
   int32_t dcode_ping, pad1;
   int32_t off_scal, off_t_next, off_t_ping, off_fmin_ts, off_f_ts, off_busy, off_w_ts, off_sring, off_q_bytes, off_f_pos,
-      off_ping_index, off_pol_pos, off_fmin_f, off_head, off_mid, off_tail, off_s_head, off_s_tail, off_fly_szc, off_fly_ord;
+      off_ping_index, off_pol_pos, off_fmin_f, off_head, off_mid, off_tail, off_s_head, off_s_tail, off_fly_szc, off_fly_ord, off_cand;
   int32_t pblob_bytes;
 };
 
@@ -123,7 +121,7 @@ struct PDyn
   int64_t *t_next, *t_ping, *fmin_ts, *f_ts, *busy, *w_ts;
   PStat *sring;
   uint32_t *q_bytes, *f_pos, *ping_index, *pol_pos;
-  int32_t *fmin_f;
+  int32_t *fmin_f, *cand;
   uint16_t *head, *mid, *tail;
   POrd *fly_ord;
   uint8_t *s_head, *s_tail, *fly_szc;
@@ -147,6 +145,7 @@ p_bind_state (const PStatic &ps, char *blob, PDyn &d)
   d.ping_index = (uint32_t *) (blob + ps.off_ping_index);
   d.pol_pos = (uint32_t *) (blob + ps.off_pol_pos);
   d.fmin_f = (int32_t *) (blob + ps.off_fmin_f);
+  d.cand = (int32_t *) (blob + ps.off_cand);
   d.head = (uint16_t *) (blob + ps.off_head);
   d.mid = (uint16_t *) (blob + ps.off_mid);
   d.tail = (uint16_t *) (blob + ps.off_tail);
@@ -236,15 +235,14 @@ ord_compare (const POrd &x, const POrd &y)
       if (cx != cy) return cx < cy ? -1 : 1;    /* the larger distance (smaller code) was scheduled earlier */
       uint32_t m = rx < ry ? rx : ry;
       rx -= m; ry -= m;
+      /* past the sixth entry a history is complete exactly when its root is still known (nothing was shed) */
       if (rx == 0)
         {
-          if (++ix == 6) return 0;
-          ex = ord_entry (x, ix); rx = ex & 127u;
+          ex = ++ix < 6 ? ord_entry (x, ix) : 0u; rx = ex & 127u;
         }
       if (ry == 0)
         {
-          if (++iy == 6) return 0;
-          ey = ord_entry (y, iy); ry = ey & 127u;
+          ey = ++iy < 6 ? ord_entry (y, iy) : 0u; ry = ey & 127u;
         }
     }
 }
@@ -252,10 +250,12 @@ ord_compare (const POrd &x, const POrd &y)
 /* the running event as a parent: when it was scheduled, its history, and its own distance code */
 struct PCtx
 {
-  int64_t sched;
+  int64_t sched;     /* P_SCHED_LAZY: an injection, whose scheduling time is recomputed only if somebody asks */
   POrd ord;
   uint32_t code;
+  int32_t flow;
 };
+constexpr int64_t P_SCHED_LAZY = INT64_MIN + 1;
 
 template <bool LOG>
 struct PSim
@@ -271,12 +271,12 @@ struct PSim
   PRB_HD static void
   to_pkt (const PRec &r, Pkt &p)
   {
-    p.w0 = r.w0; p.prev_t = r.prev_t; p.uid = r.uid; p.aux = r.aux; p.rcv_ts = 0; p.rcv_seq = 0; p.next = NIL; p.pad = 0;
+    p.w0 = r.w0; p.prev_t = 0; p.uid = r.uid; p.aux = r.aux; p.rcv_ts = 0; p.rcv_seq = 0; p.next = NIL; p.pad = 0;
   }
   PRB_HD static void
   to_rec (const Pkt &p, PRec &r)
   {
-    r.w0 = p.w0; r.prev_t = p.prev_t; r.uid = p.uid; r.aux = p.aux; r.ord.a = 0; r.ord.b = 0; r.pad = 0;
+    r.w0 = p.w0; r.uid = p.uid; r.aux = p.aux; r.ord.a = 0; r.ord.b = 0;
   }
 
   PRB_HD void
@@ -306,11 +306,14 @@ struct PSim
 
   /* ---- float statistics: appended here, folded in timestamp order by the team ---- */
   PRB_HD void
-  stat_push (int x, int64_t ts, uint32_t code, float v)
+  stat_push (int x, int64_t ts, int64_t sched, uint32_t code, float v)
   {
     uint8_t t = d.s_tail[x];
     PStat &s = d.sring[x * P_SR + (t & (P_SR - 1))];
-    s.ts = ts; s.code = code; s.v = v;
+    /* code in the top two bits; below, how long before ts the event was scheduled (saturated): records of
+     * different nodes with one timestamp are folded earliest-scheduled first, like the events ran */
+    int64_t dd = sched == P_SCHED_LAZY ? 0 : (sched < 0 ? 0x3FFFFFFF : ts - sched);
+    s.ts = ts; s.code = (code << 30) | (uint32_t) (dd > 0x3FFFFFFF ? 0x3FFFFFFF : dd); s.v = v;
     d.s_tail[x] = (uint8_t) (t + 1);
   }
   PRB_HD int
@@ -320,33 +323,91 @@ struct PSim
   }
 
   PRB_HD void
-  count_drop (int x, int64_t now, bool overlay_side)
+  count_drop (int x, int64_t now, int64_t sched, bool overlay_side)
   {
     if (overlay_side)
+      acc.overlay_lost++;
+    else
+      acc.underlay_lost++;
+    stat_push (x, now, sched, overlay_side ? PS_OVERLAY_DROP : PS_UNDERLAY_DROP, st.loss_penalty);
+  }
+
+  /* One request of the running event to a device of its node: mode 0 = PointToPointNetDevice::Send +
+   * Queue::DoEnqueue, mode 1 = the TransmitComplete of link l starts the packet at the head of its queue
+   * (already in the ring).  cur: the running event; branch: position among the transmissions of a ping
+   * round (0xFFFF: inherit).  There is ONE call site (execute), so one copy in the instruction stream. */
+  PRB_HD void
+  dev_send (int x, int l, int64_t now, const Pkt &p, const PCtx &cur, uint32_t branch, int mode)
+  {
+    int node = st.link_from[l];
+    int data = p_type (p) == PRB_DATA;
+    uint32_t size = st.szc_bytes[p_szc (p)];
+    uint32_t qb = d.q_bytes[l];
+    uint16_t m = d.mid[l], t = d.tail[l];
+    uint16_t mask = ps.ring_mask[l];
+    PRec *slot;
+    bool busy = false;
+    if (mode == 0)
       {
-        acc.overlay_lost++;
-        stat_push (x, now, PS_OVERLAY_DROP, st.loss_penalty);
+        if (PRB_UNLIKELY (data && p_rejected (p) && node < 23))
+          {
+            count_drop (x, now, cur.sched, p_valable (p));
+            return;
+          }
+        if (l >= st.L) log_event (now, PRB_EV_INJ, node, l, p, -1);
+        bool fits = l < st.L ? (qb + size <= st.max_out_buffer) : ((uint32_t) (uint16_t) (t - m) + 1 <= 1000u);
+        if (PRB_UNLIKELY (!fits))
+          {
+            if (l < st.L) log_event (now, PRB_EV_DRP, node, l, p, (int) qb);
+            if (data) count_drop (x, now, cur.sched, p_valable (p) && p_dst (p) != node);
+            return;
+          }
+        if (l < st.L) log_event (now, PRB_EV_ENQ, node, l, p, (int) (qb + size));
+        if (PRB_UNLIKELY ((uint16_t) (t - d.head[l]) > mask))
+          {
+            acc.errors |= PRB_ERR_POOL;
+            return;
+          }
+        /* a TransmitComplete with nothing waiting only marks the device idle: it is not an event here, the
+         * device is READY as soon as the clock reaches busy_until */
+        busy = m != t || d.busy[l] > now;
+        if (PRB_UNLIKELY (!busy && d.busy[l] == now && now != 0)) busy = completes_later (l, now, cur);
+        slot = &d.rings[ps.ring_off[l] + (t & mask)];
+        d.tail[l] = (uint16_t) (t + 1);
+        if (busy)
+          {
+            PRec r;
+            to_rec (p, r);
+            *slot = r;
+            d.q_bytes[l] = qb + size;
+            return;
+          }
       }
     else
       {
-        acc.underlay_lost++;
-        stat_push (x, now, PS_UNDERLAY_DROP, st.loss_penalty);
+        slot = &d.rings[ps.ring_off[l] + (m & mask)];
+        qb -= size;
+        d.q_bytes[l] = qb;
       }
-  }
-
-  /* PointToPointNetDevice::TransmitStart + PointToPointChannel::TransmitStart: the record is already in the
-   * ring at position mid; o is the history shared by the TransmitComplete and the Receive it schedules */
-  PRB_HD void
-  transmit_start (int l, int64_t now, const Pkt &p, const POrd &o)
-  {
-    if (l < st.L) log_event (now, PRB_EV_TXB, st.link_from[l], l, p, (int) d.q_bytes[l]);
+    /* PointToPointNetDevice::TransmitStart + PointToPointChannel::TransmitStart */
+    POrd o = ord_push (cur.ord, cur.code);
+    if (branch != P_NONE16) o.b = (o.b & ~0xFFFFull) | branch;
+    if (mode == 0)
+      {
+        PRec r;
+        to_rec (p, r);
+        r.ord = o;
+        *slot = r;
+      }
+    else
+      slot->ord = o;
+    if (l < st.L) log_event (now, PRB_EV_TXB, node, l, p, (int) qb);
     int szc = p_szc (p);
     int64_t tx = st.tx_ns[st.link_rc[l] * MAX_SZC + szc];
     int64_t delay = l < st.L ? st.link_delay_ns : 0;
     d.busy[l] = now + tx;
     d.fly_szc[l] = (uint8_t) szc;
     d.fly_ord[l] = o;
-    uint16_t m = d.mid[l];
     if ((uint16_t) (m - d.head[l]) >= (uint16_t) ps.W) acc.errors |= PRB_ERR_POOL;
     d.w_ts[l * ps.W + (m & (ps.W - 1))] = now + tx + delay;
     d.mid[l] = (uint16_t) (m + 1);
@@ -361,84 +422,21 @@ struct PSim
     c.sched = ts - st.tx_ns[k];
     c.ord = d.fly_ord[l];
     c.code = ps.dcode_txc[k];
+    c.flow = -1;
     return c;
   }
 
-  /* PointToPointNetDevice::Send + Queue::DoEnqueue, executed by the lane that owns the sending node.
-   * cur: the running event; branch: position among the transmissions of a ping round (or 0xFFFF: inherit) */
-  PRB_HD void
-  dev_send (int x, int l, int64_t now, const Pkt &p, const PCtx &cur, uint32_t branch)
+  /* The device completes in this very nanosecond.  If that TransmitComplete comes after the running event in
+   * scheduler order the device is still BUSY: the packet is queued and the completion, now a real event of
+   * this node at the same timestamp, starts it. */
+  PRB_HDN bool
+  completes_later (int l, int64_t now, const PCtx &cur)
   {
-    int node = st.link_from[l];
-    int data = p_type (p) == PRB_DATA;
-    if (PRB_UNLIKELY (data && p_rejected (p) && node < 23))
-      {
-        count_drop (x, now, p_valable (p));
-        return;
-      }
-    if (l >= st.L) log_event (now, PRB_EV_INJ, node, l, p, -1);
-    uint32_t size = st.szc_bytes[p_szc (p)];
-    uint32_t qb = d.q_bytes[l];
-    uint16_t h = d.head[l], m = d.mid[l], t = d.tail[l];
-    bool fits = l < st.L ? (qb + size <= st.max_out_buffer) : ((uint32_t) (uint16_t) (t - m) + 1 <= 1000u);
-    if (PRB_UNLIKELY (!fits))
-      {
-        if (l < st.L) log_event (now, PRB_EV_DRP, node, l, p, (int) qb);
-        if (data) count_drop (x, now, p_valable (p) && p_dst (p) != node);
-        return;
-      }
-    if (l < st.L) log_event (now, PRB_EV_ENQ, node, l, p, (int) (qb + size));
-    uint16_t mask = ps.ring_mask[l];
-    if (PRB_UNLIKELY ((uint16_t) (t - h) > mask))
-      {
-        acc.errors |= PRB_ERR_POOL;
-        return;
-      }
-    /* a TransmitComplete with nothing waiting only marks the device idle: it is not an event here, the
-     * device is READY as soon as the clock reaches busy_until */
-    bool busy = m != t || d.busy[l] > now;
-    if (PRB_UNLIKELY (!busy && d.busy[l] == now && now != 0))
-      {
-        /* the device completes in this very nanosecond.  If that TransmitComplete comes after the running
-         * event in scheduler order the device is still BUSY: the packet is queued and the completion, now a
-         * real event of this node at the same timestamp, starts it */
-        PCtx tc = txc_ctx (l, now);
-        int r = tc.sched != cur.sched ? (tc.sched < cur.sched ? -1 : 1) : ord_compare (tc.ord, cur.ord);
-        if (r == 0) acc.errors |= PRB_ERR_TIE;
-        if (r >= 0) busy = true;
-      }
-    PRec r;
-    to_rec (p, r);
-    POrd o;
-    o.a = 0; o.b = 0;
-    if (!busy)
-      {
-        o = ord_push (cur.ord, cur.code);
-        if (branch != P_NONE16) o.b = (o.b & ~0xFFFFull) | branch;
-        r.ord = o;
-      }
-    d.rings[ps.ring_off[l] + (t & mask)] = r;
-    d.tail[l] = (uint16_t) (t + 1);
-    if (!busy)
-      transmit_start (l, now, p, o);
-    else
-      d.q_bytes[l] = qb + size;
-  }
-
-  /* PointToPointNetDevice::TransmitComplete with a packet waiting */
-  PRB_HD void
-  transmit_complete (int l, int64_t now)
-  {
-    PCtx cur = txc_ctx (l, now);
-    uint16_t m = d.mid[l];
-    PRec *rp = &d.rings[ps.ring_off[l] + (m & ps.ring_mask[l])];
-    PRec r = *rp;
-    Pkt p;
-    to_pkt (r, p);
-    POrd o = ord_push (cur.ord, cur.code);
-    rp->ord = o;
-    d.q_bytes[l] -= st.szc_bytes[p_szc (p)];
-    transmit_start (l, now, p, o);
+    PCtx tc = txc_ctx (l, now);
+    int64_t cs = cur.sched == P_SCHED_LAZY ? flow_sched_time (cur.flow) : cur.sched;
+    int r = tc.sched != cs ? (tc.sched < cs ? -1 : 1) : ord_compare (tc.ord, cur.ord);
+    if (r == 0) acc.errors |= PRB_ERR_TIE;
+    return r >= 0;
   }
 
   PRB_HD int32_t
@@ -465,6 +463,17 @@ struct PSim
     q.w0 = 0; q.prev_t = 0; q.rcv_ts = 0; q.rcv_seq = 0; q.pad = 0; q.next = NIL; q.uid = 0; q.aux = 0;
   }
 
+  /* a control packet of node x back to node lh (ping echo, small signalling) */
+  PRB_HD static void
+  reply (Pkt &q, int type, int x, int lh, int szc)
+  {
+    blank (q);
+    set_p_type (q, type);
+    set_p_dst (q, lh); set_p_next_hop (q, lh); set_p_last_hop (q, x); set_p_src (q, x); set_p_ipdst (q, lh);
+    set_p_prev_node (q, NODE_NONE);
+    set_p_szc (q, szc);
+  }
+
   PRB_HD PCtx
   rcv_ctx (int l, int64_t ts, const PRec &r) const
   {
@@ -473,160 +482,19 @@ struct PSim
     c.sched = ts - st.tx_ns[k] - (l < st.L ? st.link_delay_ns : 0);
     c.ord = r.ord;
     c.code = ps.dcode_rcv[k];
+    c.flow = -1;
     return c;
   }
 
-  /* PointToPointNetDevice::Receive (+ agent hook, ExecuteActions, IP forward, statistics) */
-  PRB_HD void
-  receive (int x, int l, int64_t now)
-  {
-    uint16_t h = d.head[l];
-    PRec r = d.rings[ps.ring_off[l] + (h & ps.ring_mask[l])];
-    d.head[l] = (uint16_t) (h + 1);
-    Pkt p;
-    to_pkt (r, p);
-    const PCtx cur = rcv_ctx (l, now, r);
-    bool access = l >= st.L;
-    int type = p_type (p);
-    acc.ev_real++;
-    if (PRB_UNLIKELY (type == PRB_DATA && p_rejected (p) && x < 23)) return;
-    log_event (now, access ? PRB_EV_ARR : PRB_EV_RCV, x, l, p, -1);
-    if (!access)
-      {
-        acc.packet_hops++;
-        if (type == PRB_DATA) acc.data_hops++;
-      }
-    int m = st.map_overlay[x];
-    bool notify = false;
-    if (m >= 0)
-      {
-        switch (type)
-          {
-          case PRB_DATA:
-            notify = p_next_hop (p) == x && p_valable (p);
-            break;
-          case PRB_BIG_SIGN:
-            notify = p_src (p) != x && p_dst (p) == x && p_next_hop (p) == x;
-            break;
-          case PRB_SMALL_SIGN:
-            notify = p_dst (p) == x && p_next_hop (p) == x;
-            break;
-          case PRB_PING_FWD:
-            {
-              /* PingForwardPacketManager::sendPingBackPacket */
-              float delay = d2f_ (dsub_ (ns_to_seconds_ (now), dmul_ ((double) p.aux, 0.001)));
-              Pkt q;
-              blank (q);
-              set_p_type (q, PRB_PING_BACK);
-              int lh = p_last_hop (p);
-              set_p_dst (q, lh); set_p_next_hop (q, lh); set_p_last_hop (q, x); set_p_src (q, x); set_p_ipdst (q, lh);
-              set_p_prev_node (q, NODE_NONE);
-              set_p_szc (q, SZC_PING);
-              set_p_tunnel (q, p_tunnel (p));
-              q.uid = p.uid;
-#if defined(__CUDA_ARCH__)
-              q.aux = __float_as_uint (delay);
-#else
-              memcpy (&q.aux, &delay, 4);
-#endif
-              dev_send (x, l ^ 1, now, q, cur, P_NONE16);
-            }
-            break;
-          default:
-            break;   /* PING_BACK: the delay windows only feed observations, which this engine does not build */
-          }
-      }
-    if (notify)
-      {
-        acc.env_steps++;
-        int data = type == PRB_DATA;
-        if (data)
-          {
-            int done = p_dst (p) == x;
-            if (!done) acc.decisions++;
-            if (st.train && p_src (p) != x)
-              {
-                /* DataPacketManager::sendSmallSignalingPacket */
-                Pkt q;
-                blank (q);
-                set_p_type (q, PRB_SMALL_SIGN);
-                int lh = p_last_hop (p);
-                set_p_dst (q, lh); set_p_next_hop (q, lh); set_p_last_hop (q, x); set_p_src (q, x); set_p_ipdst (q, lh);
-                set_p_prev_node (q, NODE_NONE);
-                set_p_szc (q, st.agent_sign_szc[m]);
-                q.uid = p.uid;
-                dev_send (x, l ^ 1, now, q, cur, P_NONE16);
-              }
-            if (!done)
-              {
-                int32_t action = policy_action (m, p);
-                int k = st.agent_k[m];
-                if (action >= 0 && action < k)
-                  {
-                    Pkt q = p;
-                    int nb = st.agent_nbr[m * st.K + action];
-                    set_p_last_hop (q, x); set_p_next_hop (q, nb); set_p_ipdst (q, nb);
-                    set_p_first_hop (q, 0);
-                    set_p_szc (q, SZC_DATA_FWD);
-                    set_p_tracked (q, 1); set_p_prev_node (q, x);
-                    q.prev_t = now;
-                    dev_send (x, st.route[x * st.N + nb], now, q, cur, P_NONE16);
-                  }
-                else
-                  acc.vanished++;
-              }
-          }
-      }
-    /* the IP forward inside m_rxCallback and the statistics after it (point-to-point-net-device.cc:432-463) */
-    int data = type == PRB_DATA;
-    if (p_first_hop (p))
-      {
-      }
-    else if (p_ipdst (p) == x)
-      {
-        if (data && p_last_hop (p) == NODE_NONE && !p_valable (p) && !(p_rejected (p) && st.N + x < 23))
-          acc.underlay_injected++;
-      }
-    else
-      dev_send (x, st.route[x * st.N + p_ipdst (p)], now, p, cur, P_NONE16);
-    if (data && p_dst (p) == x)
-      {
-        float dly = d2f_ (dsub_ (ns_to_seconds_ (now), (double) p.aux));
-        if (p_valable (p))
-          {
-            if (p_next_hop (p) == p_dst (p))
-              {
-                acc.overlay_arrived++;
-                stat_push (x, now, PS_OVERLAY_ARRIVED, dly);
-              }
-          }
-        else
-          {
-            acc.underlay_arrived++;
-            stat_push (x, now, PS_UNDERLAY_ARRIVED, dly);
-          }
-      }
-    if (type > 0 && p_dst (p) == x) acc.bytes_signaling += st.szc_bytes[p_szc (p)] - 2;
-    if (data && p_last_hop (p) == NODE_NONE)
-      {
-        if (p_valable (p))
-          {
-            acc.overlay_injected++;
-            acc.bytes_data += st.szc_bytes[p_szc (p)] - 2;
-          }
-        else
-          acc.underlay_injected++;
-      }
-  }
-
   /* history of the pending firing of ping timer m: idx earlier firings, one ping interval apart */
-  PRB_HD PCtx
+  PRB_HDN PCtx
   ping_ctx (int m, int64_t ts) const
   {
     PCtx c;
     uint32_t n = d.ping_index[m];
     c.sched = n == 0 ? -1 : ts - st.ping_interval_ns;
     c.code = (uint32_t) ps.dcode_ping;
+    c.flow = -1;
     uint32_t e[6] = { 0, 0, 0, 0, 0, 0 };
     uint32_t left = n;
     for (int i = 0; i < 6 && left > 0; i++)
@@ -642,40 +510,15 @@ struct PSim
     return c;
   }
 
-  /* DataPacketManager::sendPingPackets */
-  PRB_HD void
-  ping_timer (int x, int m, int64_t now)
-  {
-    acc.ev_real++;
-    const PCtx cur = ping_ctx (m, now);
-    int k = st.agent_k[m];
-    uint32_t idx = d.ping_index[m];
-    uint32_t ms = (uint32_t) (now / 1000000);
-    d.ping_index[m] = idx + 1;
-    for (int t = 0; t < k; t++)
-      {
-        int nb = st.agent_nbr[m * st.K + t];
-        Pkt q;
-        blank (q);
-        set_p_type (q, PRB_PING_FWD);
-        set_p_dst (q, nb); set_p_next_hop (q, nb); set_p_last_hop (q, x); set_p_src (q, x); set_p_ipdst (q, nb);
-        set_p_prev_node (q, NODE_NONE);
-        set_p_szc (q, SZC_PING);
-        set_p_tunnel (q, t);
-        q.uid = idx; q.aux = ms;
-        dev_send (x, st.route[x * st.N + nb], now, q, cur, (uint32_t) t);
-      }
-    d.t_ping[m] = now + st.ping_interval_ns;
-  }
-
   /* ---- sources ---- */
-  PRB_HD int64_t
+  PRB_HDN int64_t
   philox_gap (int f, uint32_t nd) const
   {
     uint64_t eid = st.env_id_base + (uint64_t) env;
     uint32_t fkey = (uint32_t) (st.flow_src[f] * st.N + st.flow_dst[f]);
     uint32_t r[4];
     philox4x32 ((uint32_t) eid, (uint32_t) (eid >> 32), fkey, nd, (uint32_t) st.seed, (uint32_t) (st.seed >> 32), r);
+    if (nd == 0) return 100000 + (int64_t) dmul_ (u01_53 (r[0], r[1]), 1e9);      /* start offset of the source */
     double u = u01_53 (r[0], r[1]);
     double delay = dmul_ (st.flow_mean_s[f], neglog (u));
     return (int64_t) dmul_ (delay, 1e9);
@@ -695,11 +538,7 @@ struct PSim
     uint32_t nd = d.f_pos[f];
     if (first)
       {
-        uint64_t eid = st.env_id_base + (uint64_t) env;
-        uint32_t fkey = (uint32_t) (st.flow_src[f] * st.N + st.flow_dst[f]);
-        uint32_t r[4];
-        philox4x32 ((uint32_t) eid, (uint32_t) (eid >> 32), fkey, 0u, (uint32_t) st.seed, (uint32_t) (st.seed >> 32), r);
-        base = 100000 + (int64_t) dmul_ (u01_53 (r[0], r[1]), 1e9);
+        base = philox_gap (f, 0u);
         nd = 1;
       }
     d.f_pos[f] = nd + 1;
@@ -721,14 +560,17 @@ struct PSim
     return d.f_ts[f] - philox_gap (f, nd);
   }
 
+  /* the running / pending injection of flow f as a parent; prev: time of the flow's previous injection */
   PRB_HD PCtx
-  flow_ctx (int f) const
+  flow_ctx (int f, int64_t prev) const
   {
     PCtx c;
-    c.sched = flow_sched_time (f);
+    bool first = st.inject_mode == PRB_INJECT_TRACE ? ps.tr_prev[(int32_t) d.f_pos[f]] < 0 : d.f_pos[f] <= 2u;
+    c.sched = first ? -1 : prev;
     c.code = P_CODE_FLOW;
-    c.ord = ord_empty (c.sched < 0 ? (uint32_t) (st.M + f) : P_NONE16, P_NONE16);
-    if (c.sched >= 0) c.ord.a = (uint64_t) ((P_CODE_FLOW << 7) | 1u) << 48;
+    c.flow = f;
+    c.ord = ord_empty (first ? (uint32_t) (st.M + f) : P_NONE16, P_NONE16);
+    if (!first) c.ord.a = (uint64_t) ((P_CODE_FLOW << 7) | 1u) << 48;
     return c;
   }
 
@@ -746,61 +588,18 @@ struct PSim
             bt = t; bf = f;
           }
         else if (PRB_UNLIKELY (t == bt && t != P_FAR))
-          {
-            int64_t a = flow_sched_time (bf), b = flow_sched_time (f);
-            if (a == b && a >= 0) acc.errors |= PRB_ERR_TIE;
-            if (b < a) bf = f;      /* same setup time (-1): creation order, i.e. the lower index stays */
-          }
+          bf = flow_tie (bf, f);
       }
     d.fmin_ts[x] = bt;
     d.fmin_f[x] = bf;
   }
 
-  /* PoissonGeneratorApplication::SendPacket */
-  PRB_HD void
-  inject (int x, int f, int64_t now)
+  PRB_HDN int
+  flow_tie (int bf, int f)
   {
-    acc.ev_real++;
-    const PCtx cur = flow_ctx (f);
-    int src = st.flow_src[f], dst = st.flow_dst[f];
-    Pkt p;
-    blank (p);
-    set_p_type (p, PRB_DATA);
-    set_p_dst (p, dst); set_p_src (p, src); set_p_next_hop (p, src); set_p_last_hop (p, NODE_NONE);
-    set_p_prev_node (p, NODE_NONE);
-    set_p_szc (p, SZC_DATA_INJ);
-    p.aux = (uint32_t) (uint64_t) ns_to_seconds_ (now);
-    int both = st.map_overlay[src] >= 0 && st.map_overlay[dst] >= 0;
-    if (st.inject_mode == PRB_INJECT_TRACE)
-      {
-        int32_t i = (int32_t) d.f_pos[f];
-        p.uid = st.tr_uid[i];
-        set_p_valable (p, st.tr_flags[i] & 1);
-        set_p_rejected (p, (st.tr_flags[i] >> 1) & 1);
-      }
-    else
-      {
-        /* packet uids of synthetic traffic: (ordinal of the packet inside its flow) * F + flow */
-        p.uid = (d.f_pos[f] - 1) * (uint32_t) st.F + (uint32_t) f;
-        set_p_valable (p, both ? 1 : 0);
-        double prej = (st.opt_agent && st.opt_rejected) ? st.opt_rejected[src * st.N + dst] : 0.0;
-        int rej = 0;
-        if (prej > 0.0)
-          {
-            uint64_t eid = st.env_id_base + (uint64_t) env;
-            uint32_t r[4];
-            philox4x32 ((uint32_t) eid, (uint32_t) (eid >> 32), (uint32_t) (src * st.N + dst), d.f_pos[f] - 1,
-                        (uint32_t) st.seed, (uint32_t) (st.seed >> 32), r);
-            double u = dmul_ (dadd_ ((double) r[2], 0.5), 1.0 / 4294967296.0);
-            rej = u < prej ? 1 : 0;
-          }
-        set_p_rejected (p, rej);
-      }
-    set_p_first_hop (p, p_valable (p));
-    set_p_ipdst (p, dst);
-    dev_send (x, st.L + src, now, p, cur, P_NONE16);
-    schedule_flow (f, false, now);
-    rescan_flows (x);
+    int64_t a = flow_sched_time (bf), b = flow_sched_time (f);
+    if (a == b && a >= 0) acc.errors |= PRB_ERR_TIE;
+    return b < a ? f : bf;       /* same setup time (-1): creation order, i.e. the lower index stays */
   }
 
   /* ---- order of two simultaneous events of one node ---- */
@@ -814,7 +613,7 @@ struct PSim
       case PK_TXC:
         return txc_ctx (c.idx, c.ts);
       case PK_FLOW:
-        return flow_ctx (c.idx);
+        return flow_ctx (c.idx, flow_sched_time (c.idx));
       default:
         return ping_ctx (c.idx, c.ts);
       }
@@ -872,25 +671,21 @@ struct PSim
     PCand b;
     b.ts = P_FAR; b.kind = PK_NONE; b.idx = -1;
     const int W = ps.W;
-    for (int j = 0; j < ps.DEG; j++)
+    const int la = st.L + x;
+    /* the links that end at x (the access link last), then the ones that start at x */
+    for (int j = 0; j <= ps.DEG; j++)
       {
-        int l = ps.in_links[x * ps.DEG + j];
-        if (l < 0) break;
+        int l = j < ps.DEG ? ps.in_links[x * ps.DEG + j] : la;
+        if (l < 0) continue;
         uint16_t h = d.head[l];
         if (h != d.mid[l]) offer (b, d.w_ts[l * W + (h & (W - 1))], PK_RCV, l);
       }
-    for (int j = 0; j < ps.DEG; j++)
+    for (int j = 0; j <= ps.DEG; j++)
       {
-        int l = ps.out_links[x * ps.DEG + j];
-        if (l < 0) break;
+        int l = j < ps.DEG ? ps.out_links[x * ps.DEG + j] : la;
+        if (l < 0) continue;
         if (d.mid[l] != d.tail[l]) offer (b, d.busy[l], PK_TXC, l);
       }
-    {
-      int l = st.L + x;
-      uint16_t h = d.head[l], m = d.mid[l];
-      if (m != d.tail[l]) offer (b, d.busy[l], PK_TXC, l);
-      if (h != m) offer (b, d.w_ts[l * W + (h & (W - 1))], PK_RCV, l);
-    }
     int m = st.map_overlay[x];
     if (m >= 0) offer (b, d.t_ping[m], PK_PING, m);
     if (d.fmin_f[x] >= 0) offer (b, d.fmin_ts[x], PK_FLOW, d.fmin_f[x]);
@@ -926,21 +721,229 @@ struct PSim
     return true;
   }
 
+  /* Executes event c of node x.  Staged so that lanes running different kinds of events share the expensive
+   * steps: (A) the ring record of a Receive or of a TransmitComplete is fetched by one load, (B) the kind's
+   * own logic decides what is sent, (C) one loop hands the requests to the devices. */
   PRB_HD void
   execute (int x, const PCand &c)
   {
-    switch (c.kind)
+    const int64_t now = c.ts;
+    const int kind = c.kind;
+    int l = c.idx;
+    /* (A) */
+    PRec r;
+    r.w0 = 0; r.uid = 0; r.aux = 0; r.ord.a = 0; r.ord.b = 0;
+    if (kind == PK_RCV || kind == PK_TXC)
       {
-      case PK_RCV: receive (x, c.idx, c.ts); break;
-      case PK_TXC: transmit_complete (c.idx, c.ts); break;
-      case PK_FLOW: inject (x, c.idx, c.ts); break;
-      case PK_PING: ping_timer (x, c.idx, c.ts); break;
-      default: break;
+        uint16_t i = kind == PK_RCV ? d.head[l] : d.mid[l];
+        r = d.rings[ps.ring_off[l] + (i & ps.ring_mask[l])];
+        if (kind == PK_RCV) d.head[l] = (uint16_t) (i + 1);
+      }
+    Pkt p;
+    to_pkt (r, p);
+    /* (B) */
+    PCtx cur;
+    Pkt s0 = p, s1 = p;
+    int l0 = 0, l1 = 0, ns = 0, mode = 0;
+    if (kind == PK_RCV)
+      {
+        /* PointToPointNetDevice::Receive (+ agent hook, ExecuteActions, IP forward, statistics) */
+        cur = rcv_ctx (l, now, r);
+        bool access = l >= st.L;
+        int type = p_type (p);
+        acc.ev_real++;
+        if (PRB_UNLIKELY (type == PRB_DATA && p_rejected (p) && x < 23)) return;
+        log_event (now, access ? PRB_EV_ARR : PRB_EV_RCV, x, l, p, -1);
+        if (!access)
+          {
+            acc.packet_hops++;
+            if (type == PRB_DATA) acc.data_hops++;
+          }
+        int m = st.map_overlay[x];
+        int data = type == PRB_DATA;
+        if (m >= 0)
+          {
+            bool mine = p_next_hop (p) == x;
+            if (type == PRB_PING_FWD)
+              {
+                /* PingForwardPacketManager::sendPingBackPacket */
+                float delay = d2f_ (dsub_ (ns_to_seconds_ (now), dmul_ ((double) p.aux, 0.001)));
+                reply (s0, PRB_PING_BACK, x, p_last_hop (p), SZC_PING);
+                set_p_tunnel (s0, p_tunnel (p));
+                s0.uid = p.uid;
+#if defined(__CUDA_ARCH__)
+                s0.aux = __float_as_uint (delay);
+#else
+                memcpy (&s0.aux, &delay, 4);
+#endif
+                l0 = l ^ 1; ns = 1;
+              }
+            else if (data ? (mine && p_valable (p)) : (type != PRB_PING_BACK && mine && p_dst (p) == x && (type == PRB_SMALL_SIGN || p_src (p) != x)))
+              {
+                /* a valid Notify(): one Gym step of overlay node m */
+                acc.env_steps++;
+                if (data)
+                  {
+                    int done = p_dst (p) == x;
+                    if (st.train && p_src (p) != x)
+                      {
+                        /* DataPacketManager::sendSmallSignalingPacket */
+                        reply (s0, PRB_SMALL_SIGN, x, p_last_hop (p), st.agent_sign_szc[m]);
+                        s0.uid = p.uid;
+                        l0 = l ^ 1; ns = 1;
+                      }
+                    if (!done)
+                      {
+                        acc.decisions++;
+                        int32_t action = policy_action (m, p);
+                        if (action >= 0 && action < (int) st.agent_k[m])
+                          {
+                            Pkt q = p;
+                            int nb = st.agent_nbr[m * st.K + action];
+                            set_p_last_hop (q, x); set_p_next_hop (q, nb); set_p_ipdst (q, nb);
+                            set_p_first_hop (q, 0);
+                            set_p_szc (q, SZC_DATA_FWD);
+                            set_p_tracked (q, 1); set_p_prev_node (q, x);
+                            int lq = st.route[x * st.N + nb];
+                            if (ns == 0) { s0 = q; l0 = lq; } else { s1 = q; l1 = lq; }
+                            ns++;
+                          }
+                        else
+                          acc.vanished++;
+                      }
+                  }
+              }
+          }
+        /* the IP forward inside m_rxCallback and the statistics after it (point-to-point-net-device.cc:432-463) */
+        if (p_first_hop (p))
+          {
+          }
+        else if (p_ipdst (p) == x)
+          {
+            if (data && p_last_hop (p) == NODE_NONE && !p_valable (p) && !(p_rejected (p) && st.N + x < 23))
+              acc.underlay_injected++;
+          }
+        else
+          {
+            int lq = st.route[x * st.N + p_ipdst (p)];
+            if (ns == 0) { s0 = p; l0 = lq; } else { s1 = p; l1 = lq; }
+            ns++;
+          }
+        if (data && p_dst (p) == x)
+          {
+            float dly = d2f_ (dsub_ (ns_to_seconds_ (now), (double) p.aux));
+            if (p_valable (p))
+              {
+                if (p_next_hop (p) == p_dst (p))
+                  {
+                    acc.overlay_arrived++;
+                    stat_push (x, now, cur.sched, PS_OVERLAY_ARRIVED, dly);
+                  }
+              }
+            else
+              {
+                acc.underlay_arrived++;
+                stat_push (x, now, cur.sched, PS_UNDERLAY_ARRIVED, dly);
+              }
+          }
+        if (type > 0 && p_dst (p) == x) acc.bytes_signaling += st.szc_bytes[p_szc (p)] - 2;
+        if (data && p_last_hop (p) == NODE_NONE)
+          {
+            if (p_valable (p))
+              {
+                acc.overlay_injected++;
+                acc.bytes_data += st.szc_bytes[p_szc (p)] - 2;
+              }
+            else
+              acc.underlay_injected++;
+          }
+      }
+    else if (kind == PK_TXC)
+      {
+        /* PointToPointNetDevice::TransmitComplete with a packet waiting */
+        cur = txc_ctx (l, now);
+        l0 = l; ns = 1; mode = 1;
+      }
+    else if (kind == PK_FLOW)
+      {
+        /* PoissonGeneratorApplication::SendPacket */
+        const int f = c.idx;
+        acc.ev_real++;
+        cur = flow_ctx (f, P_SCHED_LAZY);
+        int src = st.flow_src[f], dst = st.flow_dst[f];
+        blank (s0);
+        set_p_type (s0, PRB_DATA);
+        set_p_dst (s0, dst); set_p_src (s0, src); set_p_next_hop (s0, src); set_p_last_hop (s0, NODE_NONE);
+        set_p_prev_node (s0, NODE_NONE);
+        set_p_szc (s0, SZC_DATA_INJ);
+        s0.aux = (uint32_t) (uint64_t) ns_to_seconds_ (now);
+        if (st.inject_mode == PRB_INJECT_TRACE)
+          {
+            int32_t i = (int32_t) d.f_pos[f];
+            s0.uid = st.tr_uid[i];
+            set_p_valable (s0, st.tr_flags[i] & 1);
+            set_p_rejected (s0, (st.tr_flags[i] >> 1) & 1);
+          }
+        else
+          {
+            /* packet uids of synthetic traffic: (ordinal of the packet inside its flow) * F + flow */
+            s0.uid = (d.f_pos[f] - 1) * (uint32_t) st.F + (uint32_t) f;
+            set_p_valable (s0, st.map_overlay[src] >= 0 && st.map_overlay[dst] >= 0 ? 1 : 0);
+            if (PRB_UNLIKELY (st.opt_agent && st.opt_rejected && st.opt_rejected[src * st.N + dst] > 0.0))
+              set_p_rejected (s0, draw_rejected (f, src, dst));
+          }
+        set_p_first_hop (s0, p_valable (s0));
+        set_p_ipdst (s0, dst);
+        l0 = st.L + src; ns = 1;
+        schedule_flow (f, false, now);
+        rescan_flows (x);
+      }
+    else
+      {
+        /* DataPacketManager::sendPingPackets: one ping per tunnel, built in the send loop */
+        const int m = c.idx;
+        acc.ev_real++;
+        cur = ping_ctx (m, now);
+        ns = st.agent_k[m];
+      }
+    /* (C) */
+    for (int i = 0; i < ns; i++)
+      {
+        uint32_t branch = P_NONE16;
+        int li = i == 0 ? l0 : l1;
+        Pkt q = i == 0 ? s0 : s1;
+        if (kind == PK_PING)
+          {
+            const int m = c.idx;
+            int nb = st.agent_nbr[m * st.K + i];
+            reply (q, PRB_PING_FWD, x, nb, SZC_PING);
+            set_p_tunnel (q, i);
+            q.uid = d.ping_index[m]; q.aux = (uint32_t) (now / 1000000);
+            li = st.route[x * st.N + nb];
+            branch = (uint32_t) i;
+          }
+        dev_send (x, li, now, q, cur, branch, mode);
+      }
+    if (kind == PK_PING)
+      {
+        d.ping_index[c.idx] += 1;
+        d.t_ping[c.idx] = now + st.ping_interval_ns;
       }
   }
 
+  PRB_HDN int
+  draw_rejected (int f, int src, int dst) const
+  {
+    uint64_t eid = st.env_id_base + (uint64_t) env;
+    uint32_t r[4];
+    philox4x32 ((uint32_t) eid, (uint32_t) (eid >> 32), (uint32_t) (src * st.N + dst), d.f_pos[f] - 1,
+                (uint32_t) st.seed, (uint32_t) (st.seed >> 32), r);
+    double u = dmul_ (dadd_ ((double) r[2], 0.5), 1.0 / 4294967296.0);
+    return u < st.opt_rejected[src * st.N + dst] ? 1 : 0;
+  }
+
   /* what sim.cc schedules before Simulator::Run, for the nodes of this lane */
-  PRB_HD void
+  PRB_HDN void
   start_node (int x)
   {
     int m = st.map_overlay[x];
@@ -954,7 +957,7 @@ struct PSim
 PRB_HD void
 p_apply_stat (prb_counters &c, const PStat &s)
 {
-  switch (s.code)
+  switch (s.code >> 30)
     {
     case PS_OVERLAY_ARRIVED:
       c.sum_cost = fadd_ (c.sum_cost, s.v); c.n_cost++;

@@ -214,7 +214,7 @@ struct ParArgs
 };
 
 template <int T, bool LOG, bool SMEM>
-__global__ void __launch_bounds__ (128)
+__global__ void __launch_bounds__ (128, 4)
 k_run_par (const __grid_constant__ Static st, const __grid_constant__ PStatic ps, const ParArgs a)
 {
   extern __shared__ __align__ (16) char smem[];
@@ -273,6 +273,13 @@ k_run_par (const __grid_constant__ Static st, const __grid_constant__ PStatic ps
         uint32_t m = __reduce_min_sync (tmask, rel);
         if (m == 0xFFFFFFFFu) break;
         unsigned b = __ballot_sync (tmask, rel == m);
+        if (b & (b - 1))
+          {
+            /* one timestamp on several lanes: the record whose event was scheduled earliest */
+            uint32_t inv = rel == m ? 0x3FFFFFFFu - (d.sring[fx * P_SR + (d.s_head[fx] & (P_SR - 1))].code & 0x3FFFFFFFu) : 0xFFFFFFFFu;
+            uint32_t mi = __reduce_min_sync (tmask, inv);
+            b = __ballot_sync (tmask, inv == mi);
+          }
         if (lane == __ffs (b) - 1)
           {
             p_apply_stat (sc->c, d.sring[fx * P_SR + (d.s_head[fx] & (P_SR - 1))]);
@@ -285,31 +292,31 @@ k_run_par (const __grid_constant__ Static st, const __grid_constant__ PStatic ps
   while (!finished)
     {
       /* phase 1: earliest pending event of my nodes */
-      PCand c0;
-      c0.ts = P_FAR; c0.kind = PK_NONE; c0.idx = -1;
       int64_t mt = P_FAR;
       bool mine_in_time = false;
-      for (int x = gl, i = 0; x < N; x += T, i++)
+      for (int x = gl; x < N; x += T)
         {
           PCand c = sim.select (x);
           d.t_next[x] = c.ts;
-          if (i == 0) c0 = c;
+          d.cand[x] = (c.kind << 24) | (c.idx & 0xFFFFFF);
           mt = c.ts < mt ? c.ts : mt;
           mine_in_time = mine_in_time || sim.in_time (c, until);
         }
       __syncwarp (tmask);
-      if (!__any_sync (tmask, mine_in_time)) break;
+      const bool more = __any_sync (tmask, mine_in_time);
       uint64_t off = (uint64_t) (mt - base);
       uint32_t rel = mt == P_FAR || off > 0xFFFFFFFEull ? 0xFFFFFFFEu : (uint32_t) off;
       const int64_t gmin = base + (int64_t) __reduce_min_sync (tmask, rel);
-      fold (gmin);
+      fold (more ? gmin : P_FAR);           /* at the end of the run everything that is left */
+      if (!more) break;
       /* phase 2: the earliest of my events that nothing can precede any more */
       PCand my;
       my.ts = P_FAR; my.kind = PK_NONE; my.idx = -1;
       int myx = -1;
-      for (int x = gl, i = 0; x < N; x += T, i++)
+      for (int x = gl; x < N; x += T)
         {
-          PCand c = i == 0 ? c0 : sim.select (x);
+          PCand c;
+          c.ts = d.t_next[x]; c.kind = d.cand[x] >> 24; c.idx = d.cand[x] & 0xFFFFFF;
           if (c.ts < my.ts && sim.safe (x, c, gmin, until))
             {
               my = c; myx = x;
@@ -329,7 +336,6 @@ k_run_par (const __grid_constant__ Static st, const __grid_constant__ PStatic ps
   __syncwarp (tmask);
   if (!finished)
     {
-      fold (P_FAR);
       p_flush_acc (sc, acc);
       __syncwarp (tmask);
       if (gl == 0)
@@ -462,7 +468,7 @@ struct prb_env
   int device = 0;
   cudaStream_t stream = nullptr;
   int G = 32;
-  int max_smem = 0;
+  int max_smem = 0, smem_per_sm = 0;
   char *d_tables = nullptr;   /* one allocation for all read-only tables */
   char *d_blob0 = nullptr;
   char *d_blobs = nullptr;
@@ -587,18 +593,36 @@ launch_par_t (prb_env *env, const ParArgs &a)
 {
   const Static &st = env->dst;
   const PStatic &ps = env->dps;
-  const int threads = 128;
-  const int teams = threads / T;
-  const int blocks = (st.E + teams - 1) / teams;
-  size_t smem = (size_t) teams * ps.pblob_bytes;
-  if (smem + 1024 <= (size_t) env->max_smem)
+  /* block size: the one that keeps the most environments resident per SM (shared memory holds the state
+   * of every team of a block; 1 KB per block is reserved by the system) */
+  int threads = 0, best = -1;
+  for (int t = 128; t >= 32 && t >= T; t >>= 1)
     {
+      int teams = t / T;
+      size_t per_block = (size_t) teams * ps.pblob_bytes + 1024;
+      if (per_block > (size_t) env->max_smem) continue;
+      int blocks_sm = (int) std::min<size_t> ((size_t) env->smem_per_sm / per_block, 32);
+      blocks_sm = std::min (blocks_sm, 65536 / (128 * t));      /* 128 registers per thread */
+      int resident = blocks_sm * teams;
+      if (resident > best)
+        {
+          best = resident; threads = t;
+        }
+    }
+  if (threads > 0)
+    {
+      const int teams = threads / T;
+      const int blocks = (st.E + teams - 1) / teams;
+      size_t smem = (size_t) teams * ps.pblob_bytes;
       auto k = k_run_par<T, LOG, true>;
       CUDA_TRY (cudaFuncSetAttribute (k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
       k<<<blocks, threads, smem, env->stream>>> (st, ps, a);
     }
   else
-    k_run_par<T, LOG, false><<<blocks, threads, 0, env->stream>>> (st, ps, a);
+    {
+      const int teams = 128 / T;
+      k_run_par<T, LOG, false><<<(st.E + teams - 1) / teams, 128, 0, env->stream>>> (st, ps, a);
+    }
   CUDA_TRY (cudaGetLastError ());
   env->launches++;
   return PRB_OK;
@@ -744,6 +768,7 @@ prb_create (const prb_config *cfg, int device, void *cuda_stream, prb_env **out)
   auto guard = [&] (int r) { if (r != PRB_OK) { prb_destroy (env); } return r; };
   if (cudaSetDevice (device) != cudaSuccess) return guard (fail (PRB_ECUDA, "cudaSetDevice failed"));
   cudaDeviceGetAttribute (&env->max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, device);
+  cudaDeviceGetAttribute (&env->smem_per_sm, cudaDevAttrMaxSharedMemoryPerMultiprocessor, device);
   if ((rc = upload_tables (env)) != PRB_OK) return guard (rc);
   build_pmodel (*cfg, env->hm, env->pm);      /* pm.supported says whether prb_run may use the parallel engine */
   env->team = env->hm.st.N <= 8 ? 8 : (env->hm.st.N <= 16 ? 16 : 32);

@@ -172,16 +172,30 @@ hp_run_t (hp_sim *s, int64_t until_ns)
       {
         int bx = -1, bl = 0;
         int64_t bt = P_FAR;
-        for (int x = 0; x < N; x++)
-          if (d.s_head[x] != d.s_tail[x])
-            {
-              int64_t ts = d.sring[x * P_SR + (d.s_head[x] & (P_SR - 1))].ts;
-              /* same timestamp on several lanes: the lowest lane; inside a lane the lane's own minimum */
-              if (ts < bound && (ts < bt || (ts == bt && (x % T) < bl)))
+        uint32_t bd = 0;
+        /* every lane offers the oldest record of its nodes (first node wins inside a lane); same timestamp
+         * on several lanes: the one that was scheduled earliest, then the lowest lane */
+        for (int g = 0; g < T; g++)
+          {
+            int lx = -1;
+            int64_t lt = P_FAR;
+            for (int x = g; x < N; x += T)
+              if (d.s_head[x] != d.s_tail[x])
                 {
-                  bt = ts; bx = x; bl = x % T;
+                  int64_t ts = d.sring[x * P_SR + (d.s_head[x] & (P_SR - 1))].ts;
+                  if (ts < bound && ts < lt)
+                    {
+                      lt = ts; lx = x;
+                    }
                 }
-            }
+            if (lx < 0) continue;
+            uint32_t dd = d.sring[lx * P_SR + (d.s_head[lx] & (P_SR - 1))].code & 0x3FFFFFFFu;
+            if (lt < bt || (lt == bt && dd > bd))
+              {
+                bt = lt; bx = lx; bl = g; bd = dd;
+              }
+          }
+        (void) bl;
         if (bx < 0) break;
         p_apply_stat (sc->c, d.sring[bx * P_SR + (d.s_head[bx] & (P_SR - 1))]);
         d.s_head[bx]++;
