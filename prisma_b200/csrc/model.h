@@ -454,6 +454,18 @@ build_pmodel (const prb_config &c, const HostModel &hm, PModel &pm)
       return false;
     }
   ps.la_ns = st.link_delay_ns + tx_min;
+  /* times inside a launch are 32-bit offsets from its start: the launch may cover 2^32 ns minus the longest
+   * transmission + delay that can be scheduled from inside it */
+  int64_t tx_max = 0;
+  for (size_t i = 0; i < hm.tx_ns.size (); i++) tx_max = std::max (tx_max, hm.tx_ns[i]);
+  int64_t reach = tx_max + st.link_delay_ns;
+  if (reach > 1000000000ll || ps.la_ns > 1000000000ll)
+    {
+      pm.why = "a transmission takes longer than a second";
+      return false;
+    }
+  ps.la32 = (uint32_t) ps.la_ns;
+  ps.max_chunk_ns = 4294967295ll - 2 * reach - 2 * ps.la_ns - 16;
   /* packets between TransmitStart and the peer's Receive, as seen by a sender that runs up to one lookahead
    * ahead of the receiver: 3 + 2*delay/tx_min */
   int64_t w = 3 + (2 * st.link_delay_ns + tx_min - 1) / tx_min;
@@ -542,14 +554,14 @@ build_pmodel (const prb_config &c, const HostModel &hm, PModel &pm)
   /* state layout */
   int32_t o = 0;
   ps.off_scal = o; o += align_up ((int32_t) sizeof (PScal), 8);
-  ps.off_t_next = o; o += 8 * N;
   ps.off_t_ping = o; o += 8 * M;
-  ps.off_fmin_ts = o; o += 8 * N;
   ps.off_f_ts = o; o += 8 * std::max (F, 1);
-  ps.off_busy = o; o += 8 * LA;
-  ps.off_w_ts = o; o += 8 * LA * ps.W;
-  ps.off_sring = o; o += (int32_t) sizeof (PStat) * N * P_SR;
   ps.off_fly_ord = o; o += (int32_t) sizeof (POrd) * LA;
+  ps.off_t_next = o; o += 4 * N;
+  ps.off_fmin_ts = o; o += 4 * N;
+  ps.off_busy = o; o += 4 * LA;
+  ps.off_w_ts = o; o += 4 * LA * ps.W;
+  ps.off_sring = o; o += (int32_t) sizeof (PStat) * N * P_SR;
   ps.off_q_bytes = o; o += 4 * LA;
   ps.off_f_pos = o; o += 4 * std::max (F, 1);
   ps.off_ping_index = o; o += 4 * M;
@@ -568,8 +580,8 @@ build_pmodel (const prb_config &c, const HostModel &hm, PModel &pm)
   p_bind_state (ps, pm.pblob0.data (), d);
   for (int x = 0; x < N; x++)
     {
-      d.t_next[x] = P_FAR;
-      d.fmin_ts[x] = P_FAR;
+      d.t_next[x] = P_FAR32;
+      d.fmin_ts[x] = P_FAR32;
       d.fmin_f[x] = -1;
     }
   for (int m = 0; m < M; m++) d.t_ping[m] = P_FAR;

@@ -46,6 +46,7 @@ namespace prb {
 
 constexpr int P_SR = 8;                  /* statistics-ring records per node */
 constexpr int64_t P_FAR = INT64_MAX;
+constexpr uint32_t P_FAR32 = 0xFFFFFFFFu;   /* no event: times inside a run are 32-bit offsets from PScal::base */
 constexpr uint32_t P_NONE16 = 0xFFFFu;
 constexpr uint32_t P_CODE_FLOW = 510;      /* scheduled by a source: the distance to its parent is arbitrary */
 
@@ -78,7 +79,7 @@ struct PRec
 
 struct PStat
 {
-  int64_t ts;
+  uint32_t ts;       /* offset from PScal::base */
   uint32_t code;
   float v;
 };
@@ -88,8 +89,9 @@ struct PStatic
   int32_t W;                 /* wire-ring slots per link (power of two) */
   int32_t DEG;               /* row length of in_links / out_links */
   int32_t ring_records;      /* PRec per environment */
-  int32_t pad0;
+  uint32_t la32;             /* la_ns as a 32-bit offset */
   int64_t la_ns;             /* smallest (tx + delay) of a switch<->switch link */
+  int64_t max_chunk_ns;      /* longest stretch of simulated time one launch may cover (32-bit offsets) */
   const int16_t *in_links;   /* [N*DEG] switch links that end at x, -1 padded */
   const int16_t *out_links;  /* [N*DEG] switch links that start at x, -1 padded */
   const int32_t *ring_off;   /* [LA] first record of the ring of link l */
@@ -108,6 +110,7 @@ struct PStatic
 struct PScal
 {
   int64_t front_ts;          /* every event with ts < front_ts has executed */
+  int64_t base;              /* absolute time of offset 0 of the 32-bit times in this blob */
   int64_t ev_n;
   int64_t tx_started;        /* TransmitStart calls so far (each schedules one TransmitComplete) */
   int64_t ev_real;           /* Receive / injection / ping-timer events executed */
@@ -118,7 +121,8 @@ struct PScal
 struct PDyn
 {
   PScal *sc;
-  int64_t *t_next, *t_ping, *fmin_ts, *f_ts, *busy, *w_ts;
+  int64_t *t_ping, *f_ts;                   /* absolute ns */
+  uint32_t *t_next, *fmin_ts, *busy, *w_ts;   /* offsets from sc->base; busy: offset + 1, 0 = idle since before base */
   PStat *sring;
   uint32_t *q_bytes, *f_pos, *ping_index, *pol_pos;
   int32_t *fmin_f, *cand;
@@ -133,12 +137,12 @@ PRB_HD void
 p_bind_state (const PStatic &ps, char *blob, PDyn &d)
 {
   d.sc = (PScal *) (blob + ps.off_scal);
-  d.t_next = (int64_t *) (blob + ps.off_t_next);
+  d.t_next = (uint32_t *) (blob + ps.off_t_next);
   d.t_ping = (int64_t *) (blob + ps.off_t_ping);
-  d.fmin_ts = (int64_t *) (blob + ps.off_fmin_ts);
+  d.fmin_ts = (uint32_t *) (blob + ps.off_fmin_ts);
   d.f_ts = (int64_t *) (blob + ps.off_f_ts);
-  d.busy = (int64_t *) (blob + ps.off_busy);
-  d.w_ts = (int64_t *) (blob + ps.off_w_ts);
+  d.busy = (uint32_t *) (blob + ps.off_busy);
+  d.w_ts = (uint32_t *) (blob + ps.off_w_ts);
   d.sring = (PStat *) (blob + ps.off_sring);
   d.q_bytes = (uint32_t *) (blob + ps.off_q_bytes);
   d.f_pos = (uint32_t *) (blob + ps.off_f_pos);
@@ -165,15 +169,24 @@ struct PAcc
 
 struct PCand
 {
-  int64_t ts;
+  uint32_t ts;      /* offset from sc->base */
   int32_t kind;
   int32_t idx;      /* link (RCV, TXC), flow, overlay index */
 };
 
-PRB_HD int64_t
-sat_add (int64_t a, int64_t b)
+PRB_HD uint32_t
+sat32 (uint32_t a, uint32_t b)
 {
-  return a > P_FAR - b ? P_FAR : a + b;
+  return a > P_FAR32 - b ? P_FAR32 : a + b;
+}
+
+/* absolute ns -> offset from base, saturated */
+PRB_HD uint32_t
+rel32 (int64_t t, int64_t base)
+{
+  if (t == P_FAR) return P_FAR32;
+  uint64_t dlt = (uint64_t) (t - base);
+  return dlt > 0xFFFFFFFEull ? P_FAR32 : (uint32_t) dlt;
 }
 
 /* ---- scheduling histories ---- */
@@ -265,8 +278,23 @@ struct PSim
   PDyn &d;
   PAcc &acc;
   int env;
+  int64_t base;              /* absolute time of offset 0 (sc->base) */
+  uint32_t until_rel, stop_rel;
 
-  PRB_HD PSim (const Static &st_, const PStatic &ps_, PDyn &d_, PAcc &acc_, int env_) : st (st_), ps (ps_), d (d_), acc (acc_), env (env_) {}
+  PRB_HD PSim (const Static &st_, const PStatic &ps_, PDyn &d_, PAcc &acc_, int env_) : st (st_), ps (ps_), d (d_), acc (acc_), env (env_), base (0), until_rel (0), stop_rel (0) {}
+
+  /* the run covers events before until_ns; offsets are taken from the run's start (sc->base) */
+  PRB_HD void
+  set_window (int64_t until_ns)
+  {
+    base = d.sc->base;
+    until_rel = rel32 (until_ns, base);
+    stop_rel = rel32 (st.sim_time_ns, base);
+    if (until_rel == P_FAR32) until_rel = P_FAR32 - 1;
+    if (stop_rel == P_FAR32) stop_rel = P_FAR32 - 1;
+    until_is_stop = until_ns >= st.sim_time_ns;
+  }
+  bool until_is_stop;
 
   PRB_HD static void
   to_pkt (const PRec &r, Pkt &p)
@@ -306,13 +334,13 @@ struct PSim
 
   /* ---- float statistics: appended here, folded in timestamp order by the team ---- */
   PRB_HD void
-  stat_push (int x, int64_t ts, int64_t sched, uint32_t code, float v)
+  stat_push (int x, uint32_t ts, int64_t sched, uint32_t code, float v)
   {
     uint8_t t = d.s_tail[x];
     PStat &s = d.sring[x * P_SR + (t & (P_SR - 1))];
     /* code in the top two bits; below, how long before ts the event was scheduled (saturated): records of
      * different nodes with one timestamp are folded earliest-scheduled first, like the events ran */
-    int64_t dd = sched == P_SCHED_LAZY ? 0 : (sched < 0 ? 0x3FFFFFFF : ts - sched);
+    int64_t dd = sched == P_SCHED_LAZY ? 0 : (sched < 0 ? 0x3FFFFFFF : base + ts - sched);
     s.ts = ts; s.code = (code << 30) | (uint32_t) (dd > 0x3FFFFFFF ? 0x3FFFFFFF : dd); s.v = v;
     d.s_tail[x] = (uint8_t) (t + 1);
   }
@@ -323,7 +351,7 @@ struct PSim
   }
 
   PRB_HD void
-  count_drop (int x, int64_t now, int64_t sched, bool overlay_side)
+  count_drop (int x, uint32_t now, int64_t sched, bool overlay_side)
   {
     if (overlay_side)
       acc.overlay_lost++;
@@ -337,8 +365,9 @@ struct PSim
    * (already in the ring).  cur: the running event; branch: position among the transmissions of a ping
    * round (0xFFFF: inherit).  There is ONE call site (execute), so one copy in the instruction stream. */
   PRB_HD void
-  dev_send (int x, int l, int64_t now, const Pkt &p, const PCtx &cur, uint32_t branch, int mode)
+  dev_send (int x, int l, uint32_t now, const Pkt &p, const PCtx &cur, uint32_t branch, int mode)
   {
+    const int64_t now_abs = base + now;
     int node = st.link_from[l];
     int data = p_type (p) == PRB_DATA;
     uint32_t size = st.szc_bytes[p_szc (p)];
@@ -354,15 +383,15 @@ struct PSim
             count_drop (x, now, cur.sched, p_valable (p));
             return;
           }
-        if (l >= st.L) log_event (now, PRB_EV_INJ, node, l, p, -1);
+        if (l >= st.L) log_event (now_abs, PRB_EV_INJ, node, l, p, -1);
         bool fits = l < st.L ? (qb + size <= st.max_out_buffer) : ((uint32_t) (uint16_t) (t - m) + 1 <= 1000u);
         if (PRB_UNLIKELY (!fits))
           {
-            if (l < st.L) log_event (now, PRB_EV_DRP, node, l, p, (int) qb);
+            if (l < st.L) log_event (now_abs, PRB_EV_DRP, node, l, p, (int) qb);
             if (data) count_drop (x, now, cur.sched, p_valable (p) && p_dst (p) != node);
             return;
           }
-        if (l < st.L) log_event (now, PRB_EV_ENQ, node, l, p, (int) (qb + size));
+        if (l < st.L) log_event (now_abs, PRB_EV_ENQ, node, l, p, (int) (qb + size));
         if (PRB_UNLIKELY ((uint16_t) (t - d.head[l]) > mask))
           {
             acc.errors |= PRB_ERR_POOL;
@@ -370,8 +399,8 @@ struct PSim
           }
         /* a TransmitComplete with nothing waiting only marks the device idle: it is not an event here, the
          * device is READY as soon as the clock reaches busy_until */
-        busy = m != t || d.busy[l] > now;
-        if (PRB_UNLIKELY (!busy && d.busy[l] == now && now != 0)) busy = completes_later (l, now, cur);
+        busy = m != t || d.busy[l] > now + 1;
+        if (PRB_UNLIKELY (!busy && d.busy[l] == now + 1)) busy = completes_later (l, now_abs, cur);
         slot = &d.rings[ps.ring_off[l] + (t & mask)];
         d.tail[l] = (uint16_t) (t + 1);
         if (busy)
@@ -401,11 +430,11 @@ struct PSim
       }
     else
       slot->ord = o;
-    if (l < st.L) log_event (now, PRB_EV_TXB, node, l, p, (int) qb);
+    if (l < st.L) log_event (now_abs, PRB_EV_TXB, node, l, p, (int) qb);
     int szc = p_szc (p);
-    int64_t tx = st.tx_ns[st.link_rc[l] * MAX_SZC + szc];
-    int64_t delay = l < st.L ? st.link_delay_ns : 0;
-    d.busy[l] = now + tx;
+    uint32_t tx = (uint32_t) st.tx_ns[st.link_rc[l] * MAX_SZC + szc];
+    uint32_t delay = l < st.L ? (uint32_t) st.link_delay_ns : 0u;
+    d.busy[l] = now + tx + 1;
     d.fly_szc[l] = (uint8_t) szc;
     d.fly_ord[l] = o;
     if ((uint16_t) (m - d.head[l]) >= (uint16_t) ps.W) acc.errors |= PRB_ERR_POOL;
@@ -590,7 +619,7 @@ struct PSim
         else if (PRB_UNLIKELY (t == bt && t != P_FAR))
           bf = flow_tie (bf, f);
       }
-    d.fmin_ts[x] = bt;
+    d.fmin_ts[x] = rel32 (bt, base);
     d.fmin_f[x] = bf;
   }
 
@@ -609,13 +638,13 @@ struct PSim
     switch (c.kind)
       {
       case PK_RCV:
-        return rcv_ctx (c.idx, c.ts, d.rings[ps.ring_off[c.idx] + (d.head[c.idx] & ps.ring_mask[c.idx])]);
+        return rcv_ctx (c.idx, base + c.ts, d.rings[ps.ring_off[c.idx] + (d.head[c.idx] & ps.ring_mask[c.idx])]);
       case PK_TXC:
-        return txc_ctx (c.idx, c.ts);
+        return txc_ctx (c.idx, base + c.ts);
       case PK_FLOW:
         return flow_ctx (c.idx, flow_sched_time (c.idx));
       default:
-        return ping_ctx (c.idx, c.ts);
+        return ping_ctx (c.idx, base + c.ts);
       }
   }
 
@@ -640,7 +669,7 @@ struct PSim
     if (!(a.kind == PK_TXC && b.kind == PK_TXC))
       {
 #if defined(PRB_DEBUG_TIES) && !defined(__CUDA_ARCH__)
-        fprintf (stderr, "tie: ts=%lld sched=%lld a=(%d,%d) b=(%d,%d) ord=%016llx.%016llx / %016llx.%016llx\n", (long long) a.ts,
+        fprintf (stderr, "tie: ts=%lld sched=%lld a=(%d,%d) b=(%d,%d) ord=%016llx.%016llx / %016llx.%016llx\n", (long long) (base + a.ts),
                  (long long) ca.sched, a.kind, a.idx, b.kind, b.idx, (unsigned long long) ca.ord.a, (unsigned long long) ca.ord.b,
                  (unsigned long long) cb.ord.a, (unsigned long long) cb.ord.b);
 #endif
@@ -650,13 +679,13 @@ struct PSim
   }
 
   PRB_HD void
-  offer (PCand &best, int64_t ts, int kind, int idx)
+  offer (PCand &best, uint32_t ts, int kind, int idx)
   {
     if (ts < best.ts)
       {
         best.ts = ts; best.kind = kind; best.idx = idx;
       }
-    else if (PRB_UNLIKELY (ts == best.ts && ts != P_FAR))
+    else if (PRB_UNLIKELY (ts == best.ts && ts != P_FAR32))
       {
         PCand c;
         c.ts = ts; c.kind = kind; c.idx = idx;
@@ -669,7 +698,7 @@ struct PSim
   select (int x)
   {
     PCand b;
-    b.ts = P_FAR; b.kind = PK_NONE; b.idx = -1;
+    b.ts = P_FAR32; b.kind = PK_NONE; b.idx = -1;
     const int W = ps.W;
     const int la = st.L + x;
     /* the links that end at x (the access link last), then the ones that start at x */
@@ -684,39 +713,39 @@ struct PSim
       {
         int l = j < ps.DEG ? ps.out_links[x * ps.DEG + j] : la;
         if (l < 0) continue;
-        if (d.mid[l] != d.tail[l]) offer (b, d.busy[l], PK_TXC, l);
+        if (d.mid[l] != d.tail[l]) offer (b, d.busy[l] - 1, PK_TXC, l);
       }
     int m = st.map_overlay[x];
-    if (m >= 0) offer (b, d.t_ping[m], PK_PING, m);
+    if (m >= 0) offer (b, rel32 (d.t_ping[m], base), PK_PING, m);
     if (d.fmin_f[x] >= 0) offer (b, d.fmin_ts[x], PK_FLOW, d.fmin_f[x]);
     return b;
   }
 
-  /* does c lie before the end of this run (until_ns) and of the simulation? */
+  /* does c lie before the end of this run and of the simulation? */
   PRB_HD bool
-  in_time (const PCand &c, int64_t until_ns) const
+  in_time (const PCand &c) const
   {
     if (c.kind == PK_NONE) return false;
-    const int64_t stop = st.sim_time_ns;
-    if (c.ts < until_ns && c.ts < stop) return true;
+    if (c.ts < until_rel && c.ts < stop_rel) return true;
     /* Simulator::Stop is scheduled after the first ping timers: a first ping at exactly simTime still runs */
-    return c.ts == stop && until_ns >= stop && c.kind == PK_PING && d.ping_index[c.idx] == 0;
+    return c.ts == stop_rel && until_is_stop && c.kind == PK_PING && d.ping_index[c.idx] == 0;
   }
 
   /* may node x execute c now?  (t_next[] of every node is published, gmin is their minimum) */
   PRB_HD bool
-  safe (int x, const PCand &c, int64_t gmin, int64_t until_ns) const
+  safe (int x, const PCand &c, uint32_t gmin) const
   {
-    if (!in_time (c, until_ns)) return false;
+    if (!in_time (c)) return false;
     if (stat_room (x) < 2) return false;
-    if (c.ts >= sat_add (gmin, 2 * ps.la_ns)) return false;
+    if (c.ts >= sat32 (gmin, 2 * ps.la32)) return false;
     for (int j = 0; j < ps.DEG; j++)
       {
         int l = ps.in_links[x * ps.DEG + j];
         if (l < 0) break;
-        int64_t tn = d.t_next[st.link_from[l]];
-        int64_t b = d.busy[l];
-        if (c.ts >= sat_add (b > tn ? b : tn, ps.la_ns)) return false;
+        uint32_t tn = d.t_next[st.link_from[l]];
+        uint32_t b = d.busy[l];
+        b = b ? b - 1 : 0;
+        if (c.ts >= sat32 (b > tn ? b : tn, ps.la32)) return false;
       }
     return true;
   }
@@ -727,7 +756,8 @@ struct PSim
   PRB_HD void
   execute (int x, const PCand &c)
   {
-    const int64_t now = c.ts;
+    const uint32_t now = c.ts;
+    const int64_t now_abs = base + now;
     const int kind = c.kind;
     int l = c.idx;
     /* (A) */
@@ -748,12 +778,12 @@ struct PSim
     if (kind == PK_RCV)
       {
         /* PointToPointNetDevice::Receive (+ agent hook, ExecuteActions, IP forward, statistics) */
-        cur = rcv_ctx (l, now, r);
+        cur = rcv_ctx (l, now_abs, r);
         bool access = l >= st.L;
         int type = p_type (p);
         acc.ev_real++;
         if (PRB_UNLIKELY (type == PRB_DATA && p_rejected (p) && x < 23)) return;
-        log_event (now, access ? PRB_EV_ARR : PRB_EV_RCV, x, l, p, -1);
+        log_event (now_abs, access ? PRB_EV_ARR : PRB_EV_RCV, x, l, p, -1);
         if (!access)
           {
             acc.packet_hops++;
@@ -767,7 +797,7 @@ struct PSim
             if (type == PRB_PING_FWD)
               {
                 /* PingForwardPacketManager::sendPingBackPacket */
-                float delay = d2f_ (dsub_ (ns_to_seconds_ (now), dmul_ ((double) p.aux, 0.001)));
+                float delay = d2f_ (dsub_ (ns_to_seconds_ (now_abs), dmul_ ((double) p.aux, 0.001)));
                 reply (s0, PRB_PING_BACK, x, p_last_hop (p), SZC_PING);
                 set_p_tunnel (s0, p_tunnel (p));
                 s0.uid = p.uid;
@@ -831,7 +861,7 @@ struct PSim
           }
         if (data && p_dst (p) == x)
           {
-            float dly = d2f_ (dsub_ (ns_to_seconds_ (now), (double) p.aux));
+            float dly = d2f_ (dsub_ (ns_to_seconds_ (now_abs), (double) p.aux));
             if (p_valable (p))
               {
                 if (p_next_hop (p) == p_dst (p))
@@ -861,7 +891,7 @@ struct PSim
     else if (kind == PK_TXC)
       {
         /* PointToPointNetDevice::TransmitComplete with a packet waiting */
-        cur = txc_ctx (l, now);
+        cur = txc_ctx (l, now_abs);
         l0 = l; ns = 1; mode = 1;
       }
     else if (kind == PK_FLOW)
@@ -876,7 +906,7 @@ struct PSim
         set_p_dst (s0, dst); set_p_src (s0, src); set_p_next_hop (s0, src); set_p_last_hop (s0, NODE_NONE);
         set_p_prev_node (s0, NODE_NONE);
         set_p_szc (s0, SZC_DATA_INJ);
-        s0.aux = (uint32_t) (uint64_t) ns_to_seconds_ (now);
+        s0.aux = (uint32_t) (uint64_t) ns_to_seconds_ (now_abs);
         if (st.inject_mode == PRB_INJECT_TRACE)
           {
             int32_t i = (int32_t) d.f_pos[f];
@@ -895,7 +925,7 @@ struct PSim
         set_p_first_hop (s0, p_valable (s0));
         set_p_ipdst (s0, dst);
         l0 = st.L + src; ns = 1;
-        schedule_flow (f, false, now);
+        schedule_flow (f, false, now_abs);
         rescan_flows (x);
       }
     else
@@ -903,7 +933,7 @@ struct PSim
         /* DataPacketManager::sendPingPackets: one ping per tunnel, built in the send loop */
         const int m = c.idx;
         acc.ev_real++;
-        cur = ping_ctx (m, now);
+        cur = ping_ctx (m, now_abs);
         ns = st.agent_k[m];
       }
     /* (C) */
@@ -918,7 +948,7 @@ struct PSim
             int nb = st.agent_nbr[m * st.K + i];
             reply (q, PRB_PING_FWD, x, nb, SZC_PING);
             set_p_tunnel (q, i);
-            q.uid = d.ping_index[m]; q.aux = (uint32_t) (now / 1000000);
+            q.uid = d.ping_index[m]; q.aux = (uint32_t) (now_abs / 1000000);
             li = st.route[x * st.N + nb];
             branch = (uint32_t) i;
           }
@@ -927,7 +957,7 @@ struct PSim
     if (kind == PK_PING)
       {
         d.ping_index[c.idx] += 1;
-        d.t_ping[c.idx] = now + st.ping_interval_ns;
+        d.t_ping[c.idx] = now_abs + st.ping_interval_ns;
       }
   }
 
@@ -952,6 +982,16 @@ struct PSim
     rescan_flows (x);
   }
 };
+
+/* New run: the 32-bit offsets of one environment are re-based on the run's start.  The work of the lanes of
+ * a team is split by link (re-base) and by node (p_rebase_node, after every link is done). */
+PRB_HD void
+p_rebase_link (const PStatic &ps, PDyn &d, int l, uint32_t delta)
+{
+  uint32_t b = d.busy[l];
+  d.busy[l] = b > delta ? b - delta : 0;
+  for (int k = 0; k < ps.W; k++) d.w_ts[l * ps.W + k] -= delta;       /* live slots hold arrivals >= the new base */
+}
 
 /* fold one statistics record into the float32 sums (ComputeStats push order) */
 PRB_HD void
@@ -1018,7 +1058,7 @@ p_finalize_counters (const Static &st, const PDyn &d, prb_counters &c)
   /* events = Receive + injections + ping timers + every TransmitComplete that lies before the frontier */
   int64_t pending = 0;
   for (int l = 0; l < st.LA; l++)
-    if (d.busy[l] >= sc->front_ts && d.busy[l] != 0) pending++;
+    if (d.busy[l] != 0 && sc->base + (int64_t) d.busy[l] - 1 >= sc->front_ts) pending++;
   c.events = sc->ev_real + sc->tx_started - pending;
   c.end_ns = sc->front_ts;
   c.avg_e2e = c.n_e2e ? c.sum_e2e / (float) c.n_e2e : 0.0f;

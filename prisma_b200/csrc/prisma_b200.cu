@@ -246,37 +246,47 @@ k_run_par (const __grid_constant__ Static st, const __grid_constant__ PStatic ps
   const int N = st.N;
   const int64_t stop = st.sim_time_ns;
   const int64_t until = a.until_ns;
-  const int64_t base = sc->front_ts;          /* timestamps of this launch are reduced as 32-bit offsets */
   const bool finished = sc->finished != 0;
   unsigned rounds = 0, executed = 0;
 
+  /* times inside a launch are 32-bit offsets from its start: re-base what the previous launch left */
+  if (!finished && sc->base != sc->front_ts)
+    {
+      const uint32_t delta = (uint32_t) (sc->front_ts - sc->base);
+      for (int l = gl; l < st.LA; l += T) p_rebase_link (ps, d, l, delta);
+      __syncwarp (tmask);
+      if (gl == 0) sc->base = sc->front_ts;
+      __syncwarp (tmask);
+      sim.set_window (until);
+      for (int x = gl; x < N; x += T) sim.rescan_flows (x);
+    }
+  sim.set_window (until);
   if (!finished && !sc->started)
     for (int x = gl; x < N; x += T) sim.start_node (x);
   __syncwarp (tmask);
 
   /* every statistics record older than `bound`, in timestamp order; one lane applies at a time */
-  auto fold = [&] (int64_t bound) {
+  auto fold = [&] (uint32_t bound) {
     for (;;)
       {
-        int64_t ft = P_FAR;
+        uint32_t ft = P_FAR32;
         int fx = -1;
         for (int x = gl; x < N; x += T)
           if (d.s_head[x] != d.s_tail[x])
             {
-              int64_t ts = d.sring[x * P_SR + (d.s_head[x] & (P_SR - 1))].ts;
+              uint32_t ts = d.sring[x * P_SR + (d.s_head[x] & (P_SR - 1))].ts;
               if (ts < bound && ts < ft)
                 {
                   ft = ts; fx = x;
                 }
             }
-        uint32_t rel = fx < 0 ? 0xFFFFFFFFu : (uint32_t) (ft - base);
-        uint32_t m = __reduce_min_sync (tmask, rel);
-        if (m == 0xFFFFFFFFu) break;
-        unsigned b = __ballot_sync (tmask, rel == m);
+        uint32_t m = __reduce_min_sync (tmask, ft);
+        if (m == P_FAR32) break;
+        unsigned b = __ballot_sync (tmask, ft == m);
         if (b & (b - 1))
           {
             /* one timestamp on several lanes: the record whose event was scheduled earliest */
-            uint32_t inv = rel == m ? 0x3FFFFFFFu - (d.sring[fx * P_SR + (d.s_head[fx] & (P_SR - 1))].code & 0x3FFFFFFFu) : 0xFFFFFFFFu;
+            uint32_t inv = ft == m ? 0x3FFFFFFFu - (d.sring[fx * P_SR + (d.s_head[fx] & (P_SR - 1))].code & 0x3FFFFFFFu) : P_FAR32;
             uint32_t mi = __reduce_min_sync (tmask, inv);
             b = __ballot_sync (tmask, inv == mi);
           }
@@ -289,10 +299,11 @@ k_run_par (const __grid_constant__ Static st, const __grid_constant__ PStatic ps
       }
   };
 
+  bool stats_pending = false;                  /* team-uniform: some ring may hold a record */
   while (!finished)
     {
       /* phase 1: earliest pending event of my nodes */
-      int64_t mt = P_FAR;
+      uint32_t mt = P_FAR32;
       bool mine_in_time = false;
       for (int x = gl; x < N; x += T)
         {
@@ -300,24 +311,22 @@ k_run_par (const __grid_constant__ Static st, const __grid_constant__ PStatic ps
           d.t_next[x] = c.ts;
           d.cand[x] = (c.kind << 24) | (c.idx & 0xFFFFFF);
           mt = c.ts < mt ? c.ts : mt;
-          mine_in_time = mine_in_time || sim.in_time (c, until);
+          mine_in_time = mine_in_time || sim.in_time (c);
         }
       __syncwarp (tmask);
       const bool more = __any_sync (tmask, mine_in_time);
-      uint64_t off = (uint64_t) (mt - base);
-      uint32_t rel = mt == P_FAR || off > 0xFFFFFFFEull ? 0xFFFFFFFEu : (uint32_t) off;
-      const int64_t gmin = base + (int64_t) __reduce_min_sync (tmask, rel);
-      fold (more ? gmin : P_FAR);           /* at the end of the run everything that is left */
+      const uint32_t gmin = __reduce_min_sync (tmask, mt);
+      if (stats_pending || !more) fold (more ? gmin : P_FAR32);   /* at the end of the run everything that is left */
       if (!more) break;
       /* phase 2: the earliest of my events that nothing can precede any more */
       PCand my;
-      my.ts = P_FAR; my.kind = PK_NONE; my.idx = -1;
+      my.ts = P_FAR32; my.kind = PK_NONE; my.idx = -1;
       int myx = -1;
       for (int x = gl; x < N; x += T)
         {
           PCand c;
           c.ts = d.t_next[x]; c.kind = d.cand[x] >> 24; c.idx = d.cand[x] & 0xFFFFFF;
-          if (c.ts < my.ts && sim.safe (x, c, gmin, until))
+          if (c.ts < my.ts && sim.safe (x, c, gmin))
             {
               my = c; myx = x;
             }
@@ -330,6 +339,9 @@ k_run_par (const __grid_constant__ Static st, const __grid_constant__ PStatic ps
         }
       if (myx >= 0) sim.execute (myx, my);
       __syncwarp (tmask);
+      bool left = false;
+      for (int x = gl; x < N; x += T) left = left || d.s_head[x] != d.s_tail[x];
+      stats_pending = __any_sync (tmask, left);
       rounds++;
       executed += __popc (go);
     }
@@ -653,7 +665,7 @@ run_parallel (prb_env *env, int64_t until_ns)
   a.pblobs = env->d_pblobs; a.rings = env->d_rings; a.ev_logs = env->d_ev; a.round_stats = env->d_round_stats;
   do
     {
-      int64_t chunk_end = std::min<int64_t> (target, env->par_front_ns + (int64_t) 4000000000ll);
+      int64_t chunk_end = std::min<int64_t> (target, env->par_front_ns + env->pm.ps.max_chunk_ns);
       a.until_ns = chunk_end >= stop ? std::max<int64_t> (until_ns, stop) : chunk_end;
       if ((rc = launch_par (env, a)) != PRB_OK) return rc;
       env->par_front_ns = chunk_end;

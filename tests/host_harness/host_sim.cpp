@@ -141,12 +141,12 @@ struct hp_sim
   PDyn d;
   int env_index, T;
   uint64_t rng;
-  int64_t rounds, executed;
+  int64_t rounds, executed, chunk_ns;
 };
 
 template <bool LOG>
 static void
-hp_run_t (hp_sim *s, int64_t until_ns)
+hp_run_chunk (hp_sim *s, int64_t until_ns)
 {
   const Static &st = s->hm.st;
   const PStatic &ps = s->pm.ps;
@@ -156,33 +156,46 @@ hp_run_t (hp_sim *s, int64_t until_ns)
   if (sc->finished) return;
   std::vector<PAcc> accs (T);
   memset (accs.data (), 0, sizeof (PAcc) * T);
+  /* a new run re-bases the 32-bit offsets on its start */
+  if (sc->base != sc->front_ts)
+    {
+      uint32_t delta = (uint32_t) (sc->front_ts - sc->base);
+      for (int l = 0; l < st.LA; l++) p_rebase_link (ps, d, l, delta);
+      sc->base = sc->front_ts;
+      for (int x = 0; x < N; x++)
+        {
+          PSim<LOG> sim (st, ps, d, accs[x % T], s->env_index);
+          sim.set_window (until_ns);
+          sim.rescan_flows (x);
+        }
+    }
   if (!sc->started)
     {
       for (int x = 0; x < N; x++)
         {
           PSim<LOG> sim (st, ps, d, accs[x % T], s->env_index);
+          sim.set_window (until_ns);
           sim.start_node (x);
         }
       sc->started = 1;
     }
   std::vector<PCand> cand (N);
   std::vector<int> chosen (T), order (T);
-  auto fold = [&] (int64_t bound) {
+  auto fold = [&] (uint32_t bound) {
     for (;;)
       {
-        int bx = -1, bl = 0;
-        int64_t bt = P_FAR;
-        uint32_t bd = 0;
+        int bx = -1;
+        uint32_t bt = P_FAR32, bd = 0;
         /* every lane offers the oldest record of its nodes (first node wins inside a lane); same timestamp
          * on several lanes: the one that was scheduled earliest, then the lowest lane */
         for (int g = 0; g < T; g++)
           {
             int lx = -1;
-            int64_t lt = P_FAR;
+            uint32_t lt = P_FAR32;
             for (int x = g; x < N; x += T)
               if (d.s_head[x] != d.s_tail[x])
                 {
-                  int64_t ts = d.sring[x * P_SR + (d.s_head[x] & (P_SR - 1))].ts;
+                  uint32_t ts = d.sring[x * P_SR + (d.s_head[x] & (P_SR - 1))].ts;
                   if (ts < bound && ts < lt)
                     {
                       lt = ts; lx = x;
@@ -190,12 +203,11 @@ hp_run_t (hp_sim *s, int64_t until_ns)
                 }
             if (lx < 0) continue;
             uint32_t dd = d.sring[lx * P_SR + (d.s_head[lx] & (P_SR - 1))].code & 0x3FFFFFFFu;
-            if (lt < bt || (lt == bt && dd > bd))
+            if (bx < 0 || lt < bt || (lt == bt && dd > bd))
               {
-                bt = lt; bx = lx; bl = g; bd = dd;
+                bt = lt; bx = lx; bd = dd;
               }
           }
-        (void) bl;
         if (bx < 0) break;
         p_apply_stat (sc->c, d.sring[bx * P_SR + (d.s_head[bx] & (P_SR - 1))]);
         d.s_head[bx]++;
@@ -204,17 +216,18 @@ hp_run_t (hp_sim *s, int64_t until_ns)
   for (;;)
     {
       bool any = false;
-      int64_t gmin = P_FAR;
+      uint32_t gmin = P_FAR32;
       for (int x = 0; x < N; x++)
         {
           PSim<LOG> sim (st, ps, d, accs[x % T], s->env_index);
+          sim.set_window (until_ns);
           cand[x] = sim.select (x);
           d.t_next[x] = cand[x].ts;
           gmin = std::min (gmin, cand[x].ts);
-          any = any || sim.in_time (cand[x], until_ns);
+          any = any || sim.in_time (cand[x]);
         }
+      fold (any ? gmin : P_FAR32);
       if (!any) break;
-      fold (gmin);
       int nsafe = 0;
       for (int g = 0; g < T; g++)
         {
@@ -222,7 +235,8 @@ hp_run_t (hp_sim *s, int64_t until_ns)
           for (int x = g; x < N; x += T)
             {
               PSim<LOG> sim (st, ps, d, accs[g], s->env_index);
-              if (sim.safe (x, cand[x], gmin, until_ns) && (chosen[g] < 0 || cand[x].ts < cand[chosen[g]].ts)) chosen[g] = x;
+              sim.set_window (until_ns);
+              if (sim.safe (x, cand[x], gmin) && (chosen[g] < 0 || cand[x].ts < cand[chosen[g]].ts)) chosen[g] = x;
             }
           if (chosen[g] >= 0) nsafe++;
           order[g] = g;
@@ -243,16 +257,33 @@ hp_run_t (hp_sim *s, int64_t until_ns)
           int g = order[i];
           if (chosen[g] < 0) continue;
           PSim<LOG> sim (st, ps, d, accs[g], s->env_index);
+          sim.set_window (until_ns);
           sim.execute (chosen[g], cand[chosen[g]]);
           s->executed++;
         }
       s->rounds++;
     }
-  fold (P_FAR);
   for (int g = 0; g < T; g++) p_flush_acc (sc, accs[g]);
   const int64_t stop = st.sim_time_ns;
   sc->front_ts = std::min (until_ns, stop);
   if (until_ns >= stop) sc->finished = 1;
+}
+
+/* like prb_run: launches cover at most max_chunk_ns each */
+template <bool LOG>
+static void
+hp_run_t (hp_sim *s, int64_t until_ns)
+{
+  const int64_t stop = s->hm.st.sim_time_ns;
+  const int64_t target = std::min (until_ns, stop);
+  int64_t chunk = s->chunk_ns > 0 ? std::min (s->chunk_ns, s->pm.ps.max_chunk_ns) : s->pm.ps.max_chunk_ns;
+  do
+    {
+      int64_t front = s->d.sc->front_ts;
+      int64_t end = std::min (target, front + chunk);
+      hp_run_chunk<LOG> (s, end >= stop ? std::max (until_ns, stop) : end);
+    }
+  while (s->d.sc->front_ts < target && !s->d.sc->finished);
 }
 
 extern "C" {
@@ -272,6 +303,7 @@ hp_create (const prb_config *cfg, int env_index, int64_t ev_cap, int team)
   s->T = team;
   s->rng = 0x9E3779B97F4A7C15ULL + (uint64_t) env_index;
   s->rounds = s->executed = 0;
+  s->chunk_ns = 0;
   s->blob = s->pm.pblob0;
   s->rings.resize (s->pm.ps.ring_records);
   s->ev.resize (ev_cap > 0 ? ev_cap : 1);
@@ -330,4 +362,5 @@ int64_t hp_executed (hp_sim *s) { return s->executed; }
 int32_t hp_wire_slots (hp_sim *s) { return s->pm.ps.W; }
 int32_t hp_state_bytes (hp_sim *s) { return s->pm.ps.pblob_bytes; }
 int64_t hp_lookahead_ns (hp_sim *s) { return s->pm.ps.la_ns; }
+void hp_set_chunk (hp_sim *s, int64_t ns) { s->chunk_ns = ns; }
 }

@@ -73,6 +73,7 @@ def lib():
         L.hp_queue_bytes.argtypes = [vp, i32]
         L.hp_wire_slots.argtypes = [vp]
         L.hp_state_bytes.argtypes = [vp]
+        L.hp_set_chunk.argtypes = [vp, i64]
         _lib = L
     return _lib
 
@@ -213,6 +214,14 @@ class HostParSim:
     def queue_bytes(self):
         nl = lib().hp_num_links(self.h)
         return np.array([lib().hp_queue_bytes(self.h, l) for l in range(nl)], dtype=np.int32)
+
+    def set_chunk(self, ns):
+        """Longest stretch of simulated time per emulated launch (each one re-bases the 32-bit time offsets)."""
+        lib().hp_set_chunk(self.h, int(ns))
+
+    @property
+    def state_bytes(self):
+        return lib().hp_state_bytes(self.h)
 
     @property
     def rounds(self):

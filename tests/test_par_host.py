@@ -134,3 +134,23 @@ def test_parallel_engine_many_envs_against_oracle():
         hp.run(log=False)
         common.assert_counters_equal(osim.counters(), hp.counters())
         assert np.array_equal(osim.queue_bytes(), hp.queue_bytes())
+
+
+def test_parallel_engine_rebases_time_offsets():
+    """Times inside a launch are 32-bit offsets from its start: 37 ms launches (an odd size, so that packets
+    are in flight and queued across every boundary) against one launch, on the real ns-3 trace."""
+    g = golden_util.Golden("abilene_random_drops_3s")
+    o2u = g.arrays.overlay_to_underlay()
+    inj, policy, table, seed = common.replay_inputs(g)
+    hp = host_sim.HostParSim(g.cfg.abi_params(g.arrays), team=16)
+    hp.set_chunk(37_000_001)
+    hp.set_inject_trace(*inj)
+    hp.set_policy("node_trace", host_sim.node_trace(g.dec["node"], g.dec["action"], o2u))
+    hp.run()
+    c = hp.counters()
+    assert c["errors"] == 0
+    assert_same_multiset(g.events, hp.events())
+    for key, v in g.counters.items():
+        assert c[key] == v, key
+    for key, v in g.float_bits.items():
+        assert struct.unpack("I", struct.pack("f", c[key]))[0] == v, key
