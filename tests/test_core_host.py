@@ -182,3 +182,15 @@ def test_core_sparse_timers_beyond_key_range():
     assert common.first_event_mismatch(oe, hs.events()) is None
     common.assert_steps_equal(osim.decisions(), hs.steps())
     common.assert_counters_equal(osim.counters(), hs.counters())
+
+
+def test_whole_seconds_of_a_timestamp_is_the_integer_quotient():
+    """`uint64_t (Simulator::Now ().GetSeconds ())` (poisson-application.cc:310) goes through the Q64.64 product
+    with Invert (1e9) and a double; the parallel engine uses ns / 10^9.  Equal at every second boundary +-3 ns
+    and on random values (2e8 random values were checked once offline)."""
+    L = host_sim.lib()
+    rng = np.random.default_rng(5)
+    vals = [k * 1_000_000_000 + d for k in range(0, 4000, 7) for d in (-3, -2, -1, 0, 1, 2, 3) if k * 1_000_000_000 + d >= 0]
+    vals += [int(v) for v in rng.integers(0, 1 << 44, 20000)]
+    for ns in vals:
+        assert int(L.hs_ns_to_seconds(None, ns)) == ns // 1_000_000_000, ns
