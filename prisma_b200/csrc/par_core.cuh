@@ -693,48 +693,9 @@ struct PSim
       }
   }
 
-  /* earliest pending event of node x: one pass of predicated minimum updates; two pending events with the
-   * same timestamp (rare) send the lane through the pass that knows the tie rules */
+  /* earliest pending event of node x */
   PRB_HD PCand
   select (int x)
-  {
-    PCand b;
-    b.ts = P_FAR32; b.kind = PK_NONE; b.idx = -1;
-    bool tie = false;
-    const int W = ps.W;
-    const int la = st.L + x;
-    for (int j = 0; j <= ps.DEG; j++)
-      {
-        int li = j < ps.DEG ? ps.in_links[x * ps.DEG + j] : la;
-        int lo = j < ps.DEG ? ps.out_links[x * ps.DEG + j] : la;
-        int l1 = li < 0 ? la : li, l2 = lo < 0 ? la : lo;
-        uint16_t h = d.head[l1];
-        uint32_t t1 = (li >= 0 && h != d.mid[l1]) ? d.w_ts[l1 * W + (h & (W - 1))] : P_FAR32;
-        uint32_t t2 = (lo >= 0 && d.mid[l2] != d.tail[l2]) ? d.busy[l2] - 1 : P_FAR32;
-        tie = tie || (t1 == b.ts && t1 != P_FAR32);
-        bool k1 = t1 < b.ts;
-        b.ts = k1 ? t1 : b.ts; b.kind = k1 ? PK_RCV : b.kind; b.idx = k1 ? l1 : b.idx;
-        tie = tie || (t2 == b.ts && t2 != P_FAR32);
-        bool k2 = t2 < b.ts;
-        b.ts = k2 ? t2 : b.ts; b.kind = k2 ? PK_TXC : b.kind; b.idx = k2 ? l2 : b.idx;
-      }
-    {
-      int m = st.map_overlay[x];
-      uint32_t t1 = m >= 0 ? rel32 (d.t_ping[m >= 0 ? m : 0], base) : P_FAR32;
-      uint32_t t2 = d.fmin_f[x] >= 0 ? d.fmin_ts[x] : P_FAR32;
-      tie = tie || (t1 == b.ts && t1 != P_FAR32);
-      bool k1 = t1 < b.ts;
-      b.ts = k1 ? t1 : b.ts; b.kind = k1 ? PK_PING : b.kind; b.idx = k1 ? m : b.idx;
-      tie = tie || (t2 == b.ts && t2 != P_FAR32);
-      bool k2 = t2 < b.ts;
-      b.ts = k2 ? t2 : b.ts; b.kind = k2 ? PK_FLOW : b.kind; b.idx = k2 ? d.fmin_f[x] : b.idx;
-    }
-    if (PRB_UNLIKELY (tie)) return select_ties (x);
-    return b;
-  }
-
-  PRB_HDN PCand
-  select_ties (int x)
   {
     PCand b;
     b.ts = P_FAR32; b.kind = PK_NONE; b.idx = -1;
