@@ -229,8 +229,8 @@ def main():
     ap.add_argument("--lanes", type=int, default=0, help="serial engine: lanes per environment (0 = library default)")
     ap.add_argument("--engine", default="auto", choices=["auto", "serial", "parallel"])
     ap.add_argument("--team", type=int, default=0, help="parallel engine: lanes per environment (0 = from the node count)")
-    ap.add_argument("--ref-sim-time", type=float, default=10.0, dest="ref_sim_time")
-    ap.add_argument("--cpu-sim-time", type=float, default=30.0, dest="cpu_sim_time")
+    ap.add_argument("--ref-sim-time", type=float, default=60.0, dest="ref_sim_time")
+    ap.add_argument("--cpu-sim-time", type=float, default=240.0, dest="cpu_sim_time")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
