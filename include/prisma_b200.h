@@ -192,6 +192,19 @@ int prb_step (prb_env *env, const int32_t *actions_dev, prb_step_rec *out_dev);
 /* the same through host buffers (copies inside) */
 int prb_step_host (prb_env *env, const int32_t *actions, prb_step_rec *out);
 
+/* ---- dqn_buffer agents on the device (prisma/source/models.py:257-301, learner.py:142-159) ----
+ * prb_qnet_load: the weights of the M per-node networks, prb_qnet_num_floats floats, node after node, per node
+ *   W_dst[M][32] b_dst[32] W_buf[K][32] b_buf[32] W_1[64][64] b_1[64] W_2[64][64] b_2[64] W_3[64][K] b_3[K]
+ *   (Keras kernel layout [in][out], K = largest overlay degree, unused columns ignored).
+ * prb_qnet_act: argmin-Q action (uniform random neighbour with probability eps) for the pending step of every
+ *   environment; rec_dev / actions_dev are the buffers of prb_step; q_out_dev [E][K] optional.
+ * prb_step_qnet: n_steps x (prb_qnet_act, prb_step) without leaving the device: out_dev must hold the records
+ *   of the previous prb_step (zeroed before the first call of an episode). */
+int64_t prb_qnet_num_floats (prb_env *env);
+int prb_qnet_load (prb_env *env, const float *weights, int64_t n_floats);
+int prb_qnet_act (prb_env *env, const prb_step_rec *rec_dev, int32_t *actions_dev, float *q_out_dev, float eps, uint64_t seed);
+int prb_step_qnet (prb_env *env, int32_t n_steps, float eps, uint64_t seed, prb_step_rec *out_dev);
+
 int prb_counters_host (prb_env *env, prb_counters *out /* [E] */);
 int prb_counters_dev (prb_env *env, prb_counters *out_dev /* [E] device */);
 int prb_queue_bytes (prb_env *env, int32_t e, int32_t *out /* [L] */);

@@ -161,6 +161,10 @@ def lib():
         "prb_sync": (C.c_int, [vp]),
         "prb_launch_count": (i64, [vp]),
         "prb_set_engine": (C.c_int, [vp, C.c_int, C.c_int]),
+        "prb_qnet_num_floats": (i64, [vp]),
+        "prb_qnet_load": (C.c_int, [vp, vp, i64]),
+        "prb_qnet_act": (C.c_int, [vp, vp, vp, vp, C.c_float, u64]),
+        "prb_step_qnet": (C.c_int, [vp, i32, C.c_float, u64, vp]),
         "prb_engine": (C.c_int, [vp]),
         "prb_round_stats": (C.c_int, [vp, C.POINTER(i64), C.POINTER(i64)]),
     }
@@ -176,7 +180,8 @@ EXPORTS = ["prb_last_error", "prb_version", "prb_seconds_to_ns", "prb_ns_to_seco
            "prb_build_links", "prb_global_routes", "prb_create", "prb_destroy", "prb_reset", "prb_num_links",
            "prb_state_bytes", "prb_set_inject_trace", "prb_set_policy", "prb_enable_log", "prb_read_events",
            "prb_read_steps", "prb_run", "prb_step", "prb_step_host", "prb_counters_host", "prb_counters_dev",
-           "prb_queue_bytes", "prb_sync", "prb_launch_count", "prb_set_engine", "prb_engine", "prb_round_stats"]
+           "prb_queue_bytes", "prb_sync", "prb_launch_count", "prb_set_engine", "prb_engine", "prb_round_stats",
+           "prb_qnet_num_floats", "prb_qnet_load", "prb_qnet_act", "prb_step_qnet"]
 
 
 class PrbError(RuntimeError):

@@ -112,6 +112,7 @@ class BatchedRoutingEnv:
 
     def reset(self):
         _abi.check(self.lib.prb_reset(self.h))
+        self._out.zero_()
 
     def sync(self):
         _abi.check(self.lib.prb_sync(self.h))
@@ -190,6 +191,29 @@ class BatchedRoutingEnv:
             ap = actions.ctypes.data_as(C.c_void_p)
         _abi.check(self.lib.prb_step_host(self.h, ap, out.ctypes.data_as(C.c_void_p)))
         return out
+
+    # ---- dqn_buffer agents on the device ----
+    def qnet_load(self, weights: np.ndarray):
+        """Per-node Q-networks (prisma_b200.qnet.pack_weights layout), float32."""
+        w = np.ascontiguousarray(weights, dtype=np.float32).ravel()
+        _abi.check(self.lib.prb_qnet_load(self.h, w.ctypes.data_as(C.c_void_p), w.size))
+
+    def qnet_act(self, eps: float = 0.0, seed: int = 0, actions=None, q_out=None):
+        """argmin-Q actions (eps-greedy) for the records of the last `step`; returns the int32 [E] cuda tensor."""
+        torch = self._torch
+        if actions is None:
+            if not hasattr(self, "_q_actions"):
+                self._q_actions = torch.zeros(self.num_envs, dtype=torch.int32, device=self._out.device)
+            actions = self._q_actions
+        _abi.check(self.lib.prb_qnet_act(self.h, C.c_void_p(self._out.data_ptr()), C.c_void_p(actions.data_ptr()),
+                                         C.c_void_p(q_out.data_ptr()) if q_out is not None else None,
+                                         C.c_float(eps), int(seed)))
+        return actions
+
+    def step_qnet(self, n_steps: int = 1, eps: float = 0.0, seed: int = 0) -> StepBatch:
+        """n_steps x (Q-network forward, argmin, env step) without leaving the device."""
+        _abi.check(self.lib.prb_step_qnet(self.h, int(n_steps), C.c_float(eps), int(seed), C.c_void_p(self._out.data_ptr())))
+        return self.last
 
     # ---- read-out ----
     def counters(self) -> np.ndarray:

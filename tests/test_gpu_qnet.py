@@ -1,0 +1,119 @@
+"""Device-side dqn_buffer agents (prb_qnet_act / prb_step_qnet) against a plain PyTorch fp32 statement of the
+reference's DQN_buffer_model (prisma/source/models.py:257-301) and its argmin / eps-greedy step
+(prisma/source/learner.py:142-159).  Tolerance: 1e-5 absolute on Q-values (fp32, different summation order);
+actions equal wherever the two smallest reference Q-values are more than 1e-4 apart."""
+import numpy as np
+import pytest
+
+from tests import common
+
+pytestmark = pytest.mark.gpu
+
+
+def torch_reference(nets, degrees, overlay, obs):
+    import torch
+    import torch.nn.functional as F
+    q_all = torch.zeros((len(overlay), obs.shape[1] - 1), dtype=torch.float32)
+    for e in range(len(overlay)):
+        m = int(overlay[e])
+        k = degrees[m]
+        w = {n: torch.from_numpy(v) for n, v in nets[m].items()}
+        dst = F.one_hot(torch.tensor(int(obs[e, 0])), num_classes=len(nets)).float()
+        hd = F.elu(dst @ w["w_dst"] + w["b_dst"])
+        buf = torch.from_numpy(obs[e, 1:1 + k].astype(np.float32))
+        ln = F.layer_norm(buf, (k,), eps=1e-3)
+        hb = F.elu(ln @ w["w_buf"][:k] + w["b_buf"])
+        h = F.elu(torch.cat([hd, hb]) @ w["w1"] + w["b1"])
+        h = F.elu(h @ w["w2"] + w["b2"])
+        q_all[e, :k] = F.elu(h @ w["w3"][:, :k] + w["b3"][:k])
+    return q_all.numpy()
+
+
+def setup(num_envs=256, **over):
+    from prisma_b200 import qnet
+    from prisma_b200.env import BatchedRoutingEnv
+    cfg = common.env_config("abilene", num_envs=num_envs, simTime=1.0, load_factor=1.5, pingAsObs=0,
+                            activateUnderlayTraffic=1, **over)
+    arrays = cfg.load()
+    env = BatchedRoutingEnv(cfg, arrays=arrays)
+    degrees = [len(n) for n in env.neighbors]
+    k_max = max(degrees)
+    nets = qnet.init_weights(len(degrees), degrees, k_max, seed=7)
+    rng = np.random.default_rng(1)
+    for net in nets:                      # non-zero biases so that every term is exercised
+        for b in ("b_dst", "b_buf", "b1", "b2", "b3"):
+            net[b][:] = rng.normal(0, 0.1, size=net[b].shape).astype(np.float32)
+    env.qnet_load(qnet.pack_weights(nets))
+    return env, nets, degrees, k_max
+
+
+def test_q_values_and_argmin_match_torch_fp32():
+    import torch
+    env, nets, degrees, k_max = setup()
+    q = torch.zeros((env.num_envs, k_max), dtype=torch.float32, device="cuda")
+    batch = env.step(None)
+    checked = 0
+    for it in range(60):
+        actions = env.qnet_act(q_out=q)
+        torch.cuda.synchronize()
+        rec = batch.numpy()
+        need = (rec["valid"] != 0) & (rec["need_action"] != 0)
+        if it % 10 == 9:                 # after some steps the queues are non-empty
+            idx = np.nonzero(need)[0]
+            ref = torch_reference(nets, degrees, rec["overlay"][idx], rec["obs"][idx][:, :1 + k_max])
+            got = q.cpu().numpy()[idx]
+            assert np.abs(ref - got).max() < 1e-5
+            act = actions.cpu().numpy()[idx]
+            for j, e in enumerate(idx):
+                k = degrees[int(rec["overlay"][e])]
+                srt = np.sort(ref[j, :k])
+                assert 0 <= act[j] < k
+                if k == 1 or srt[1] - srt[0] > 1e-4:
+                    assert act[j] == int(np.argmin(ref[j, :k]))
+            assert (actions.cpu().numpy()[~need] == 0).all()
+            checked += len(idx)
+            assert rec["obs"][idx][:, 1:].max() > 0
+        batch = env.step(actions)
+    assert checked > 500
+    env.check_errors()
+    env.close()
+
+
+def test_step_qnet_equals_step_plus_act():
+    """The fused device loop is the same sequence of launches as the explicit one: identical counters."""
+    res = []
+    for fused in (False, True):
+        env, nets, degrees, k_max = setup(num_envs=64)
+        if fused:
+            env.step_qnet(400)
+        else:
+            batch = env.step(None)
+            for _ in range(399):
+                batch = env.step(env.qnet_act())
+        c = env.counters()
+        env.check_errors(c)
+        res.append(c)
+        env.close()
+    for k in common.COUNTER_INTS:
+        assert np.array_equal(res[0][k], res[1][k]), k
+    assert int(res[0]["packet_hops"].sum()) > 0
+
+
+def test_eps_greedy_explores_uniformly():
+    import torch
+    env, nets, degrees, k_max = setup(num_envs=2048)
+    batch = env.step(None)
+    greedy = env.qnet_act().clone()
+    rnd = env.qnet_act(eps=1.0, seed=11).clone()
+    half = env.qnet_act(eps=0.5, seed=11).clone()
+    torch.cuda.synchronize()
+    rec = batch.numpy()
+    need = (rec["valid"] != 0) & (rec["need_action"] != 0)
+    k = np.array([degrees[int(m)] for m in rec["overlay"]])
+    g, r, h = (x.cpu().numpy() for x in (greedy, rnd, half))
+    assert ((r >= 0) & (r < k))[need].all()
+    multi = need & (k > 1)
+    assert 0.3 < np.mean(r[multi] != g[multi]) < 0.9          # a uniform draw differs from argmin (k-1)/k of the time
+    changed = np.mean(h[multi] != g[multi])
+    assert 0.1 < changed < 0.5
+    env.close()
