@@ -232,6 +232,8 @@ def main():
     ap.add_argument("--ref-sim-time", type=float, default=60.0, dest="ref_sim_time")
     ap.add_argument("--cpu-sim-time", type=float, default=240.0, dest="cpu_sim_time")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--gym-steps", type=int, default=512, dest="gym_steps",
+                    help="iterations of the supplementary Gym-mode leg with device-side dqn_buffer agents (0 = skip)")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
@@ -329,6 +331,29 @@ def main():
     h2d = int(tab_host.nbytes)
     d2h = int(cnt.nbytes)
 
+    # ---- Gym mode with the dqn_buffer agents on the device (supplementary; single GPU runs only) ----
+    gym = None
+    if world == 1 and args.gym_steps > 0:
+        from prisma_b200 import qnet
+        degrees = [len(x) for x in arrays.overlay_neighbors()]
+        env.qnet_load(qnet.pack_weights(qnet.init_weights(len(degrees), degrees, kdeg, seed=1)))
+        env.reset()
+        env.step_qnet(64, eps=0.05, seed=1)
+        torch.cuda.synchronize()
+        s0 = int(env.counters()["env_steps"].sum())
+        l0 = env.launch_count
+        g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        g0.record()
+        env.step_qnet(args.gym_steps, eps=0.05, seed=1)
+        g1.record()
+        torch.cuda.synchronize()
+        c = env.counters()
+        env.check_errors(c)
+        gym = {"value": (int(c["env_steps"].sum()) - s0) / (g0.elapsed_time(g1) / 1000.0), "unit": "agent-steps/s",
+               "launches": env.launch_count - l0, "calls": args.gym_steps,
+               "what": "prb_step_qnet: Q-network forward + eps-greedy argmin (k_qnet_act) and one Gym step of every "
+                       "environment (k_advance) per iteration, records and actions stay in HBM"}
+
     # ---- reductions over ranks ----
     if world > 1:
         t = torch.tensor([elapsed, e2e_wall], dtype=torch.float64, device="cuda")
@@ -364,6 +389,8 @@ def main():
             line["engine"] = {"name": "node-parallel (k_run_par)", "events_per_round": executed / max(rounds, 1)}
         else:
             line["engine"] = {"name": "event-serial (k_advance)"}
+        if gym:
+            line["gym_dqn_buffer"] = gym
         if world == 1 and not args.no_cpu_baseline:
             cores = os.cpu_count() or 1
             hc, sc_, dt, kind = ref_sample(args.cpu_sim_time, cores)
