@@ -205,6 +205,24 @@ int prb_qnet_load (prb_env *env, const float *weights, int64_t n_floats);
 int prb_qnet_act (prb_env *env, const prb_step_rec *rec_dev, int32_t *actions_dev, float *q_out_dev, float eps, uint64_t seed);
 int prb_step_qnet (prb_env *env, int32_t n_steps, float eps, uint64_t seed, prb_step_rec *out_dev);
 
+/* ---- replay buffers in HBM (prisma/source/replay_buffer.py:12-86; producers forwarder.py:135-161,214-244,352-379) ----
+ * One ring of rows_per_node transitions per overlay node, shared by all environments; a row is 2*(1+K)+3 floats
+ *   obs[1+K] action reward next_obs[1+K] done.
+ * prb_replay_record: feed the records of the last prb_step together with the actions that answer them (call it
+ *   between choosing the actions and the next prb_step; prb_step_qnet does so itself): the transit packet's
+ *   transition goes to the previous decision maker's ring with reward = hop time, lost packets to the reporting
+ *   node's ring with reward = loss_penalty, next_obs = [dst, 0...], done = 1.  pending_slots (power of two) is
+ *   the per-environment table of decisions in flight, keyed by packet uid (Agent.temp_obs).
+ * prb_replay_sample: uniform sampling with replacement (ReplayBuffer.sample) into device arrays [batch][1+K] / [batch].
+ * prb_replay_counts: rows ever written per node (host), transitions dropped because their decision was not found.
+ * prb_replay_read: the stored rows of one node to the host (ReplayBuffer.save). */
+int prb_replay_enable (prb_env *env, int64_t rows_per_node, int32_t pending_slots);
+int prb_replay_record (prb_env *env, const prb_step_rec *rec_dev, const int32_t *actions_dev);
+int prb_replay_counts (prb_env *env, int64_t *rows_written /* host [M] */, int64_t *missed /* host, may be NULL */);
+int prb_replay_read (prb_env *env, int32_t node, float *rows_host, int64_t max_rows, int64_t *n_rows);
+int prb_replay_sample (prb_env *env, int32_t node, int32_t batch, uint64_t seed, float *obs_dev, int32_t *action_dev,
+                       float *reward_dev, float *next_obs_dev, float *done_dev);
+
 int prb_counters_host (prb_env *env, prb_counters *out /* [E] */);
 int prb_counters_dev (prb_env *env, prb_counters *out_dev /* [E] device */);
 int prb_queue_bytes (prb_env *env, int32_t e, int32_t *out /* [L] */);

@@ -542,6 +542,106 @@ k_qnet_act (const __grid_constant__ Static st, const float *w, const prb_step_re
     }
 }
 
+/* ------------------------------------------------------------------------------------------------
+ * Replay buffers in HBM (prisma/source/replay_buffer.py:12-86), fed from the step records the way Forwarder
+ * does it (prisma/source/forwarder.py:135-161 temp_obs, :214-244 lost packets, :352-379 transit packets with
+ * 'ideal' signalling).  One ring per overlay node shared by all environments; a row is
+ *     obs[1+K] action reward next_obs[1+K] done            (float32, the dtype the reference stores: float)
+ * and a per-environment table keyed by packet uid holds the decision a packet is travelling with
+ * (Agent.temp_obs).  One thread per environment: the record of an environment is one packet. */
+struct ReplayArgs
+{
+  float *rows;                /* [M][cap][R] */
+  unsigned long long *cursor; /* [M] rows ever written */
+  unsigned long long *missed; /* transitions whose decision was not found (table collision / lost list overflow) */
+  int32_t *pending;           /* [E][pcap][PW]: uid lo, uid hi, node, action, obs[1+K] */
+  int64_t cap;
+  int32_t pcap, R, PW;
+};
+
+__device__ inline void
+replay_push (const Static &st, const ReplayArgs &ra, int node, const int32_t *ent, float reward, const int32_t *next_obs,
+             int next_n, int done)
+{
+  unsigned long long slot = atomicAdd (&ra.cursor[node], 1ull) % (unsigned long long) ra.cap;
+  float *row = ra.rows + ((size_t) node * ra.cap + slot) * ra.R;
+  const int ow = 1 + st.K;
+  for (int i = 0; i < ow; i++) row[i] = (float) ent[4 + i];
+  row[ow] = (float) ent[3];
+  row[ow + 1] = reward;
+  for (int i = 0; i < ow; i++) row[ow + 2 + i] = i < next_n ? (float) next_obs[i] : 0.0f;
+  row[2 * ow + 2] = (float) done;
+}
+
+__global__ void
+k_replay_record (const __grid_constant__ Static st, const ReplayArgs ra, const prb_step_rec *rec, const int32_t *actions)
+{
+  const int e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= st.E) return;
+  const prb_step_rec *r = &rec[e];
+  if (!r->valid || r->ptype != PRB_DATA) return;
+  int32_t *tab = ra.pending + (size_t) e * ra.pcap * ra.PW;
+  const int ow = 1 + st.K;
+  /* lost packets reported with this step: (s, a, loss_penalty, [dst, 0...], done) into THIS node's buffer */
+  int nl = r->n_lost;
+  if (nl > PRB_MAX_LOST)
+    {
+      atomicAdd (ra.missed, (unsigned long long) (nl - PRB_MAX_LOST));
+      nl = PRB_MAX_LOST;
+    }
+  for (int j = 0; j < nl; j++)
+    {
+      int64_t uid = r->lost_uid[j];
+      int32_t *ent = tab + (size_t) (uid & (ra.pcap - 1)) * ra.PW;
+      if (ent[0] == (int32_t) uid && ent[1] == (int32_t) (uid >> 32) && ent[2] >= 0)
+        {
+          int32_t nxt[1] = { ent[4] };
+          replay_push (st, ra, r->overlay, ent, st.loss_penalty, nxt, 1, 1);
+          ent[2] = -1;
+        }
+      else
+        atomicAdd (ra.missed, 1ull);
+    }
+  int32_t *ent = tab + (size_t) (r->uid & (ra.pcap - 1)) * ra.PW;
+  /* a packet that travelled from another agent: the transition of that agent's decision */
+  if (!r->is_new)
+    {
+      if (ent[0] == (int32_t) r->uid && ent[1] == (int32_t) (r->uid >> 32) && ent[2] >= 0)
+        {
+          replay_push (st, ra, ent[2], ent, (float) r->hop_time, r->obs, r->nobs, r->done);
+          ent[2] = -1;
+        }
+      else
+        atomicAdd (ra.missed, 1ull);
+    }
+  /* the decision taken now travels with the packet */
+  if (r->need_action)
+    {
+      ent[0] = (int32_t) r->uid; ent[1] = (int32_t) (r->uid >> 32); ent[2] = r->overlay; ent[3] = actions[e];
+      for (int i = 0; i < ow; i++) ent[4 + i] = r->obs[i];
+    }
+}
+
+__global__ void
+k_replay_sample (const ReplayArgs ra, int node, int batch, int ow, uint64_t seed, uint64_t call, float *obs, int32_t *act,
+                 float *rew, float *next_obs, float *done)
+{
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= batch) return;
+  unsigned long long n = ra.cursor[node];
+  if (n > (unsigned long long) ra.cap) n = (unsigned long long) ra.cap;
+  if (n == 0) return;
+  uint32_t rr[4];
+  philox4x32 ((uint32_t) b, (uint32_t) node, (uint32_t) call, (uint32_t) (call >> 32), (uint32_t) seed, (uint32_t) (seed >> 32) ^ 0x5A3Du, rr);
+  unsigned long long idx = (((unsigned long long) rr[0] << 32) | rr[1]) % n;     /* random.randint(0, len - 1) */
+  const float *row = ra.rows + ((size_t) node * ra.cap + idx) * ra.R;
+  for (int i = 0; i < ow; i++) obs[(size_t) b * ow + i] = row[i];
+  act[b] = (int32_t) row[ow];
+  rew[b] = row[ow + 1];
+  for (int i = 0; i < ow; i++) next_obs[(size_t) b * ow + i] = row[ow + 2 + i];
+  done[b] = row[2 * ow + 2];
+}
+
 /* reset: every env gets the initial blob, its policy RNG, and a fully linked free list */
 __global__ void
 k_reset (const __grid_constant__ Static st, char *blobs, Pkt *pools, const char *blob0)
@@ -645,6 +745,9 @@ struct prb_env
   /* dqn_buffer agents */
   float *d_qw = nullptr;
   uint64_t q_step = 0;
+  /* replay buffers */
+  ReplayArgs rp = {};
+  uint64_t rp_call = 0;
 };
 
 template <typename T>
@@ -883,6 +986,7 @@ prb_destroy (prb_env *env)
   cudaFree (env->d_scratch);
   cudaFree (env->d_ptables); cudaFree (env->d_pblob0); cudaFree (env->d_pblobs); cudaFree (env->d_rings);
   cudaFree (env->d_tr_prev); cudaFree (env->d_round_stats); cudaFree (env->d_qw);
+  cudaFree (env->rp.rows); cudaFree (env->rp.cursor); cudaFree (env->rp.pending);
   delete env;
   return PRB_OK;
 }
@@ -969,6 +1073,8 @@ prb_reset (prb_env *env)
       CUDA_TRY (cudaGetLastError ());
       env->launches++;
     }
+  if (env->rp.pending)   /* Agent.temp_obs belongs to the episode; the stored transitions survive it */
+    CUDA_TRY (cudaMemsetAsync (env->rp.pending, 0xFF, sizeof (int32_t) * (size_t) st.E * (size_t) env->rp.pcap * env->rp.PW, env->stream));
   env->engine_active = 0;
   env->par_front_ns = 0;
   return PRB_OK;
@@ -1278,6 +1384,93 @@ prb_qnet_act (prb_env *env, const prb_step_rec *rec_dev, int32_t *actions_dev, f
 }
 
 int
+prb_replay_enable (prb_env *env, int64_t rows_per_node, int32_t pending_slots)
+{
+  if (!env || rows_per_node < 1 || pending_slots < 1 || (pending_slots & (pending_slots - 1))) return fail (PRB_EINVAL, "bad argument");
+  if (env->rp.rows) return fail (PRB_ESTATE, "replay buffers already enabled");
+  CUDA_TRY (cudaSetDevice (env->device));
+  const Static &st = env->dst;
+  ReplayArgs &ra = env->rp;
+  ra.cap = rows_per_node; ra.pcap = pending_slots;
+  ra.R = 2 * (1 + st.K) + 3;
+  ra.PW = 4 + 1 + st.K;
+  size_t rows_b = sizeof (float) * (size_t) st.M * (size_t) ra.cap * ra.R;
+  size_t pend_b = sizeof (int32_t) * (size_t) st.E * (size_t) ra.pcap * ra.PW;
+  CUDA_TRY (cudaMalloc (&ra.rows, rows_b));
+  CUDA_TRY (cudaMalloc (&ra.cursor, sizeof (unsigned long long) * (st.M + 1)));
+  CUDA_TRY (cudaMalloc (&ra.pending, pend_b));
+  ra.missed = ra.cursor + st.M;
+  CUDA_TRY (cudaMemsetAsync (ra.rows, 0, rows_b, env->stream));
+  CUDA_TRY (cudaMemsetAsync (ra.cursor, 0, sizeof (unsigned long long) * (st.M + 1), env->stream));
+  CUDA_TRY (cudaMemsetAsync (ra.pending, 0xFF, pend_b, env->stream));
+  return PRB_OK;
+}
+
+int
+prb_replay_record (prb_env *env, const prb_step_rec *rec_dev, const int32_t *actions_dev)
+{
+  if (!env || !rec_dev || !actions_dev) return fail (PRB_EINVAL, "null argument");
+  if (!env->rp.rows) return fail (PRB_ESTATE, "replay buffers not enabled (prb_replay_enable)");
+  CUDA_TRY (cudaSetDevice (env->device));
+  const Static &st = env->dst;
+  k_replay_record<<<(st.E + 127) / 128, 128, 0, env->stream>>> (st, env->rp, rec_dev, actions_dev);
+  CUDA_TRY (cudaGetLastError ());
+  env->launches++;
+  return PRB_OK;
+}
+
+int
+prb_replay_counts (prb_env *env, int64_t *rows_written /* host [M] */, int64_t *missed /* host */)
+{
+  if (!env || !rows_written) return fail (PRB_EINVAL, "null argument");
+  if (!env->rp.rows) return fail (PRB_ESTATE, "replay buffers not enabled (prb_replay_enable)");
+  CUDA_TRY (cudaSetDevice (env->device));
+  std::vector<unsigned long long> h (env->dst.M + 1);
+  CUDA_TRY (cudaMemcpyAsync (h.data (), env->rp.cursor, sizeof (unsigned long long) * h.size (), cudaMemcpyDeviceToHost, env->stream));
+  CUDA_TRY (cudaStreamSynchronize (env->stream));
+  for (int m = 0; m < env->dst.M; m++) rows_written[m] = (int64_t) h[m];
+  if (missed) *missed = (int64_t) h[env->dst.M];
+  return PRB_OK;
+}
+
+int
+prb_replay_read (prb_env *env, int32_t node, float *rows_host, int64_t max_rows, int64_t *n_rows)
+{
+  if (!env || !n_rows) return fail (PRB_EINVAL, "null argument");
+  if (!env->rp.rows) return fail (PRB_ESTATE, "replay buffers not enabled (prb_replay_enable)");
+  if (node < 0 || node >= env->dst.M) return fail (PRB_EINVAL, "node out of range");
+  CUDA_TRY (cudaSetDevice (env->device));
+  unsigned long long w = 0;
+  CUDA_TRY (cudaMemcpyAsync (&w, env->rp.cursor + node, sizeof (w), cudaMemcpyDeviceToHost, env->stream));
+  CUDA_TRY (cudaStreamSynchronize (env->stream));
+  int64_t n = (int64_t) std::min<unsigned long long> (w, (unsigned long long) env->rp.cap);
+  *n_rows = n;
+  if (rows_host && max_rows > 0)
+    {
+      n = std::min<int64_t> (n, max_rows);
+      CUDA_TRY (cudaMemcpyAsync (rows_host, env->rp.rows + (size_t) node * env->rp.cap * env->rp.R, sizeof (float) * (size_t) n * env->rp.R,
+                                 cudaMemcpyDeviceToHost, env->stream));
+      CUDA_TRY (cudaStreamSynchronize (env->stream));
+    }
+  return PRB_OK;
+}
+
+int
+prb_replay_sample (prb_env *env, int32_t node, int32_t batch, uint64_t seed, float *obs_dev, int32_t *action_dev, float *reward_dev,
+                   float *next_obs_dev, float *done_dev)
+{
+  if (!env || !obs_dev || !action_dev || !reward_dev || !next_obs_dev || !done_dev || batch < 1) return fail (PRB_EINVAL, "bad argument");
+  if (!env->rp.rows) return fail (PRB_ESTATE, "replay buffers not enabled (prb_replay_enable)");
+  if (node < 0 || node >= env->dst.M) return fail (PRB_EINVAL, "node out of range");
+  CUDA_TRY (cudaSetDevice (env->device));
+  k_replay_sample<<<(batch + 127) / 128, 128, 0, env->stream>>> (env->rp, node, batch, 1 + env->dst.K, seed, env->rp_call++, obs_dev, action_dev,
+                                                                  reward_dev, next_obs_dev, done_dev);
+  CUDA_TRY (cudaGetLastError ());
+  env->launches++;
+  return PRB_OK;
+}
+
+int
 prb_step_qnet (prb_env *env, int32_t n_steps, float eps, uint64_t seed, prb_step_rec *out_dev)
 {
   if (!env || !out_dev || n_steps < 1) return fail (PRB_EINVAL, "bad argument");
@@ -1286,6 +1479,7 @@ prb_step_qnet (prb_env *env, int32_t n_steps, float eps, uint64_t seed, prb_step
     {
       /* the first call of an episode has no pending step: every record is invalid and the actions are zeros */
       rc = prb_qnet_act (env, out_dev, env->d_actions, nullptr, eps, seed);
+      if (rc == PRB_OK && env->rp.rows) rc = prb_replay_record (env, out_dev, env->d_actions);
       if (rc == PRB_OK) rc = prb_step (env, env->d_actions, out_dev);
     }
   return rc;

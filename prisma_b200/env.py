@@ -215,6 +215,44 @@ class BatchedRoutingEnv:
         _abi.check(self.lib.prb_step_qnet(self.h, int(n_steps), C.c_float(eps), int(seed), C.c_void_p(self._out.data_ptr())))
         return self.last
 
+    # ---- replay buffers in HBM ----
+    def replay_enable(self, rows_per_node: int, pending_slots: int = 4096):
+        _abi.check(self.lib.prb_replay_enable(self.h, int(rows_per_node), int(pending_slots)))
+        self._replay_k = max(len(n) for n in self.neighbors)
+
+    def replay_record(self, actions):
+        """Feed the records of the last `step` and the actions that answer them (before the next `step`)."""
+        _abi.check(self.lib.prb_replay_record(self.h, C.c_void_p(self._out.data_ptr()), C.c_void_p(actions.data_ptr())))
+
+    def replay_counts(self):
+        n = (C.c_int64 * len(self.neighbors))()
+        missed = C.c_int64()
+        _abi.check(self.lib.prb_replay_counts(self.h, n, C.byref(missed)))
+        return np.array(list(n), dtype=np.int64), int(missed.value)
+
+    def replay_rows(self, node: int) -> np.ndarray:
+        """Stored transitions of one node: float32 [n, 2*(1+K)+3] = obs, action, reward, next_obs, done."""
+        n = C.c_int64()
+        _abi.check(self.lib.prb_replay_read(self.h, int(node), None, 0, C.byref(n)))
+        out = np.empty((n.value, 2 * (1 + self._replay_k) + 3), dtype=np.float32)
+        if n.value:
+            _abi.check(self.lib.prb_replay_read(self.h, int(node), out.ctypes.data_as(C.c_void_p), n.value, C.byref(n)))
+        return out
+
+    def replay_sample(self, node: int, batch: int, seed: int = 0):
+        """ReplayBuffer.sample on the device: (obs [B,1+K], action [B], reward [B], next_obs [B,1+K], done [B])."""
+        torch = self._torch
+        dev, ow = self._out.device, 1 + self._replay_k
+        obs = torch.zeros((batch, ow), dtype=torch.float32, device=dev)
+        nxt = torch.zeros((batch, ow), dtype=torch.float32, device=dev)
+        act = torch.zeros(batch, dtype=torch.int32, device=dev)
+        rew = torch.zeros(batch, dtype=torch.float32, device=dev)
+        done = torch.zeros(batch, dtype=torch.float32, device=dev)
+        _abi.check(self.lib.prb_replay_sample(self.h, int(node), int(batch), int(seed), C.c_void_p(obs.data_ptr()),
+                                              C.c_void_p(act.data_ptr()), C.c_void_p(rew.data_ptr()),
+                                              C.c_void_p(nxt.data_ptr()), C.c_void_p(done.data_ptr())))
+        return obs, act, rew, nxt, done
+
     # ---- read-out ----
     def counters(self) -> np.ndarray:
         out = np.empty(self.num_envs, dtype=_abi.COUNTERS_DTYPE)

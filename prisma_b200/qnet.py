@@ -2,7 +2,7 @@
 
 The network is the reference's `DQN_buffer_model` (prisma/source/models.py:257-301): one-hot destination ->
 Dense(32, elu); LayerNormalization (no affine) of the k output-queue occupancies -> Dense(32, elu); concat ->
-Dense(64, elu) -> Dense(64, elu) -> Dense(k, elu), he_uniform kernels, zero biases; one network per overlay
+Dense(64, elu) -> Dense(64, elu) -> Dense(k, elu), he_uniform kernels and biases; one network per overlay
 node (prisma/source/agent.py).  The forward pass and the argmin / eps-greedy choice (learner.py:142-159) run in
 prisma_b200/csrc/prisma_b200.cu:k_qnet_act; this module only lays the weights out for prb_qnet_load."""
 from typing import Dict, List
@@ -28,7 +28,8 @@ def he_uniform(rng, fan_in: int, shape) -> np.ndarray:
 
 
 def init_weights(m: int, degrees: List[int], k_max: int, seed: int = 0) -> List[Dict[str, np.ndarray]]:
-    """Fresh networks as the reference builds them (he_uniform kernels, zero biases).  Node i has degrees[i]
+    """Fresh networks as the reference builds them (he_uniform kernels and biases; Keras takes fan_in =
+    units for a 1-D bias).  Node i has degrees[i]
     actions; its arrays are padded to k_max columns / rows with zeros."""
     rng = np.random.default_rng(seed)
     nets = []
@@ -41,6 +42,9 @@ def init_weights(m: int, degrees: List[int], k_max: int, seed: int = 0) -> List[
         net["w1"][:] = he_uniform(rng, 2 * H1, sh["w1"])
         net["w2"][:] = he_uniform(rng, H2, sh["w2"])
         net["w3"][:, :k] = he_uniform(rng, H2, (H2, k))
+        for b, fan in (("b_dst", H1), ("b_buf", H1), ("b1", H2), ("b2", H2)):
+            net[b][:] = he_uniform(rng, fan, sh[b])
+        net["b3"][:k] = he_uniform(rng, k, (k,))
         nets.append(net)
     return nets
 
