@@ -38,6 +38,15 @@
 
 #include "sim_core.cuh"
 
+#ifndef PRB_SELECT_UNROLL
+#define PRB_SELECT_UNROLL
+#endif
+#ifndef PRB_RESCAN_UNROLL
+#define PRB_RESCAN_UNROLL
+#endif
+#ifndef PRB_SAFE_LEVEL
+#define PRB_SAFE_LEVEL 1
+#endif
 #ifndef PRB_UNLIKELY
 #define PRB_UNLIKELY(x) __builtin_expect (!!(x), 0)
 #endif
@@ -609,6 +618,7 @@ struct PSim
   {
     int64_t bt = P_FAR;
     int bf = -1;
+    PRB_RESCAN_UNROLL
     for (int f = ps.flow_begin[x]; f < ps.flow_begin[x + 1]; f++)
       {
         int64_t t = d.f_ts[f];
@@ -702,6 +712,7 @@ struct PSim
     const int W = ps.W;
     const int la = st.L + x;
     /* the links that end at x (the access link last), then the ones that start at x */
+    PRB_SELECT_UNROLL
     for (int j = 0; j <= ps.DEG; j++)
       {
         int l = j < ps.DEG ? ps.in_links[x * ps.DEG + j] : la;
@@ -709,6 +720,7 @@ struct PSim
         uint16_t h = d.head[l];
         if (h != d.mid[l]) offer (b, d.w_ts[l * W + (h & (W - 1))], PK_RCV, l);
       }
+    PRB_SELECT_UNROLL
     for (int j = 0; j <= ps.DEG; j++)
       {
         int l = j < ps.DEG ? ps.out_links[x * ps.DEG + j] : la;
@@ -731,21 +743,68 @@ struct PSim
     return c.ts == stop_rel && until_is_stop && c.kind == PK_PING && d.ping_index[c.idx] == 0;
   }
 
-  /* may node x execute c now?  (t_next[] of every node is published, gmin is their minimum) */
+  /* Lower bounds on the time of the next event a node can still execute (t_next[] of every node is published,
+   * gmin is their minimum).  Level 0: its own pending events, or an arrival nobody has sent yet (>= gmin + LA).
+   * Level 1: the unsent arrivals are bounded through the node's in-links with the level-0 bounds of its
+   * neighbours: a link delivers no sooner than LA after max (end of its current transmission, the sender's
+   * next event). */
+  PRB_HD uint32_t
+  horizon0 (int y, uint32_t gmin) const
+  {
+    uint32_t tn = d.t_next[y], g = sat32 (gmin, ps.la32);
+    return tn < g ? tn : g;
+  }
+
+  PRB_HD uint32_t
+  link_bound (int l, uint32_t e_from) const
+  {
+    uint32_t b = d.busy[l];
+    b = b ? b - 1 : 0;
+#ifdef PRB_EXP_QHEAD
+    if (d.mid[l] != d.tail[l])
+      {
+        const PRec &r = d.rings[ps.ring_off[l] + (d.mid[l] & ps.ring_mask[l])];
+        uint32_t tx = (uint32_t) st.tx_ns[st.link_rc[l] * MAX_SZC + (int) ((r.w0 >> 7) & 15)];
+        return sat32 (b, tx + (uint32_t) st.link_delay_ns);
+      }
+#endif
+    return sat32 (b > e_from ? b : e_from, ps.la32);
+  }
+
+  PRB_HD uint32_t
+  horizon1 (int y, uint32_t gmin) const
+  {
+    uint32_t e = d.t_next[y];
+    for (int j = 0; j < ps.DEG; j++)
+      {
+        int l = ps.in_links[y * ps.DEG + j];
+        if (l < 0) break;
+        uint32_t a = link_bound (l, horizon0 (st.link_from[l], gmin));
+        e = a < e ? a : e;
+      }
+    return e;
+  }
+
+  /* may node x execute c now? */
   PRB_HD bool
   safe (int x, const PCand &c, uint32_t gmin) const
   {
     if (!in_time (c)) return false;
     if (stat_room (x) < 2) return false;
+#if PRB_SAFE_LEVEL == 0
     if (c.ts >= sat32 (gmin, 2 * ps.la32)) return false;
+#endif
     for (int j = 0; j < ps.DEG; j++)
       {
         int l = ps.in_links[x * ps.DEG + j];
         if (l < 0) break;
-        uint32_t tn = d.t_next[st.link_from[l]];
-        uint32_t b = d.busy[l];
-        b = b ? b - 1 : 0;
-        if (c.ts >= sat32 (b > tn ? b : tn, ps.la32)) return false;
+#if PRB_SAFE_LEVEL == 0
+        if (c.ts >= link_bound (l, d.t_next[st.link_from[l]])) return false;
+#elif PRB_SAFE_LEVEL == 2
+        if (c.ts >= link_bound (l, horizon1 (st.link_from[l], gmin))) return false;
+#else
+        if (c.ts >= link_bound (l, horizon0 (st.link_from[l], gmin))) return false;
+#endif
       }
     return true;
   }

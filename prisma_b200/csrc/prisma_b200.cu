@@ -214,7 +214,10 @@ struct ParArgs
 };
 
 template <int T, bool LOG, bool SMEM>
-__global__ void __launch_bounds__ (128, 4)
+#ifndef PRB_PAR_MINB
+#define PRB_PAR_MINB 4          /* 128-thread blocks per SM the register allocation must allow */
+#endif
+__global__ void __launch_bounds__ (128, PRB_PAR_MINB)
 k_run_par (const __grid_constant__ Static st, const __grid_constant__ PStatic ps, const ParArgs a)
 {
   extern __shared__ __align__ (16) char smem[];
@@ -316,7 +319,11 @@ k_run_par (const __grid_constant__ Static st, const __grid_constant__ PStatic ps
       __syncwarp (tmask);
       const bool more = __any_sync (tmask, mine_in_time);
       const uint32_t gmin = __reduce_min_sync (tmask, mt);
-      if (stats_pending || !more) fold (more ? gmin : P_FAR32);   /* at the end of the run everything that is left */
+#ifndef PRB_FOLD_EVERY
+#define PRB_FOLD_EVERY 4
+#endif
+      /* the rings hold 8 records and an event pushes at most 2; at the end of the run everything that is left */
+      if ((stats_pending && rounds % PRB_FOLD_EVERY == 0) || !more) fold (more ? gmin : P_FAR32);
       if (!more) break;
       /* phase 2: the earliest of my events that nothing can precede any more */
       PCand my;
@@ -852,7 +859,7 @@ launch_par_t (prb_env *env, const ParArgs &a)
       size_t per_block = (size_t) teams * ps.pblob_bytes + 1024;
       if (per_block > (size_t) env->max_smem) continue;
       int blocks_sm = (int) std::min<size_t> ((size_t) env->smem_per_sm / per_block, 32);
-      blocks_sm = std::min (blocks_sm, 65536 / (128 * t));      /* 128 registers per thread */
+      blocks_sm = std::min (blocks_sm, PRB_PAR_MINB * 128 / t);  /* registers: __launch_bounds__ of k_run_par */
       int resident = blocks_sm * teams;
       if (resident > best)
         {

@@ -12,6 +12,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 LIB = os.path.join(HERE, "libhost_sim.so")
 SRC = [os.path.join(HERE, "host_sim.cpp"),
        os.path.join(HERE, "..", "..", "prisma_b200", "csrc", "sim_core.cuh"),
+       os.path.join(HERE, "..", "..", "prisma_b200", "csrc", "par_core.cuh"),
        os.path.join(HERE, "..", "..", "prisma_b200", "csrc", "model.h"),
        os.path.join(HERE, "..", "..", "include", "prisma_b200.h")]
 _lib = None
@@ -19,7 +20,8 @@ _lib = None
 
 def build():
     subprocess.check_call(["g++", "-O2", "-g", "-std=c++17", "-ffp-contract=off", "-fno-fast-math", "-fPIC", "-shared",
-                           "-Wall", "-Wno-unused-function", "-Wno-unknown-pragmas", "-o", LIB, SRC[0]])
+                           "-Wall", "-Wno-unused-function", "-Wno-unknown-pragmas"]
+                          + ["-D" + x for x in os.environ.get("PRB_HOST_DEFINES", "").split()] + ["-o", LIB, SRC[0]])
 
 
 def lib():
