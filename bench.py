@@ -331,6 +331,9 @@ def main():
     h2d = int(tab_host.nbytes)
     d2h = int(cnt.nbytes)
 
+    run_engine = env.engine
+    round_stats = env.round_stats() if run_engine == "parallel" else (1, 1)
+
     # ---- Gym mode with the dqn_buffer agents on the device (supplementary; single GPU runs only) ----
     gym = None
     if world == 1 and args.gym_steps > 0:
@@ -366,7 +369,7 @@ def main():
     if rank == 0:
         peak, peak_src = measured_peak_gbs()
         # dominant kernel: k_advance, one launch per step; algorithmic bytes of THIS rank's launch
-        kernel_name = "k_run_par" if env.engine == "parallel" else "k_advance"
+        kernel_name = "k_run_par" if run_engine == "parallel" else "k_advance"
         my_hops_per_launch = (hops1 - hops0) / K
         kern_s = (sum(step_ms) / K) / 1000.0
         achieved = my_hops_per_launch * b_hop / kern_s / 1e9
@@ -384,8 +387,8 @@ def main():
                              "bytes_per_packet_hop": b_hop, "packet_hops_per_launch": my_hops_per_launch,
                              "kernel_ms": kern_s * 1000.0,
                              "note": "discrete-event simulator: issue/latency bound, not HBM bound (DESIGN.md)"}}
-        if env.engine == "parallel":
-            rounds, executed = env.round_stats()
+        if run_engine == "parallel":
+            rounds, executed = round_stats
             line["engine"] = {"name": "node-parallel (k_run_par)", "events_per_round": executed / max(rounds, 1)}
         else:
             line["engine"] = {"name": "event-serial (k_advance)"}
