@@ -658,6 +658,16 @@ struct PSim
       }
   }
 
+  /* is the packet at the head of access link l one of flow f? */
+  PRB_HD bool
+  sent_by_flow (int l, int f) const
+  {
+    if (l < st.L) return false;
+    const PRec &r = d.rings[ps.ring_off[l] + (d.head[l] & ps.ring_mask[l])];
+    return (int) ((r.w0 >> 16) & 255) == (int) st.flow_src[f] && (int) ((r.w0 >> 24) & 255) == (int) st.flow_dst[f]
+           && (int) (r.w0 & 7) == PRB_DATA;
+  }
+
   /* true when a runs before b (same timestamp, same node).
    * 1. the event that was scheduled earlier has the smaller scheduler uid;
    * 2. TransmitStart schedules its TransmitComplete before the peer's Receive (zero-delay access link);
@@ -665,6 +675,7 @@ struct PSim
    *    (POrd) are compared generation by generation, down to the creation order of the setup events (ping
    *    timers in overlay-index order before the sources, sim.cc:519-560,599-632) and the tunnel order inside
    *    one ping round (data-packet-manager.cc:349-357);
+   * 3b. a source's packet reaches the node (access link) before the source's next packet is scheduled;
    * 4. histories that do not tell (shed entries, a source among the ancestors) set PRB_ERR_TIE unless the
    *    two events cannot influence each other (TransmitComplete of two different devices). */
   PRB_HDN bool
@@ -674,6 +685,11 @@ struct PSim
     if (ca.sched != cb.sched) return ca.sched < cb.sched;
     if (a.kind == PK_TXC && b.kind == PK_RCV && a.idx == b.idx) return true;
     if (a.kind == PK_RCV && b.kind == PK_TXC && a.idx == b.idx) return false;
+    /* a source hands its packet to the device (Send -> TransmitStart schedules the peer's Receive) before it
+     * schedules its next packet (poisson-application.cc:331,357): gaps as short as the access link's
+     * serialisation time do occur */
+    if (a.kind == PK_FLOW && b.kind == PK_RCV && sent_by_flow (b.idx, a.idx)) return false;
+    if (a.kind == PK_RCV && b.kind == PK_FLOW && sent_by_flow (a.idx, b.idx)) return true;
     int r = ord_compare (ca.ord, cb.ord);
     if (r != 0) return r < 0;
     if (!(a.kind == PK_TXC && b.kind == PK_TXC))

@@ -84,6 +84,10 @@ CASES = [
                                           max_out_buffer_size=3000), 123456789012, 8),
     ("geant", dict(simTime=1.5, load_factor=1.3, pingAsObs=0, activateUnderlayTraffic=1), 77, 32),
     ("geant", dict(simTime=1.0, load_factor=1.0, pingAsObs=0, activateUnderlayTraffic=1), 3, 8),   # 3 nodes per lane
+    # a source whose next packet follows 4 ns after the previous one (the access link's serialisation time): the
+    # arrival at the node and the next injection fall into the same nanosecond (found by the 8-GPU bench)
+    ("abilene", dict(simTime=1.3, load_factor=0.9, pingAsObs=0, activateUnderlayTraffic=1, agent_type="dqn_routing",
+                     seed=100), 32284, 16),
 ]
 
 
