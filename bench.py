@@ -354,8 +354,8 @@ def main():
         env.check_errors(c)
         gym = {"value": (int(c["env_steps"].sum()) - s0) / (g0.elapsed_time(g1) / 1000.0), "unit": "agent-steps/s",
                "launches": env.launch_count - l0, "calls": args.gym_steps,
-               "what": "prb_step_qnet: Q-network forward + eps-greedy argmin (k_qnet_act) and one Gym step of every "
-                       "environment (k_advance) per iteration, records and actions stay in HBM"}
+               "what": "prb_step_qnet: every environment takes `calls` Gym steps; its warp evaluates the dqn_buffer Q-network "
+                       "(forward + eps-greedy argmin) for each step inside k_advance; records and actions never leave the GPU"}
 
     # ---- reductions over ranks ----
     if world > 1:

@@ -46,6 +46,250 @@ fail (int code, const std::string &msg)
  * Device side
  * ---------------------------------------------------------------------------------------------- */
 
+/* ------------------------------------------------------------------------------------------------
+ * Batched Q-network of the dqn_buffer agents (prisma/source/models.py:257-301, learner.py:142-159):
+ * one network per overlay node,
+ *     h_d = elu (W_dst[dst] + b_dst)                      one-hot destination -> Dense(H1): a row lookup
+ *     h_b = elu (LayerNorm (buffers) W_buf + b_buf)       LayerNormalization without affine, epsilon 1e-3
+ *     h_1 = elu ([h_d, h_b] W_1 + b_1)   h_2 = elu (h_1 W_2 + b_2)   q = elu (h_2 W_3 + b_3)
+ *     action = argmin q, or a uniform random neighbour with probability eps (DQN_AGENT.step).
+ * One warp per environment evaluates the pending Gym step of that environment (prb_step_rec) and writes the
+ * action prb_step consumes next.  17.7 kFLOP per decision, 70 MFLOP for 4096 environments: the step is launch
+ * bound, so this is a CUDA-core kernel (fp32, fixed summation order) and not a tensor-core GEMM.
+ * Weights of node m (floats, Keras kernel layout [in][out]):
+ *     W_dst[M][H1] b_dst[H1] W_buf[K][H1] b_buf[H1] W_1[2*H1][H2] b_1[H2] W_2[H2][H2] b_2[H2] W_3[H2][K] b_3[K]
+ * with H1 = 32, H2 = 64. ---------------------------------------------------------------------------- */
+constexpr int QH1 = 32, QH2 = 64;
+
+__host__ __device__ inline int64_t
+qnet_floats_per_node (int M, int K)
+{
+  return (int64_t) M * QH1 + QH1 + (int64_t) K * QH1 + QH1 + 2 * QH1 * QH2 + QH2 + QH2 * QH2 + QH2 + (int64_t) QH2 * K + K;
+}
+
+__device__ __forceinline__ float
+elu_ (float x)
+{
+  return x > 0.0f ? x : expm1f (x);
+}
+
+/* all 32 lanes of a warp: action for the pending data step *r of environment-id eid (every lane returns it) */
+__device__ __forceinline__ int
+qnet_forward (const Static &st, const float *w, const prb_step_rec *r, int lane, float eps, uint64_t seed, uint64_t step, uint64_t eid,
+              float *q_row)
+{
+  const int m = r->overlay, K = st.K, M = st.M;
+  const int k = st.agent_k[m];
+  const float *W = w + (size_t) m * qnet_floats_per_node (M, K);
+  const float *w_dst = W, *b_dst = w_dst + (size_t) M * QH1, *w_buf = b_dst + QH1, *b_buf = w_buf + (size_t) K * QH1;
+  const float *w1 = b_buf + QH1, *b1 = w1 + 2 * QH1 * QH2, *w2 = b1 + QH2, *b2 = w2 + QH2 * QH2, *w3 = b2 + QH2, *b3 = w3 + (size_t) QH2 * K;
+  /* destination branch: row obs[0] of W_dst */
+  int dst = r->obs[0];
+  dst = dst < 0 ? 0 : (dst >= M ? M - 1 : dst);
+  float hd = elu_ (w_dst[(size_t) dst * QH1 + lane] + b_dst[lane]);
+  /* buffer branch: layer normalisation over the k observed queues, then Dense(H1) */
+  float x = lane < k ? (float) (uint32_t) r->obs[1 + lane] : 0.0f;
+  float sum = x;
+  for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync (0xFFFFFFFFu, sum, o);
+  float mean = sum / (float) k;
+  float dv = lane < k ? x - mean : 0.0f;
+  float var = dv * dv;
+  for (int o = 16; o > 0; o >>= 1) var += __shfl_xor_sync (0xFFFFFFFFu, var, o);
+  float xn = dv * rsqrtf (var / (float) k + 1e-3f);
+  float acc = b_buf[lane];
+  for (int i = 0; i < k; i++) acc = fmaf (__shfl_sync (0xFFFFFFFFu, xn, i), w_buf[(size_t) i * QH1 + lane], acc);
+  float hb = elu_ (acc);
+  /* Dense(64) on [h_d, h_b]: lane j owns outputs j and j + 32 */
+  float a0 = b1[lane], a1 = b1[lane + 32];
+  for (int i = 0; i < QH1; i++)
+    {
+      float c = __shfl_sync (0xFFFFFFFFu, hd, i);
+      a0 = fmaf (c, w1[(size_t) i * QH2 + lane], a0);
+      a1 = fmaf (c, w1[(size_t) i * QH2 + lane + 32], a1);
+    }
+  for (int i = 0; i < QH1; i++)
+    {
+      float c = __shfl_sync (0xFFFFFFFFu, hb, i);
+      a0 = fmaf (c, w1[(size_t) (QH1 + i) * QH2 + lane], a0);
+      a1 = fmaf (c, w1[(size_t) (QH1 + i) * QH2 + lane + 32], a1);
+    }
+  float h0 = elu_ (a0), h1 = elu_ (a1);
+  a0 = b2[lane]; a1 = b2[lane + 32];
+  for (int i = 0; i < 32; i++)
+    {
+      float c = __shfl_sync (0xFFFFFFFFu, h0, i);
+      a0 = fmaf (c, w2[(size_t) i * QH2 + lane], a0);
+      a1 = fmaf (c, w2[(size_t) i * QH2 + lane + 32], a1);
+    }
+  for (int i = 0; i < 32; i++)
+    {
+      float c = __shfl_sync (0xFFFFFFFFu, h1, i);
+      a0 = fmaf (c, w2[(size_t) (32 + i) * QH2 + lane], a0);
+      a1 = fmaf (c, w2[(size_t) (32 + i) * QH2 + lane + 32], a1);
+    }
+  h0 = elu_ (a0); h1 = elu_ (a1);
+  /* Dense(k): lane j < k owns q_j */
+  float q = lane < k ? b3[lane] : 0.0f;
+  for (int i = 0; i < 32; i++)
+    {
+      float c = __shfl_sync (0xFFFFFFFFu, h0, i);
+      if (lane < k) q = fmaf (c, w3[(size_t) i * K + lane], q);
+    }
+  for (int i = 0; i < 32; i++)
+    {
+      float c = __shfl_sync (0xFFFFFFFFu, h1, i);
+      if (lane < k) q = fmaf (c, w3[(size_t) (32 + i) * K + lane], q);
+    }
+  q = elu_ (q);
+  if (q_row && lane < K) q_row[lane] = lane < k ? q : 0.0f;
+  /* argmin, first index on equal values (tf.argmin) */
+  float bq = lane < k ? q : INFINITY;
+  int bi = lane;
+  for (int o = 16; o > 0; o >>= 1)
+    {
+      float oq = __shfl_xor_sync (0xFFFFFFFFu, bq, o);
+      int oi = __shfl_xor_sync (0xFFFFFFFFu, bi, o);
+      if (oq < bq || (oq == bq && oi < bi))
+        {
+          bq = oq; bi = oi;
+        }
+    }
+  int action = bi;
+  if (eps > 0.0f)
+    {
+      uint32_t rr[4];
+      philox4x32 ((uint32_t) eid, (uint32_t) (eid >> 32), (uint32_t) step, (uint32_t) (step >> 32), (uint32_t) seed,
+                  (uint32_t) (seed >> 32) ^ 0x51DEu, rr);
+      float u = (float) (rr[0] >> 8) * (1.0f / 16777216.0f);
+      if (u < eps) action = (int) (rr[1] % (uint32_t) k);
+    }
+  return action;
+}
+
+__global__ void __launch_bounds__ (128)
+k_qnet_act (const __grid_constant__ Static st, const float *w, const prb_step_rec *rec, int32_t *actions, float *q_out,
+            float eps, uint64_t seed, uint64_t step)
+{
+  const int lane = threadIdx.x & 31;
+  const int e = blockIdx.x * (blockDim.x / 32) + (threadIdx.x >> 5);
+  if (e >= st.E) return;
+  const prb_step_rec *r = &rec[e];
+  if (!r->valid || !r->need_action)
+    {
+      if (lane == 0) actions[e] = 0;
+      return;
+    }
+  int action = qnet_forward (st, w, r, lane, eps, seed, step, st.env_id_base + (uint64_t) e, q_out ? q_out + (size_t) e * st.K : nullptr);
+  if (lane == 0) actions[e] = action;
+}
+
+/* ------------------------------------------------------------------------------------------------
+ * Replay buffers in HBM (prisma/source/replay_buffer.py:12-86), fed from the step records the way Forwarder
+ * does it (prisma/source/forwarder.py:135-161 temp_obs, :214-244 lost packets, :352-379 transit packets with
+ * 'ideal' signalling).  One ring per overlay node shared by all environments; a row is
+ *     obs[1+K] action reward next_obs[1+K] done            (float32, the dtype the reference stores: float)
+ * and a per-environment table keyed by packet uid holds the decision a packet is travelling with
+ * (Agent.temp_obs).  One thread per environment: the record of an environment is one packet. */
+struct ReplayArgs
+{
+  float *rows;                /* [M][cap][R] */
+  unsigned long long *cursor; /* [M] rows ever written */
+  unsigned long long *missed; /* transitions whose decision was not found (table collision / lost list overflow) */
+  int32_t *pending;           /* [E][pcap][PW]: uid lo, uid hi, node, action, obs[1+K] */
+  int64_t cap;
+  int32_t pcap, R, PW;
+};
+
+__device__ inline void
+replay_push (const Static &st, const ReplayArgs &ra, int node, const int32_t *ent, float reward, const int32_t *next_obs,
+             int next_n, int done)
+{
+  unsigned long long slot = atomicAdd (&ra.cursor[node], 1ull) % (unsigned long long) ra.cap;
+  float *row = ra.rows + ((size_t) node * ra.cap + slot) * ra.R;
+  const int ow = 1 + st.K;
+  for (int i = 0; i < ow; i++) row[i] = (float) ent[4 + i];
+  row[ow] = (float) ent[3];
+  row[ow + 1] = reward;
+  for (int i = 0; i < ow; i++) row[ow + 2 + i] = i < next_n ? (float) next_obs[i] : 0.0f;
+  row[2 * ow + 2] = (float) done;
+}
+
+/* the bookkeeping of one step record (one thread) */
+__device__ inline void
+replay_record_one (const Static &st, const ReplayArgs &ra, int e, const prb_step_rec *r, int32_t action)
+{
+  if (!r->valid || r->ptype != PRB_DATA) return;
+  int32_t *tab = ra.pending + (size_t) e * ra.pcap * ra.PW;
+  const int ow = 1 + st.K;
+  /* lost packets reported with this step: (s, a, loss_penalty, [dst, 0...], done) into THIS node's buffer */
+  int nl = r->n_lost;
+  if (nl > PRB_MAX_LOST)
+    {
+      atomicAdd (ra.missed, (unsigned long long) (nl - PRB_MAX_LOST));
+      nl = PRB_MAX_LOST;
+    }
+  for (int j = 0; j < nl; j++)
+    {
+      int64_t uid = r->lost_uid[j];
+      int32_t *ent = tab + (size_t) (uid & (ra.pcap - 1)) * ra.PW;
+      if (ent[0] == (int32_t) uid && ent[1] == (int32_t) (uid >> 32) && ent[2] >= 0)
+        {
+          int32_t nxt[1] = { ent[4] };
+          replay_push (st, ra, r->overlay, ent, st.loss_penalty, nxt, 1, 1);
+          ent[2] = -1;
+        }
+      else
+        atomicAdd (ra.missed, 1ull);
+    }
+  int32_t *ent = tab + (size_t) (r->uid & (ra.pcap - 1)) * ra.PW;
+  /* a packet that travelled from another agent: the transition of that agent's decision */
+  if (!r->is_new)
+    {
+      if (ent[0] == (int32_t) r->uid && ent[1] == (int32_t) (r->uid >> 32) && ent[2] >= 0)
+        {
+          replay_push (st, ra, ent[2], ent, (float) r->hop_time, r->obs, r->nobs, r->done);
+          ent[2] = -1;
+        }
+      else
+        atomicAdd (ra.missed, 1ull);
+    }
+  /* the decision taken now travels with the packet */
+  if (r->need_action)
+    {
+      ent[0] = (int32_t) r->uid; ent[1] = (int32_t) (r->uid >> 32); ent[2] = r->overlay; ent[3] = action;
+      for (int i = 0; i < ow; i++) ent[4 + i] = r->obs[i];
+    }
+}
+
+__global__ void
+k_replay_record (const __grid_constant__ Static st, const ReplayArgs ra, const prb_step_rec *rec, const int32_t *actions)
+{
+  const int e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= st.E) return;
+  replay_record_one (st, ra, e, &rec[e], actions[e]);
+}
+
+__global__ void
+k_replay_sample (const ReplayArgs ra, int node, int batch, int ow, uint64_t seed, uint64_t call, float *obs, int32_t *act,
+                 float *rew, float *next_obs, float *done)
+{
+  const int b = blockIdx.x * blockDim.x + threadIdx.x;
+  if (b >= batch) return;
+  unsigned long long n = ra.cursor[node];
+  if (n > (unsigned long long) ra.cap) n = (unsigned long long) ra.cap;
+  if (n == 0) return;
+  uint32_t rr[4];
+  philox4x32 ((uint32_t) b, (uint32_t) node, (uint32_t) call, (uint32_t) (call >> 32), (uint32_t) seed, (uint32_t) (seed >> 32) ^ 0x5A3Du, rr);
+  unsigned long long idx = (((unsigned long long) rr[0] << 32) | rr[1]) % n;     /* random.randint(0, len - 1) */
+  const float *row = ra.rows + ((size_t) node * ra.cap + idx) * ra.R;
+  for (int i = 0; i < ow; i++) obs[(size_t) b * ow + i] = row[i];
+  act[b] = (int32_t) row[ow];
+  rew[b] = row[ow + 1];
+  for (int i = 0; i < ow; i++) next_obs[(size_t) b * ow + i] = row[ow + 2 + i];
+  done[b] = row[2 * ow + 2];
+}
+
+
 struct LaunchArgs
 {
   char *blobs;            /* [E * blob_bytes] */
@@ -55,6 +299,13 @@ struct LaunchArgs
   const int32_t *actions; /* gym mode, may be null */
   prb_step_rec *out;      /* gym mode */
   int64_t until_ns;
+  /* gym mode with the dqn_buffer agents evaluated inside the kernel (prb_step_qnet): every environment answers its
+   * own steps until it has taken `steps` of them */
+  const float *qw;        /* null: one step per launch, actions from `actions` */
+  int32_t steps;
+  float eps;
+  uint64_t seed, step0;
+  ReplayArgs replay;      /* replay.rows == null: no replay buffers */
 };
 
 /* minimum (key, uid) over the lanes of a group; every lane gets the winning slot (or -1) and its key */
@@ -115,6 +366,24 @@ k_advance (const __grid_constant__ Static st, const LaunchArgs a)
   const int64_t until = a.until_ns;
 
   int active_resume = 0;      /* gym mode: the first thing to run is the rest of the suspended Receive */
+  int32_t own_action = -1;    /* in-kernel agents: the answer to the pending step */
+  int steps_done = 0;
+  if (GYM && G == 32 && a.qw && active)
+    {
+      /* the step this environment is suspended on is answered first (a.out holds its record) */
+      int pend = 0;
+      if (gl == 0) pend = sc->pending && !sc->finished && rec->valid;
+      pend = __shfl_sync (gmask, pend, leader);
+      if (pend)
+        {
+          int32_t act = 0;
+          if (rec->need_action)
+            act = qnet_forward (st, a.qw, rec, lane, a.eps, a.seed, a.step0, st.env_id_base + (uint64_t) env, nullptr);
+          if (gl == 0 && a.replay.rows) replay_record_one (st, a.replay, env, rec, act);
+          __syncwarp (gmask);
+          own_action = act;
+        }
+    }
   if (active && gl == 0)
     {
       if (GYM) rec->valid = 0;
@@ -156,7 +425,8 @@ k_advance (const __grid_constant__ Static st, const LaunchArgs a)
         {
           mslot = SLOT_RESUME;
           mkey = 0;
-          action = a.actions ? a.actions[env] : 0;
+          action = own_action >= 0 ? own_action : (a.actions ? a.actions[env] : 0);
+          own_action = -1;
           active_resume = 0;
         }
       if (mkey == KEY_FAR)
@@ -177,6 +447,23 @@ k_advance (const __grid_constant__ Static st, const LaunchArgs a)
       go = __shfl_sync (gmask, go, leader);
       if (mslot == fslot && mslot >= 0) scan_flows (st, d, gl, G, fts, fseq, fslot);
       if (!go) active = false;
+      if (GYM && G == 32 && a.qw)
+        {
+          /* the environment paused on a step: answer it here and go on (the whole warp evaluates the network) */
+          status = __shfl_sync (gmask, status, leader);
+          if (!go && status == ST_PAUSE && ++steps_done < a.steps)
+            {
+              int32_t act = 0;
+              if (rec->need_action)
+                act = qnet_forward (st, a.qw, rec, lane, a.eps, a.seed, a.step0 + (uint64_t) steps_done, st.env_id_base + (uint64_t) env,
+                                    nullptr);
+              if (gl == 0 && a.replay.rows) replay_record_one (st, a.replay, env, rec, act);
+              __syncwarp (gmask);
+              own_action = act;
+              active_resume = 1;
+              active = true;
+            }
+        }
     }
   __syncwarp (gmask);
   if (env < st.E && gl == 0)
@@ -418,237 +705,6 @@ k_log_counts_par (const __grid_constant__ PStatic ps, const char *pblobs, int e,
 }
 
 
-/* ------------------------------------------------------------------------------------------------
- * Batched Q-network of the dqn_buffer agents (prisma/source/models.py:257-301, learner.py:142-159):
- * one network per overlay node,
- *     h_d = elu (W_dst[dst] + b_dst)                      one-hot destination -> Dense(H1): a row lookup
- *     h_b = elu (LayerNorm (buffers) W_buf + b_buf)       LayerNormalization without affine, epsilon 1e-3
- *     h_1 = elu ([h_d, h_b] W_1 + b_1)   h_2 = elu (h_1 W_2 + b_2)   q = elu (h_2 W_3 + b_3)
- *     action = argmin q, or a uniform random neighbour with probability eps (DQN_AGENT.step).
- * One warp per environment evaluates the pending Gym step of that environment (prb_step_rec) and writes the
- * action prb_step consumes next.  17.7 kFLOP per decision, 70 MFLOP for 4096 environments: the step is launch
- * bound, so this is a CUDA-core kernel (fp32, fixed summation order) and not a tensor-core GEMM.
- * Weights of node m (floats, Keras kernel layout [in][out]):
- *     W_dst[M][H1] b_dst[H1] W_buf[K][H1] b_buf[H1] W_1[2*H1][H2] b_1[H2] W_2[H2][H2] b_2[H2] W_3[H2][K] b_3[K]
- * with H1 = 32, H2 = 64. ---------------------------------------------------------------------------- */
-constexpr int QH1 = 32, QH2 = 64;
-
-__host__ __device__ inline int64_t
-qnet_floats_per_node (int M, int K)
-{
-  return (int64_t) M * QH1 + QH1 + (int64_t) K * QH1 + QH1 + 2 * QH1 * QH2 + QH2 + QH2 * QH2 + QH2 + (int64_t) QH2 * K + K;
-}
-
-__device__ __forceinline__ float
-elu_ (float x)
-{
-  return x > 0.0f ? x : expm1f (x);
-}
-
-__global__ void __launch_bounds__ (128)
-k_qnet_act (const __grid_constant__ Static st, const float *w, const prb_step_rec *rec, int32_t *actions, float *q_out,
-            float eps, uint64_t seed, uint64_t step)
-{
-  const int lane = threadIdx.x & 31;
-  const int e = blockIdx.x * (blockDim.x / 32) + (threadIdx.x >> 5);
-  if (e >= st.E) return;
-  const prb_step_rec *r = &rec[e];
-  if (!r->valid || !r->need_action)
-    {
-      if (lane == 0) actions[e] = 0;
-      return;
-    }
-  const int m = r->overlay, K = st.K, M = st.M;
-  const int k = st.agent_k[m];
-  const float *W = w + (size_t) m * qnet_floats_per_node (M, K);
-  const float *w_dst = W, *b_dst = w_dst + (size_t) M * QH1, *w_buf = b_dst + QH1, *b_buf = w_buf + (size_t) K * QH1;
-  const float *w1 = b_buf + QH1, *b1 = w1 + 2 * QH1 * QH2, *w2 = b1 + QH2, *b2 = w2 + QH2 * QH2, *w3 = b2 + QH2, *b3 = w3 + (size_t) QH2 * K;
-  /* destination branch: row obs[0] of W_dst */
-  int dst = r->obs[0];
-  dst = dst < 0 ? 0 : (dst >= M ? M - 1 : dst);
-  float hd = elu_ (w_dst[(size_t) dst * QH1 + lane] + b_dst[lane]);
-  /* buffer branch: layer normalisation over the k observed queues, then Dense(H1) */
-  float x = lane < k ? (float) (uint32_t) r->obs[1 + lane] : 0.0f;
-  float sum = x;
-  for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync (0xFFFFFFFFu, sum, o);
-  float mean = sum / (float) k;
-  float dv = lane < k ? x - mean : 0.0f;
-  float var = dv * dv;
-  for (int o = 16; o > 0; o >>= 1) var += __shfl_xor_sync (0xFFFFFFFFu, var, o);
-  float xn = dv * rsqrtf (var / (float) k + 1e-3f);
-  float acc = b_buf[lane];
-  for (int i = 0; i < k; i++) acc = fmaf (__shfl_sync (0xFFFFFFFFu, xn, i), w_buf[(size_t) i * QH1 + lane], acc);
-  float hb = elu_ (acc);
-  /* Dense(64) on [h_d, h_b]: lane j owns outputs j and j + 32 */
-  float a0 = b1[lane], a1 = b1[lane + 32];
-  for (int i = 0; i < QH1; i++)
-    {
-      float c = __shfl_sync (0xFFFFFFFFu, hd, i);
-      a0 = fmaf (c, w1[(size_t) i * QH2 + lane], a0);
-      a1 = fmaf (c, w1[(size_t) i * QH2 + lane + 32], a1);
-    }
-  for (int i = 0; i < QH1; i++)
-    {
-      float c = __shfl_sync (0xFFFFFFFFu, hb, i);
-      a0 = fmaf (c, w1[(size_t) (QH1 + i) * QH2 + lane], a0);
-      a1 = fmaf (c, w1[(size_t) (QH1 + i) * QH2 + lane + 32], a1);
-    }
-  float h0 = elu_ (a0), h1 = elu_ (a1);
-  a0 = b2[lane]; a1 = b2[lane + 32];
-  for (int i = 0; i < 32; i++)
-    {
-      float c = __shfl_sync (0xFFFFFFFFu, h0, i);
-      a0 = fmaf (c, w2[(size_t) i * QH2 + lane], a0);
-      a1 = fmaf (c, w2[(size_t) i * QH2 + lane + 32], a1);
-    }
-  for (int i = 0; i < 32; i++)
-    {
-      float c = __shfl_sync (0xFFFFFFFFu, h1, i);
-      a0 = fmaf (c, w2[(size_t) (32 + i) * QH2 + lane], a0);
-      a1 = fmaf (c, w2[(size_t) (32 + i) * QH2 + lane + 32], a1);
-    }
-  h0 = elu_ (a0); h1 = elu_ (a1);
-  /* Dense(k): lane j < k owns q_j */
-  float q = lane < k ? b3[lane] : 0.0f;
-  for (int i = 0; i < 32; i++)
-    {
-      float c = __shfl_sync (0xFFFFFFFFu, h0, i);
-      if (lane < k) q = fmaf (c, w3[(size_t) i * K + lane], q);
-    }
-  for (int i = 0; i < 32; i++)
-    {
-      float c = __shfl_sync (0xFFFFFFFFu, h1, i);
-      if (lane < k) q = fmaf (c, w3[(size_t) (32 + i) * K + lane], q);
-    }
-  q = elu_ (q);
-  if (q_out && lane < K) q_out[(size_t) e * K + lane] = lane < k ? q : 0.0f;
-  /* argmin, first index on equal values (tf.argmin) */
-  float bq = lane < k ? q : INFINITY;
-  int bi = lane;
-  for (int o = 16; o > 0; o >>= 1)
-    {
-      float oq = __shfl_xor_sync (0xFFFFFFFFu, bq, o);
-      int oi = __shfl_xor_sync (0xFFFFFFFFu, bi, o);
-      if (oq < bq || (oq == bq && oi < bi))
-        {
-          bq = oq; bi = oi;
-        }
-    }
-  if (lane == 0)
-    {
-      int action = bi;
-      if (eps > 0.0f)
-        {
-          uint32_t rr[4];
-          philox4x32 ((uint32_t) (st.env_id_base + e), (uint32_t) ((st.env_id_base + e) >> 32), (uint32_t) step, (uint32_t) (step >> 32),
-                      (uint32_t) seed, (uint32_t) (seed >> 32) ^ 0x51DEu, rr);
-          float u = (float) (rr[0] >> 8) * (1.0f / 16777216.0f);
-          if (u < eps) action = (int) (rr[1] % (uint32_t) k);
-        }
-      actions[e] = action;
-    }
-}
-
-/* ------------------------------------------------------------------------------------------------
- * Replay buffers in HBM (prisma/source/replay_buffer.py:12-86), fed from the step records the way Forwarder
- * does it (prisma/source/forwarder.py:135-161 temp_obs, :214-244 lost packets, :352-379 transit packets with
- * 'ideal' signalling).  One ring per overlay node shared by all environments; a row is
- *     obs[1+K] action reward next_obs[1+K] done            (float32, the dtype the reference stores: float)
- * and a per-environment table keyed by packet uid holds the decision a packet is travelling with
- * (Agent.temp_obs).  One thread per environment: the record of an environment is one packet. */
-struct ReplayArgs
-{
-  float *rows;                /* [M][cap][R] */
-  unsigned long long *cursor; /* [M] rows ever written */
-  unsigned long long *missed; /* transitions whose decision was not found (table collision / lost list overflow) */
-  int32_t *pending;           /* [E][pcap][PW]: uid lo, uid hi, node, action, obs[1+K] */
-  int64_t cap;
-  int32_t pcap, R, PW;
-};
-
-__device__ inline void
-replay_push (const Static &st, const ReplayArgs &ra, int node, const int32_t *ent, float reward, const int32_t *next_obs,
-             int next_n, int done)
-{
-  unsigned long long slot = atomicAdd (&ra.cursor[node], 1ull) % (unsigned long long) ra.cap;
-  float *row = ra.rows + ((size_t) node * ra.cap + slot) * ra.R;
-  const int ow = 1 + st.K;
-  for (int i = 0; i < ow; i++) row[i] = (float) ent[4 + i];
-  row[ow] = (float) ent[3];
-  row[ow + 1] = reward;
-  for (int i = 0; i < ow; i++) row[ow + 2 + i] = i < next_n ? (float) next_obs[i] : 0.0f;
-  row[2 * ow + 2] = (float) done;
-}
-
-__global__ void
-k_replay_record (const __grid_constant__ Static st, const ReplayArgs ra, const prb_step_rec *rec, const int32_t *actions)
-{
-  const int e = blockIdx.x * blockDim.x + threadIdx.x;
-  if (e >= st.E) return;
-  const prb_step_rec *r = &rec[e];
-  if (!r->valid || r->ptype != PRB_DATA) return;
-  int32_t *tab = ra.pending + (size_t) e * ra.pcap * ra.PW;
-  const int ow = 1 + st.K;
-  /* lost packets reported with this step: (s, a, loss_penalty, [dst, 0...], done) into THIS node's buffer */
-  int nl = r->n_lost;
-  if (nl > PRB_MAX_LOST)
-    {
-      atomicAdd (ra.missed, (unsigned long long) (nl - PRB_MAX_LOST));
-      nl = PRB_MAX_LOST;
-    }
-  for (int j = 0; j < nl; j++)
-    {
-      int64_t uid = r->lost_uid[j];
-      int32_t *ent = tab + (size_t) (uid & (ra.pcap - 1)) * ra.PW;
-      if (ent[0] == (int32_t) uid && ent[1] == (int32_t) (uid >> 32) && ent[2] >= 0)
-        {
-          int32_t nxt[1] = { ent[4] };
-          replay_push (st, ra, r->overlay, ent, st.loss_penalty, nxt, 1, 1);
-          ent[2] = -1;
-        }
-      else
-        atomicAdd (ra.missed, 1ull);
-    }
-  int32_t *ent = tab + (size_t) (r->uid & (ra.pcap - 1)) * ra.PW;
-  /* a packet that travelled from another agent: the transition of that agent's decision */
-  if (!r->is_new)
-    {
-      if (ent[0] == (int32_t) r->uid && ent[1] == (int32_t) (r->uid >> 32) && ent[2] >= 0)
-        {
-          replay_push (st, ra, ent[2], ent, (float) r->hop_time, r->obs, r->nobs, r->done);
-          ent[2] = -1;
-        }
-      else
-        atomicAdd (ra.missed, 1ull);
-    }
-  /* the decision taken now travels with the packet */
-  if (r->need_action)
-    {
-      ent[0] = (int32_t) r->uid; ent[1] = (int32_t) (r->uid >> 32); ent[2] = r->overlay; ent[3] = actions[e];
-      for (int i = 0; i < ow; i++) ent[4 + i] = r->obs[i];
-    }
-}
-
-__global__ void
-k_replay_sample (const ReplayArgs ra, int node, int batch, int ow, uint64_t seed, uint64_t call, float *obs, int32_t *act,
-                 float *rew, float *next_obs, float *done)
-{
-  const int b = blockIdx.x * blockDim.x + threadIdx.x;
-  if (b >= batch) return;
-  unsigned long long n = ra.cursor[node];
-  if (n > (unsigned long long) ra.cap) n = (unsigned long long) ra.cap;
-  if (n == 0) return;
-  uint32_t rr[4];
-  philox4x32 ((uint32_t) b, (uint32_t) node, (uint32_t) call, (uint32_t) (call >> 32), (uint32_t) seed, (uint32_t) (seed >> 32) ^ 0x5A3Du, rr);
-  unsigned long long idx = (((unsigned long long) rr[0] << 32) | rr[1]) % n;     /* random.randint(0, len - 1) */
-  const float *row = ra.rows + ((size_t) node * ra.cap + idx) * ra.R;
-  for (int i = 0; i < ow; i++) obs[(size_t) b * ow + i] = row[i];
-  act[b] = (int32_t) row[ow];
-  rew[b] = row[ow + 1];
-  for (int i = 0; i < ow; i++) next_obs[(size_t) b * ow + i] = row[ow + 2 + i];
-  done[b] = row[2 * ow + 2];
-}
-
 /* reset: every env gets the initial blob, its policy RNG, and a fully linked free list */
 __global__ void
 k_reset (const __grid_constant__ Static st, char *blobs, Pkt *pools, const char *blob0)
@@ -752,6 +808,7 @@ struct prb_env
   /* dqn_buffer agents */
   float *d_qw = nullptr;
   uint64_t q_step = 0;
+  bool qnet_unfused = false;   /* PRB_QNET_UNFUSED=1: prb_step_qnet as a sequence of launches (A/B tests) */
   /* replay buffers */
   ReplayArgs rp = {};
   uint64_t rp_call = 0;
@@ -931,7 +988,7 @@ launch_advance_g (prb_env *env, const LaunchArgs &a)
   size_t smem = (size_t) envs_per_block * st.blob_bytes;
   /* shared-memory staging pays when the launch executes many events per env (run mode) and the blobs of
    * a block fit; gym-mode launches execute a handful of events and work on the blob in place */
-  bool use_smem = !GYM && smem + sizeof (prb_step_rec) * envs_per_block + 1024 <= (size_t) env->max_smem;
+  bool use_smem = (!GYM || (a.qw && a.steps >= 8)) && smem + sizeof (prb_step_rec) * envs_per_block + 1024 <= (size_t) env->max_smem;
   if (use_smem)
     {
       auto k = k_advance<G, LOG, GYM, true>;
@@ -1017,6 +1074,7 @@ prb_create (const prb_config *cfg, int device, void *cuda_stream, prb_env **out)
   env->device = device;
   env->stream = (cudaStream_t) cuda_stream;
   env->G = cfg->lanes_per_env > 0 ? cfg->lanes_per_env : 32;
+  env->qnet_unfused = getenv ("PRB_QNET_UNFUSED") != nullptr;
   if (env->G != 32 && env->G != 16 && env->G != 8)
     {
       delete env;
@@ -1323,6 +1381,7 @@ prb_run (prb_env *env, int64_t until_ns)
   LaunchArgs a;
   a.blobs = env->d_blobs; a.pools = env->d_pools; a.ev_logs = env->d_ev; a.st_logs = env->d_st;
   a.actions = nullptr; a.out = nullptr; a.until_ns = until_ns;
+  a.qw = nullptr; a.steps = 1; a.eps = 0.0f; a.seed = 0; a.step0 = 0; a.replay = ReplayArgs ();
   return launch_advance (env, a);
 }
 
@@ -1339,6 +1398,7 @@ prb_step (prb_env *env, const int32_t *actions_dev, prb_step_rec *out_dev)
   LaunchArgs a;
   a.blobs = env->d_blobs; a.pools = env->d_pools; a.ev_logs = env->d_ev; a.st_logs = env->d_st;
   a.actions = actions_dev; a.out = out_dev; a.until_ns = st.sim_time_ns;
+  a.qw = nullptr; a.steps = 1; a.eps = 0.0f; a.seed = 0; a.step0 = 0; a.replay = ReplayArgs ();
   return launch_advance (env, a);
 }
 
@@ -1481,7 +1541,24 @@ int
 prb_step_qnet (prb_env *env, int32_t n_steps, float eps, uint64_t seed, prb_step_rec *out_dev)
 {
   if (!env || !out_dev || n_steps < 1) return fail (PRB_EINVAL, "bad argument");
+  if (!env->d_qw) return fail (PRB_ESTATE, "no Q-network loaded (prb_qnet_load)");
   int rc = PRB_OK;
+  if (env->G == 32 && !env->qnet_unfused)
+    {
+      /* one launch: every warp answers the steps of its environment itself (k_advance, gym mode) */
+      CUDA_TRY (cudaSetDevice (env->device));
+      Static &st = env->dst;
+      if (env->engine_active == PRB_ENGINE_PARALLEL)
+        return fail (PRB_ESTATE, "this episode runs on the parallel engine (prb_run with a table agent): prb_reset before prb_step");
+      st.mode = MODE_GYM;
+      env->engine_active = PRB_ENGINE_SERIAL;
+      LaunchArgs a;
+      a.blobs = env->d_blobs; a.pools = env->d_pools; a.ev_logs = env->d_ev; a.st_logs = env->d_st;
+      a.actions = nullptr; a.out = out_dev; a.until_ns = st.sim_time_ns;
+      a.qw = env->d_qw; a.steps = n_steps; a.eps = eps; a.seed = seed; a.step0 = env->q_step; a.replay = env->rp;
+      env->q_step += (uint64_t) n_steps;
+      return launch_advance (env, a);
+    }
   for (int i = 0; i < n_steps && rc == PRB_OK; i++)
     {
       /* the first call of an episode has no pending step: every record is invalid and the actions are zeros */
