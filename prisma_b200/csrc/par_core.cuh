@@ -12,8 +12,9 @@
  * s + LA, LA = link_delay + tx(smallest packet) (point-to-point-net-device.cc:272-302,
  * point-to-point-channel.cc:86-107).  With t_next[y] the timestamp of the earliest pending event of node
  * y and gmin their minimum, node x may execute its earliest event e iff
- *     ts(e) <  max(busy_until[y->x], t_next[y]) + LA   for every in-link, and   ts(e) < gmin + 2 LA
- * (strictly: an arrival with the same timestamp could still be ordered before e).  The node that holds
+ *     ts(e) <  max(busy_until[y->x], min(t_next[y], gmin + LA)) + LA   for every in-link
+ * (the next event y executes is one it holds already, or an arrival nobody has sent yet: not before
+ * gmin + LA; strictly: an arrival with the same timestamp could still be ordered before e).  The node that holds
  * gmin always qualifies, so every round makes progress.
  *
  * Order of simultaneous events of ONE node.  ns-3 orders equal timestamps by scheduler uid, i.e. by the

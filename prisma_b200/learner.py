@@ -1,0 +1,162 @@
+"""DQN learner for the dqn_buffer agents (learner half), above the device-side environment.
+
+Mirrors prisma/source/learner.py:160-255 and prisma/source/trainer.py:45-100 for `signaling_type` "ideal":
+node i samples (s, a, r, s', done) from its replay ring (HBM, prb_replay_sample), the TD target of a transition
+whose action pointed at neighbour j is  r + gamma * (1 - done) * min_{a' != back to i} Q_target_j (s'),  the
+loss is Huber (Q_i (s)[a] - target), the optimiser Adam (one state per node, as in the reference).  The M
+networks live in ONE flat float32 tensor [M, P] in exactly the layout prb_qnet_load takes
+(prisma_b200/qnet.py), so that
+
+* acting on the device needs no conversion (`env.qnet_load (learner.weights ())`),
+* the data-parallel gradient exchange is a single all-reduce over one bucket (torch.distributed, NCCL over
+  NVLink on a multi-GPU job; gloo in the CPU tests).
+
+PyTorch autograd and its matmul kernels do the training math here: library code above the environment, not
+part of the simulated path."""
+from typing import List, Optional, Sequence
+
+import numpy as np
+import torch
+import torch.nn.functional as F
+
+from . import qnet
+
+H1, H2 = qnet.H1, qnet.H2
+
+
+def _views(flat: torch.Tensor, m: int, k_max: int):
+    """Named views of one node's flat parameter vector."""
+    out, o = {}, 0
+    for name, shape in qnet.shapes(m, k_max).items():
+        n = int(np.prod(shape))
+        out[name] = flat[o:o + n].view(*shape)
+        o += n
+    return out
+
+
+def forward(flat: torch.Tensor, obs: torch.Tensor, m: int, k: int, k_max: int) -> torch.Tensor:
+    """Q-values [B, k] of the node whose parameters are `flat` for observations [B, 1 + k_max]
+    (prisma/source/models.py:257-301)."""
+    w = _views(flat, m, k_max)
+    dst = obs[:, 0].long().clamp(0, m - 1)
+    hd = F.elu(w["w_dst"][dst] + w["b_dst"])
+    buf = obs[:, 1:1 + k].float()
+    ln = F.layer_norm(buf, (k,), eps=1e-3)
+    hb = F.elu(ln @ w["w_buf"][:k] + w["b_buf"])
+    h = F.elu(torch.cat([hd, hb], dim=1) @ w["w1"] + w["b1"])
+    h = F.elu(h @ w["w2"] + w["b2"])
+    return F.elu(h @ w["w3"][:, :k] + w["b3"][:k])
+
+
+def huber(x: torch.Tensor, delta: float = 1.0) -> torch.Tensor:
+    return torch.where(x.abs() < delta, 0.5 * x * x, delta * (x.abs() - 0.5 * delta))
+
+
+class DQNLearner:
+    def __init__(self, neighbors: Sequence[Sequence[int]], lr: float = 1e-3, gamma: float = 1.0, seed: int = 0,
+                 device: str = "cpu", betas=(0.9, 0.999), adam_eps: float = 1e-7):
+        """neighbors[i] = overlay neighbours of node i in action order (BatchedRoutingEnv.neighbors mapped to overlay
+        indices).  Adam defaults are Keras' (learner.py:103: tf.keras.optimizers.Adam (lr))."""
+        self.neighbors = [list(n) for n in neighbors]
+        self.m = len(self.neighbors)
+        self.degrees = [len(n) for n in self.neighbors]
+        self.k_max = max(self.degrees)
+        self.gamma, self.lr, self.betas, self.adam_eps = float(gamma), float(lr), betas, float(adam_eps)
+        nets = qnet.init_weights(self.m, self.degrees, self.k_max, seed=seed)
+        w = torch.from_numpy(qnet.pack_weights(nets)).view(self.m, -1)
+        self.W = w.to(device).requires_grad_(True)
+        self.W_target = self.W.detach().clone()
+        self.exp_avg = torch.zeros_like(self.W_target)
+        self.exp_avg_sq = torch.zeros_like(self.W_target)
+        self.steps = torch.zeros(self.m, dtype=torch.float32, device=device)
+        # filtered_indices (trainer.py:60): at neighbour j, every action except the one that leads back to i
+        self.filtered = [[[a for a, nb in enumerate(self.neighbors[j]) if nb != i] for j in self.neighbors[i]]
+                         for i in range(self.m)]
+
+    # ---- parameters ----
+    def weights(self) -> np.ndarray:
+        return self.W.detach().cpu().numpy().ravel()
+
+    def sync_targets(self):
+        """update_target / sync_neighbor_target_q_network (learner.py:190-199,256-270)."""
+        self.W_target.copy_(self.W.detach())
+
+    def q_values(self, node: int, obs: torch.Tensor) -> torch.Tensor:
+        return forward(self.W[node], obs, self.m, self.degrees[node], self.k_max)
+
+    # ---- one gradient step of every node that has a batch ----
+    def targets(self, node: int, act, rew, nxt, done) -> torch.Tensor:
+        """get_neighbor_target_value (learner.py:232-255) for a batch of node `node`."""
+        t = rew.clone().float()
+        with torch.no_grad():
+            for a, j in enumerate(self.neighbors[node]):
+                sel = (act == a).nonzero(as_tuple=True)[0]
+                idx = self.filtered[node][a]
+                if len(sel) == 0 or not idx:
+                    continue
+                q = forward(self.W_target[j], nxt[sel], self.m, self.degrees[j], self.k_max)[:, idx]
+                t[sel] = rew[sel].float() + self.gamma * (1.0 - done[sel].float()) * q.min(dim=1).values
+        return t
+
+    def loss(self, node: int, obs, act, rew, nxt, done, weights: Optional[torch.Tensor] = None):
+        q = self.q_values(node, obs)
+        q_sel = q.gather(1, act.long().clamp(0, self.degrees[node] - 1).view(-1, 1)).squeeze(1)
+        td = q_sel - self.targets(node, act, rew, nxt, done)
+        err = huber(td)
+        if weights is not None:
+            err = err * weights
+        return err.mean(), td.detach()
+
+    def step(self, batches: List[Optional[tuple]], world_size: int = 1, all_reduce=None):
+        """batches[i] = (obs, action, reward, next_obs, done) of node i or None.  Gradients of all nodes are summed
+        over ranks with ONE all-reduce (`all_reduce (tensor)`, e.g. torch.distributed.all_reduce) and divided by
+        world_size; Adam is applied per node (nodes without a batch on any rank keep their state)."""
+        if self.W.grad is not None:
+            self.W.grad.zero_()
+        active = torch.zeros(self.m, dtype=torch.float32, device=self.W.device)
+        td_mse = [None] * self.m
+        total = None
+        for i, b in enumerate(batches):
+            if b is None or len(b[1]) == 0:
+                continue
+            l, td = self.loss(i, *b)
+            total = l if total is None else total + l
+            active[i] = 1.0
+            td_mse[i] = float((td * td).mean())
+        if total is not None:
+            total.backward()
+        grad = self.W.grad if self.W.grad is not None else torch.zeros_like(self.W_target)
+        if all_reduce is not None and world_size > 1:
+            bucket = torch.cat([grad.reshape(-1), active])
+            all_reduce(bucket)
+            grad = (bucket[:-self.m] / world_size).view_as(self.W_target)
+            active = (bucket[-self.m:] > 0).float()
+        with torch.no_grad():
+            b1, b2 = self.betas
+            on = active.view(-1, 1)
+            self.steps += active
+            self.exp_avg.mul_(1 - on * (1 - b1)).add_(on * (1 - b1) * grad)
+            self.exp_avg_sq.mul_(1 - on * (1 - b2)).add_(on * (1 - b2) * grad * grad)
+            t = self.steps.clamp(min=1).view(-1, 1)
+            m_hat = self.exp_avg / (1 - b1 ** t)
+            v_hat = self.exp_avg_sq / (1 - b2 ** t)
+            self.W -= on * self.lr * m_hat / (v_hat.sqrt() + self.adam_eps)
+        return td_mse
+
+    # ---- glue to the device-side environment ----
+    def train_on_env(self, env, batch_size: int, seed: int = 0, min_rows: Optional[int] = None, world_size: int = 1,
+                     all_reduce=None):
+        """One training step from the replay rings of `env` (prb_replay_sample), then the new weights go back to
+        the device-side agents (prb_qnet_load)."""
+        counts, _ = env.replay_counts()
+        need = batch_size if min_rows is None else min_rows          # trainer.py:41: total_samples >= batch_size
+        batches = []
+        for i in range(self.m):
+            if counts[i] < need:
+                batches.append(None)
+                continue
+            obs, act, rew, nxt, done = env.replay_sample(i, batch_size, seed=seed)
+            batches.append((obs, act, rew, nxt, done))
+        out = self.step(batches, world_size=world_size, all_reduce=all_reduce)
+        env.qnet_load(self.weights())
+        return out

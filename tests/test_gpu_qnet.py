@@ -117,3 +117,46 @@ def test_eps_greedy_explores_uniformly():
     changed = np.mean(h[multi] != g[multi])
     assert 0.1 < changed < 0.5
     env.close()
+
+
+def test_learner_trains_from_the_device_replay_rings():
+    """Collect with the device-side agents, train with prisma_b200.learner from the HBM replay rings, load the
+    new weights back: the device forward and the learner's torch forward stay the same function."""
+    import torch
+    from prisma_b200 import learner
+    from prisma_b200.env import BatchedRoutingEnv
+    cfg = common.env_config("abilene", num_envs=256, simTime=3.0, load_factor=1.2, pingAsObs=0, activateUnderlayTraffic=1)
+    arrays = cfg.load()
+    env = BatchedRoutingEnv(cfg, arrays=arrays)
+    u2o = {int(u): i for i, u in enumerate(env.overlay_to_underlay)}
+    neigh = [[u2o[int(u)] for u in nb] for nb in env.neighbors]
+    L = learner.DQNLearner(neigh, lr=1e-3, seed=2, device="cuda")
+    env.qnet_load(L.weights())
+    env.replay_enable(rows_per_node=1 << 15)
+    mse_first = mse_last = None
+    for it in range(12):
+        env.step_qnet(200, eps=0.2, seed=it)
+        mse = L.train_on_env(env, batch_size=256, seed=it)
+        if it % 4 == 3:
+            L.sync_targets()
+        vals = [m for m in mse if m is not None]
+        assert len(vals) == L.m and all(np.isfinite(vals))
+        mse_first = mse_first or float(np.mean(vals))
+        mse_last = float(np.mean(vals))
+    counts, missed = env.replay_counts()
+    assert missed == 0 and counts.min() > 256
+    # device forward == learner forward on the current weights
+    q = torch.zeros((env.num_envs, L.k_max), dtype=torch.float32, device="cuda")
+    batch = env.last
+    env.qnet_act(q_out=q)
+    torch.cuda.synchronize()
+    rec = batch.numpy()
+    need = np.nonzero((rec["valid"] != 0) & (rec["need_action"] != 0))[0]
+    assert len(need) > 50
+    for e in need[:64]:
+        node = int(rec["overlay"][e])
+        obs = torch.from_numpy(rec["obs"][e][:1 + L.k_max].astype(np.float32)).cuda().view(1, -1)
+        ref = L.q_values(node, obs).detach().cpu().numpy()[0]
+        assert np.abs(q[e, :L.degrees[node]].cpu().numpy() - ref).max() < 1e-4
+    env.check_errors()
+    env.close()
