@@ -333,6 +333,7 @@ def main():
 
     run_engine = env.engine
     round_stats = env.round_stats() if run_engine == "parallel" else (1, 1)
+    handovers = env.handovers() if run_engine == "parallel" else 0
 
     # ---- Gym mode with the dqn_buffer agents on the device (supplementary; single GPU runs only) ----
     gym = None
@@ -389,7 +390,8 @@ def main():
                              "note": "discrete-event simulator: issue/latency bound, not HBM bound (DESIGN.md)"}}
         if run_engine == "parallel":
             rounds, executed = round_stats
-            line["engine"] = {"name": "node-parallel (k_run_par)", "events_per_round": executed / max(rounds, 1)}
+            line["engine"] = {"name": "node-parallel (k_run_par)", "events_per_round": executed / max(rounds, 1),
+                              "envs_replayed_by_the_serial_engine": handovers}
         else:
             line["engine"] = {"name": "event-serial (k_advance)"}
         if gym:

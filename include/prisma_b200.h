@@ -165,6 +165,12 @@ int prb_reset (prb_env *env);
  * parallel engine, 0 = from the node count.  prb_engine: the engine that has advanced the environments
  * since the last reset (0 none).  prb_round_stats: rounds and events of the parallel engine so far. */
 int prb_set_engine (prb_env *env, int mode, int team);
+/* Environments of this episode that the node-parallel engine handed over to the event-serial engine because the
+ * order of two simultaneous events could not be rebuilt from local information (rare: long lock-step chains)
+ * or because a link's record ring filled up (a queue of nothing but the smallest packets).
+ * They are replayed from the reset state in global (timestamp, uid) order and kept up to date before every
+ * read-out, so results stay exact; with an ordered log or a per-node action trace PRB_ERR_TIE is reported instead. */
+int prb_handovers (prb_env *env);
 int prb_engine (prb_env *env);
 int prb_round_stats (prb_env *env, int64_t *rounds, int64_t *executed);
 int prb_num_links (prb_env *env);        /* L (switch<->switch, directed) */

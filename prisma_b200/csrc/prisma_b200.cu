@@ -306,6 +306,9 @@ struct LaunchArgs
   float eps;
   uint64_t seed, step0;
   ReplayArgs replay;      /* replay.rows == null: no replay buffers */
+  /* run mode on a subset: slot i of the grid advances environment env_list[i] (the parallel engine's hand-overs) */
+  const int32_t *env_list;
+  int32_t n_list;
 };
 
 /* minimum (key, uid) over the lanes of a group; every lane gets the winning slot (or -1) and its key */
@@ -337,9 +340,11 @@ k_advance (const __grid_constant__ Static st, const LaunchArgs a)
   const int gl = lane % G;                                   /* lane inside the group */
   const int leader = (lane / G) * G;
   const int group_in_block = threadIdx.x / G;
-  const int env = blockIdx.x * (blockDim.x / G) + group_in_block;
+  const int slot_ = blockIdx.x * (blockDim.x / G) + group_in_block;
+  const bool exists = slot_ < (a.env_list ? a.n_list : st.E);
+  const int env = a.env_list ? (exists ? a.env_list[slot_] : 0) : slot_;
   const unsigned gmask = G == 32 ? 0xFFFFFFFFu : (((1u << G) - 1u) << leader);
-  bool active = env < st.E;
+  bool active = exists;
   char *gblob = a.blobs + (size_t) (active ? env : 0) * st.blob_bytes;
   char *blob = gblob;
   if (SMEM)
@@ -466,7 +471,7 @@ k_advance (const __grid_constant__ Static st, const LaunchArgs a)
         }
     }
   __syncwarp (gmask);
-  if (env < st.E && gl == 0)
+  if (exists && gl == 0)
     {
       if (!sc->pending && until < stop && sc->now < until && !sc->finished) sc->now = until;
       sc->c.end_ns = sc->now;
@@ -474,7 +479,7 @@ k_advance (const __grid_constant__ Static st, const LaunchArgs a)
   if (SMEM)
     {
       __syncwarp (gmask);
-      if (env < st.E)
+      if (exists)
         {
           const uint4 *src = (const uint4 *) blob;
           uint4 *dst = (uint4 *) gblob;
@@ -538,6 +543,7 @@ k_run_par (const __grid_constant__ Static st, const __grid_constant__ PStatic ps
   const int64_t until = a.until_ns;
   const bool finished = sc->finished != 0;
   unsigned rounds = 0, executed = 0;
+  bool tied = false;
 
   /* times inside a launch are 32-bit offsets from its start: re-base what the previous launch left */
   if (!finished && sc->base != sc->front_ts)
@@ -606,6 +612,14 @@ k_run_par (const __grid_constant__ Static st, const __grid_constant__ PStatic ps
       __syncwarp (tmask);
       const bool more = __any_sync (tmask, mine_in_time);
       const uint32_t gmin = __reduce_min_sync (tmask, mt);
+      if (__any_sync (tmask, (acc.errors & (PRB_ERR_TIE | PRB_ERR_POOL)) != 0))
+        {
+          /* the order of two simultaneous events could not be rebuilt, or a link ring is full (sized for the
+           * usual mix of packet sizes, not for a queue of nothing but the smallest ones): this environment is
+           * handed over to the event-serial engine (host: resolve_ties), which replays it from its reset state */
+          tied = true;
+          break;
+        }
 #ifndef PRB_FOLD_EVERY
 #define PRB_FOLD_EVERY 4
 #endif
@@ -649,6 +663,12 @@ k_run_par (const __grid_constant__ Static st, const __grid_constant__ PStatic ps
           sc->started = 1;
           sc->front_ts = until < stop ? until : stop;
           if (until >= stop) sc->finished = 1;
+          if (tied)
+            {
+              sc->finished = 1;
+              sc->c.errors |= PRB_ERR_TIE;       /* marks the hand-over, whatever caused it */
+              if (a.round_stats) atomicAdd (&a.round_stats[2], 1ull);
+            }
           if (a.round_stats)
             {
               atomicAdd (&a.round_stats[0], (unsigned long long) rounds);
@@ -735,6 +755,29 @@ k_seed_policy (const __grid_constant__ Static st, char *blobs)
 }
 
 __global__ void
+k_tied_flags (const __grid_constant__ Static st, const __grid_constant__ PStatic ps, const char *pblobs, uint8_t *flags)
+{
+  int e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= st.E) return;
+  PDyn d;
+  p_bind_state (ps, const_cast<char *> (pblobs) + (size_t) e * ps.pblob_bytes, d);
+  flags[e] = (d.sc->c.errors & PRB_ERR_TIE) ? 1 : 0;
+}
+
+__global__ void
+k_counters_list (const __grid_constant__ Static st, const char *blobs, const int32_t *list, int n, prb_counters *out)
+{
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  int e = list[i];
+  Dyn d;
+  bind_state (st, const_cast<char *> (blobs) + (size_t) e * st.blob_bytes, d);
+  prb_counters c;
+  finalize_counters (st, d, c);
+  out[e] = c;
+}
+
+__global__ void
 k_counters (const __grid_constant__ Static st, const char *blobs, prb_counters *out)
 {
   int e = blockIdx.x * blockDim.x + threadIdx.x;
@@ -805,6 +848,13 @@ struct prb_env
   int team = 0;
   int64_t par_front_ns = 0;
   bool pol_node_trace = false;
+  /* environments the parallel engine handed over to the serial engine (undecided order of simultaneous events) */
+  std::vector<int32_t> tied;
+  std::vector<uint8_t> tied_flag;
+  int32_t *d_tied_list = nullptr;
+  uint8_t *d_tied_flags = nullptr;
+  int64_t par_until_arg = 0;       /* until_ns of the last parallel launch */
+  int64_t tied_until = 0;          /* until_ns the handed-over environments have been advanced to */
   /* dqn_buffer agents */
   float *d_qw = nullptr;
   uint64_t q_step = 0;
@@ -870,8 +920,8 @@ upload_ptables (prb_env *env)
   CUDA_TRY (cudaMemcpyAsync (env->d_ptables, buf.data (), buf.size (), cudaMemcpyHostToDevice, env->stream));
   CUDA_TRY (cudaMalloc (&env->d_pblob0, pm.ps.pblob_bytes));
   CUDA_TRY (cudaMemcpyAsync (env->d_pblob0, pm.pblob0.data (), pm.ps.pblob_bytes, cudaMemcpyHostToDevice, env->stream));
-  CUDA_TRY (cudaMalloc (&env->d_round_stats, 16));
-  CUDA_TRY (cudaMemsetAsync (env->d_round_stats, 0, 16, env->stream));
+  CUDA_TRY (cudaMalloc (&env->d_round_stats, 32));
+  CUDA_TRY (cudaMemsetAsync (env->d_round_stats, 0, 32, env->stream));
   CUDA_TRY (cudaStreamSynchronize (env->stream));
   PStatic &s = env->dps;
   char *b = env->d_ptables;
@@ -970,6 +1020,7 @@ run_parallel (prb_env *env, int64_t until_ns)
       int64_t chunk_end = std::min<int64_t> (target, env->par_front_ns + env->pm.ps.max_chunk_ns);
       a.until_ns = chunk_end >= stop ? std::max<int64_t> (until_ns, stop) : chunk_end;
       if ((rc = launch_par (env, a)) != PRB_OK) return rc;
+      env->par_until_arg = a.until_ns;
       env->par_front_ns = chunk_end;
     }
   while (env->par_front_ns < target);
@@ -984,7 +1035,8 @@ launch_advance_g (prb_env *env, const LaunchArgs &a)
   const Static &st = env->dst;
   const int threads = 128;
   const int envs_per_block = threads / G;
-  const int blocks = (st.E + envs_per_block - 1) / envs_per_block;
+  const int n_envs = a.env_list ? a.n_list : st.E;
+  const int blocks = (n_envs + envs_per_block - 1) / envs_per_block;
   size_t smem = (size_t) envs_per_block * st.blob_bytes;
   /* shared-memory staging pays when the launch executes many events per env (run mode) and the blobs of
    * a block fit; gym-mode launches execute a handful of events and work on the blob in place */
@@ -1049,7 +1101,7 @@ prb_destroy (prb_env *env)
   cudaFree (env->d_flow_first); cudaFree (env->d_counters); cudaFree (env->d_out); cudaFree (env->d_actions);
   cudaFree (env->d_scratch);
   cudaFree (env->d_ptables); cudaFree (env->d_pblob0); cudaFree (env->d_pblobs); cudaFree (env->d_rings);
-  cudaFree (env->d_tr_prev); cudaFree (env->d_round_stats); cudaFree (env->d_qw);
+  cudaFree (env->d_tr_prev); cudaFree (env->d_round_stats); cudaFree (env->d_qw); cudaFree (env->d_tied_list); cudaFree (env->d_tied_flags);
   cudaFree (env->rp.rows); cudaFree (env->rp.cursor); cudaFree (env->rp.pending);
   delete env;
   return PRB_OK;
@@ -1142,6 +1194,78 @@ prb_reset (prb_env *env)
     CUDA_TRY (cudaMemsetAsync (env->rp.pending, 0xFF, sizeof (int32_t) * (size_t) st.E * (size_t) env->rp.pcap * env->rp.PW, env->stream));
   env->engine_active = 0;
   env->par_front_ns = 0;
+  env->tied.clear ();
+  std::fill (env->tied_flag.begin (), env->tied_flag.end (), 0);
+  env->tied_until = 0;
+  if (env->d_round_stats) CUDA_TRY (cudaMemsetAsync (env->d_round_stats + 2, 0, 8, env->stream));
+  return PRB_OK;
+}
+
+/* Environments the parallel engine gave up on (PRB_ERR_TIE: the order of two simultaneous events could not be
+ * rebuilt from local information) are replayed by the event-serial engine, whose global (timestamp, uid) order
+ * needs no such reconstruction.  Their serial state still sits at the episode's reset, so they are advanced
+ * from there to where the parallel launches stand; from then on every read-out first brings them up to date.
+ * Called before anything is read from the environments. */
+static int
+resolve_ties (prb_env *env)
+{
+  if (env->engine_active != PRB_ENGINE_PARALLEL || !env->d_pblobs) return PRB_OK;
+  Static &st = env->dst;
+  if (env->log_on || st.policy == PRB_POLICY_NODE_TRACE) return PRB_OK;   /* parity runs: the flag is reported instead */
+  unsigned long long n = 0;
+  CUDA_TRY (cudaMemcpyAsync (&n, env->d_round_stats + 2, sizeof (n), cudaMemcpyDeviceToHost, env->stream));
+  CUDA_TRY (cudaStreamSynchronize (env->stream));
+  if (n == 0) return PRB_OK;
+  if ((size_t) n != env->tied.size ())
+    {
+      if (!env->d_tied_flags)
+        {
+          CUDA_TRY (cudaMalloc (&env->d_tied_flags, (size_t) st.E));
+          CUDA_TRY (cudaMalloc (&env->d_tied_list, sizeof (int32_t) * (size_t) st.E));
+          env->tied_flag.assign ((size_t) st.E, 0);
+        }
+      k_tied_flags<<<(st.E + 127) / 128, 128, 0, env->stream>>> (st, env->dps, env->d_pblobs, env->d_tied_flags);
+      CUDA_TRY (cudaGetLastError ());
+      std::vector<uint8_t> f ((size_t) st.E);
+      CUDA_TRY (cudaMemcpyAsync (f.data (), env->d_tied_flags, (size_t) st.E, cudaMemcpyDeviceToHost, env->stream));
+      CUDA_TRY (cudaStreamSynchronize (env->stream));
+      /* newcomers first catch up with the others (from the reset state to tied_until), then all move together */
+      std::vector<int32_t> fresh;
+      for (int e = 0; e < st.E; e++)
+        if (f[(size_t) e] && !env->tied_flag[(size_t) e])
+          {
+            fresh.push_back (e);
+            env->tied_flag[(size_t) e] = 1;
+          }
+      if (!fresh.empty () && env->tied_until > 0)
+        {
+          CUDA_TRY (cudaMemcpyAsync (env->d_tied_list, fresh.data (), sizeof (int32_t) * fresh.size (), cudaMemcpyHostToDevice, env->stream));
+          LaunchArgs a;
+          a.blobs = env->d_blobs; a.pools = env->d_pools; a.ev_logs = nullptr; a.st_logs = nullptr;
+          a.actions = nullptr; a.out = nullptr; a.until_ns = env->tied_until;
+          a.qw = nullptr; a.steps = 1; a.eps = 0.0f; a.seed = 0; a.step0 = 0; a.replay = ReplayArgs ();
+          a.env_list = env->d_tied_list; a.n_list = (int32_t) fresh.size ();
+          st.mode = MODE_RUN;
+          int rc = launch_advance (env, a);
+          if (rc != PRB_OK) return rc;
+          CUDA_TRY (cudaStreamSynchronize (env->stream));
+        }
+      env->tied.insert (env->tied.end (), fresh.begin (), fresh.end ());
+      CUDA_TRY (cudaMemcpyAsync (env->d_tied_list, env->tied.data (), sizeof (int32_t) * env->tied.size (), cudaMemcpyHostToDevice, env->stream));
+      CUDA_TRY (cudaStreamSynchronize (env->stream));
+    }
+  if (env->tied_until != env->par_until_arg)
+    {
+      LaunchArgs a;
+      a.blobs = env->d_blobs; a.pools = env->d_pools; a.ev_logs = nullptr; a.st_logs = nullptr;
+      a.actions = nullptr; a.out = nullptr; a.until_ns = env->par_until_arg;
+      a.qw = nullptr; a.steps = 1; a.eps = 0.0f; a.seed = 0; a.step0 = 0; a.replay = ReplayArgs ();
+      a.env_list = env->d_tied_list; a.n_list = (int32_t) env->tied.size ();
+      st.mode = MODE_RUN;
+      int rc = launch_advance (env, a);
+      if (rc != PRB_OK) return rc;
+      env->tied_until = env->par_until_arg;
+    }
   return PRB_OK;
 }
 
@@ -1174,6 +1298,14 @@ prb_round_stats (prb_env *env, int64_t *rounds, int64_t *executed)
   if (rounds) *rounds = (int64_t) h[0];
   if (executed) *executed = (int64_t) h[1];
   return PRB_OK;
+}
+
+int
+prb_handovers (prb_env *env)
+{
+  if (!env) return PRB_EINVAL;
+  int rc = resolve_ties (env);
+  return rc != PRB_OK ? rc : (int) env->tied.size ();
 }
 
 int prb_num_links (prb_env *env) { return env ? env->dst.L : PRB_EINVAL; }
@@ -1381,7 +1513,7 @@ prb_run (prb_env *env, int64_t until_ns)
   LaunchArgs a;
   a.blobs = env->d_blobs; a.pools = env->d_pools; a.ev_logs = env->d_ev; a.st_logs = env->d_st;
   a.actions = nullptr; a.out = nullptr; a.until_ns = until_ns;
-  a.qw = nullptr; a.steps = 1; a.eps = 0.0f; a.seed = 0; a.step0 = 0; a.replay = ReplayArgs ();
+  a.qw = nullptr; a.steps = 1; a.eps = 0.0f; a.seed = 0; a.step0 = 0; a.replay = ReplayArgs (); a.env_list = nullptr; a.n_list = 0;
   return launch_advance (env, a);
 }
 
@@ -1398,7 +1530,7 @@ prb_step (prb_env *env, const int32_t *actions_dev, prb_step_rec *out_dev)
   LaunchArgs a;
   a.blobs = env->d_blobs; a.pools = env->d_pools; a.ev_logs = env->d_ev; a.st_logs = env->d_st;
   a.actions = actions_dev; a.out = out_dev; a.until_ns = st.sim_time_ns;
-  a.qw = nullptr; a.steps = 1; a.eps = 0.0f; a.seed = 0; a.step0 = 0; a.replay = ReplayArgs ();
+  a.qw = nullptr; a.steps = 1; a.eps = 0.0f; a.seed = 0; a.step0 = 0; a.replay = ReplayArgs (); a.env_list = nullptr; a.n_list = 0;
   return launch_advance (env, a);
 }
 
@@ -1556,6 +1688,7 @@ prb_step_qnet (prb_env *env, int32_t n_steps, float eps, uint64_t seed, prb_step
       a.blobs = env->d_blobs; a.pools = env->d_pools; a.ev_logs = env->d_ev; a.st_logs = env->d_st;
       a.actions = nullptr; a.out = out_dev; a.until_ns = st.sim_time_ns;
       a.qw = env->d_qw; a.steps = n_steps; a.eps = eps; a.seed = seed; a.step0 = env->q_step; a.replay = env->rp;
+      a.env_list = nullptr; a.n_list = 0;
       env->q_step += (uint64_t) n_steps;
       return launch_advance (env, a);
     }
@@ -1575,8 +1708,15 @@ prb_counters_dev (prb_env *env, prb_counters *out_dev)
   if (!env || !out_dev) return fail (PRB_EINVAL, "null argument");
   CUDA_TRY (cudaSetDevice (env->device));
   const Static &st = env->dst;
+  int rc = resolve_ties (env);
+  if (rc != PRB_OK) return rc;
   if (env->engine_active == PRB_ENGINE_PARALLEL)
-    k_counters_par<<<(st.E + 127) / 128, 128, 0, env->stream>>> (st, env->dps, env->d_pblobs, out_dev);
+    {
+      k_counters_par<<<(st.E + 127) / 128, 128, 0, env->stream>>> (st, env->dps, env->d_pblobs, out_dev);
+      if (!env->tied.empty ())
+        k_counters_list<<<((int) env->tied.size () + 127) / 128, 128, 0, env->stream>>> (st, env->d_blobs, env->d_tied_list, (int) env->tied.size (),
+                                                                                       out_dev);
+    }
   else
     k_counters<<<(st.E + 127) / 128, 128, 0, env->stream>>> (st, env->d_blobs, out_dev);
   CUDA_TRY (cudaGetLastError ());
@@ -1603,7 +1743,9 @@ prb_queue_bytes (prb_env *env, int32_t e, int32_t *out)
   const Static &st = env->dst;
   if (e < 0 || e >= st.E) return fail (PRB_EINVAL, "env index out of range");
   if (st.L > 1000) return fail (PRB_EINVAL, "too many links for the scratch buffer");
-  if (env->engine_active == PRB_ENGINE_PARALLEL)
+  int rc = resolve_ties (env);
+  if (rc != PRB_OK) return rc;
+  if (env->engine_active == PRB_ENGINE_PARALLEL && !(e < (int) env->tied_flag.size () && env->tied_flag[(size_t) e]))
     k_queue_bytes_par<<<(st.L + 127) / 128, 128, 0, env->stream>>> (st, env->dps, env->d_pblobs, e, (int32_t *) env->d_scratch);
   else
     k_queue_bytes<<<(st.L + 127) / 128, 128, 0, env->stream>>> (st, env->d_blobs, e, (int32_t *) env->d_scratch);

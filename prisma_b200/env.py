@@ -168,6 +168,13 @@ class BatchedRoutingEnv:
         _abi.check(self.lib.prb_round_stats(self.h, C.byref(a), C.byref(b)))
         return a.value, b.value
 
+    def handovers(self) -> int:
+        """Environments the node-parallel engine handed over to the event-serial engine in this episode."""
+        n = self.lib.prb_handovers(self.h)
+        if n < 0:
+            _abi.check(n)
+        return int(n)
+
     # ---- stepping ----
     def run(self, until_s: Optional[float] = None, until_ns: Optional[int] = None):
         if until_ns is None:

@@ -177,3 +177,45 @@ def test_drop_heavy_100_nodes_four_nodes_per_lane():
         x, y = res["serial"][k].astype(np.float64), res["parallel"][k].astype(np.float64)
         assert np.all(np.abs(x - y) <= 1e-6 * np.maximum(np.abs(x), 1e-30)), k
     assert int(res["parallel"]["overlay_lost"].sum()) > 0
+
+
+HANDOVER = [
+    # GEANT at load 1.5 (full queues, long lock-step chains after the ping rounds): in environment 1558 two arrivals
+    # at one node fall into the same nanosecond with identical 6-generation histories
+    ("geant", dict(load_factor=1.5), 1600, (0.5, 1.0, 1.5), 1558),
+    # small signalling packets: in environment 2853 a queue holds more records than the link ring has slots
+    ("abilene", dict(load_factor=0.9, train=1, signaling_type="target", agent_type="dqn_buffer"), 2900, (1.0, 2.0), 2853),
+]
+
+
+@pytest.mark.parametrize("topo,over,num_envs,times,probe", HANDOVER)
+def test_handover_to_the_serial_engine(topo, over, num_envs, times, probe):
+    """What the parallel engine cannot finish exactly (an undecided order of simultaneous events, a full link
+    ring) is replayed by the serial engine: every counter of every environment still equals the serial run, at
+    every read-out."""
+    cfg = common.env_config(topo, num_envs=num_envs, simTime=times[-1], pingAsObs=0, activateUnderlayTraffic=1, **over)
+    arrays = cfg.load()
+    table = common.sp_table(arrays)
+    res = {}
+    for mode in ("serial", "parallel"):
+        env = make_env(cfg, arrays=arrays)
+        env.set_engine(mode)
+        env.set_policy("table", table)
+        out = []
+        for t in times:
+            env.run(until_s=t)
+            cs = env.counters()
+            env.check_errors(cs)
+            out.append((cs, env.queue_bytes(probe), env.queue_bytes(7)))
+        if mode == "parallel":
+            assert env.engine == "parallel"
+            assert env.handovers() >= 1
+        res[mode] = out
+        env.close()
+    for (a, qa, ra), (b, qb, rb) in zip(res["serial"], res["parallel"]):
+        for k in common.COUNTER_INTS:
+            assert np.array_equal(a[k], b[k]), k
+        for k in common.COUNTER_FLOATS:
+            x, y = a[k].astype(np.float64), b[k].astype(np.float64)
+            assert np.all(np.abs(x - y) <= 1e-6 * np.maximum(np.abs(x), 1e-30)), k
+        assert np.array_equal(qa, qb) and np.array_equal(ra, rb)
