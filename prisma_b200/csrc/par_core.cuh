@@ -24,8 +24,9 @@
  * by the rules that cover the systematic cases (ping rounds: every ping timer fires at the same instant,
  * in overlay-index order, and sends tunnel by tunnel, data-packet-manager.cc:349-357; TransmitComplete is
  * scheduled before the peer's Receive, point-to-point-net-device.cc:295-296).  A tie that none of these
- * decides sets PRB_ERR_TIE: the run is then not claimed to be in ns-3's order (it never happened in the
- * test-suite; two unrelated events would have to coincide to the nanosecond twice in a row).
+ * decides sets PRB_ERR_TIE: the kernel abandons the environment and the host has the event-serial engine
+ * replay it (prisma_b200.cu: resolve_ties).  It takes lock-step chains longer than the recorded history
+ * (full queues after a ping round) or two unrelated events that coincide to the nanosecond twice in a row.
  *
  * float32 statistics.  The reference re-sums float vectors front to back (compute-stats-v2.cc:87-97), so
  * the sums depend on the global order of deliveries and drops.  Nodes append (ts, value) records to a small
