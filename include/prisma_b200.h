@@ -83,6 +83,11 @@ typedef struct prb_config
   uint64_t env_id_base;            /* synthetic traffic: id of env 0 (env e draws stream env_id_base+e)  */
   int32_t pool_capacity;           /* packet records per env, 0 = derive from the topology              */
   int32_t lanes_per_env;           /* 0 = default (32: one warp per environment)                        */
+  /* NN-weight segments between overlay neighbours (BigSignalingGeneratorApplication): one source per directed
+   * overlay edge that carries traffic when train && signaling && signaling_type == NN; all zero = none */
+  int32_t signaling;               /* activateSignaling after sim.cc:374-376 (signalingSim, not sp/opt/ideal) */
+  uint32_t big_signaling_size;     /* bigSignalingSize, bytes                            sim.cc:144,641 */
+  double sync_step;                /* syncStep, seconds                                  sim.cc:143,641 */
 } prb_config;
 
 /* one record of the parity event log (same vocabulary as the reference harness) — 64 bytes */
@@ -103,7 +108,8 @@ typedef struct prb_event
 typedef struct prb_step_rec
 {
   int64_t t_ns;         /*   0 simulated time of the step                                              */
-  int64_t uid;          /*   8 data: packet uid; small signalling: uid it reports; else -1              */
+  int64_t uid;          /*   8 data: packet uid; small signalling: uid it reports; big signalling:
+                               NNIndex << 32 | segIndex (big-signaling-packet-manager.cc:104-121)        */
   double hop_time;      /*  16 now - time of the packet's previous decision, s (forwarder.py:360)       */
   int32_t node;         /*  24 underlay id of the stepping overlay node                                 */
   int32_t overlay;      /*  28 its overlay index == the reference's per-node env index                  */
@@ -113,7 +119,8 @@ typedef struct prb_step_rec
   int32_t need_action;  /*  44 1: prb_step consumes actions_dev[e] for this record                      */
   int32_t nobs;         /*  48                                                                          */
   int32_t is_new;       /*  52 first time the agents see this packet (forwarder.py:316-317)             */
-  int32_t prev_node;    /*  56 underlay id of the previous decision maker, -1 if new                    */
+  int32_t prev_node;    /*  56 underlay id of the previous decision maker, -1 if new; big signalling: the
+                               node whose weights the segment carries ("NodeId Signaled" = its overlay index) */
   int32_t n_lost;       /*  60 lost uids flushed with this step (data-packet-manager.cc:229-237)        */
   float e2e_delay;      /*  64 info field 0 (packet-manager.cc:121-122)                                 */
   int32_t valid;        /*  68 1: this env produced a step; 0: it reached simTime (obs[0] == -1 sentinel) */
@@ -179,6 +186,11 @@ int prb_state_bytes (prb_env *env, int64_t *blob_bytes, int64_t *pool_bytes);
 /* traffic: recorded injections shared by every env (replay), or NULL/0 to go back to Philox */
 int prb_set_inject_trace (prb_env *env, int64_t n, const int64_t *t_ns, const int32_t *src, const int32_t *dst,
                           const int64_t *uid, const uint8_t *valable, const uint8_t *rejected);
+/* the same with the packet type of every injection (PRB_DATA, or PRB_BIG_SIGN for the segments of
+ * big-signaling-application.cc:261-306); ptype == NULL: all data */
+int prb_set_inject_trace_typed (prb_env *env, int64_t n, const int64_t *t_ns, const int32_t *src, const int32_t *dst,
+                                const int64_t *uid, const uint8_t *valable, const uint8_t *rejected,
+                                const uint8_t *ptype);
 /* agent hook evaluated on the device: TABLE data[M*M] (row = stepping overlay node, column = obs[0]);
  * TRACE data[n] actions in decision order; RANDOM uses seed (+ env index); NODE_TRACE data = [M+1 offsets]
  * [actions of overlay node 0][of node 1]...: every node replays its own decisions (parallel engine) */

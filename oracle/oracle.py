@@ -31,6 +31,7 @@ class PoConfig(C.Structure):
         ("signaling_type", C.c_int32), ("opt_agent", C.c_int32),
         ("loss_penalty", C.c_double), ("inject_mode", C.c_int32),
         ("seed", C.c_uint64), ("env_id", C.c_uint64),
+        ("signaling", C.c_int32), ("big_signaling_size", C.c_uint32), ("sync_step", C.c_double),
     ]
 
 
@@ -98,6 +99,8 @@ def lib():
         L.po_set_inject_trace.argtypes = [C.c_void_p, C.c_int64, C.POINTER(C.c_int64), C.POINTER(C.c_int32),
                                           C.POINTER(C.c_int32), C.POINTER(C.c_int64), C.POINTER(C.c_uint8),
                                           C.POINTER(C.c_uint8)]
+        L.po_set_inject_trace_typed.restype = C.c_int32
+        L.po_set_inject_trace_typed.argtypes = L.po_set_inject_trace.argtypes + [C.POINTER(C.c_uint8)]
         L.po_set_policy.argtypes = [C.c_void_p, C.c_int32, C.POINTER(C.c_int32), C.c_int64, C.c_uint64]
         L.po_run.argtypes = [C.c_void_p, C.c_int64]
         L.po_get_counters.argtypes = [C.c_void_p, C.POINTER(PoCounters)]
@@ -197,11 +200,12 @@ class OracleSim:
             cfg.opt_rejected = r
         for k in ("link_rate_bps", "link_delay_ns", "packet_size", "max_out_buffer_size", "sim_time_ns",
                   "ping_interval_ns", "moving_average_size", "ping_as_obs", "activate_underlay_traffic",
-                  "train", "opt_agent", "inject_mode", "seed", "env_id"):
+                  "train", "opt_agent", "inject_mode", "seed", "env_id", "signaling", "big_signaling_size"):
             setattr(cfg, k, int(p.get(k, 0)))
         st = p.get("signaling_type", 0)
         cfg.signaling_type = SIGNALING[st] if isinstance(st, str) else int(st)
         cfg.loss_penalty = float(p.get("loss_penalty", 0.0))
+        cfg.sync_step = float(p.get("sync_step", 0.0))
         self.cfg = cfg
         self.h = lib().po_create(C.byref(cfg))
         lib().po_set_event_log(self.h, 1 if log_events else 0)
@@ -217,13 +221,17 @@ class OracleSim:
         except Exception:
             pass
 
-    def set_inject_trace(self, t_ns, src, dst, uid, valable, rejected):
+    def set_inject_trace(self, t_ns, src, dst, uid, valable, rejected, ptype=None):
+        """ptype: packet type of every injection (0 data, 1 big signalling); None = all data."""
         a = [np.ascontiguousarray(t_ns, dtype=np.int64), np.ascontiguousarray(src, dtype=np.int32),
              np.ascontiguousarray(dst, dtype=np.int32), np.ascontiguousarray(uid, dtype=np.int64),
              np.ascontiguousarray(valable, dtype=np.uint8), np.ascontiguousarray(rejected, dtype=np.uint8)]
-        rc = lib().po_set_inject_trace(self.h, len(a[0]), _p(a[0], C.c_int64), _p(a[1], C.c_int32),
-                                       _p(a[2], C.c_int32), _p(a[3], C.c_int64), _p(a[4], C.c_uint8),
-                                       _p(a[5], C.c_uint8))
+        if ptype is None:
+            ptype = np.zeros(len(a[0]), dtype=np.uint8)
+        a.append(np.ascontiguousarray(ptype, dtype=np.uint8))
+        rc = lib().po_set_inject_trace_typed(self.h, len(a[0]), _p(a[0], C.c_int64), _p(a[1], C.c_int32),
+                                             _p(a[2], C.c_int32), _p(a[3], C.c_int64), _p(a[4], C.c_uint8),
+                                             _p(a[5], C.c_uint8), _p(a[6], C.c_uint8))
         if rc != 0:
             raise ValueError("injection trace names a flow that the configuration does not have")
 

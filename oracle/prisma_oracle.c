@@ -320,6 +320,7 @@ typedef struct po_pkt
   float one_hop_delay;    /* ping back */
   uint32_t ping_idx, tunnel_idx;
   int64_t pkt_id;         /* small signalling: uid of the data packet it reports */
+  uint32_t seg_index, nn_index; /* big signalling: m_segIndex / m_NNIndex (big-signaling-application.cc:241-246,276-277) */
   /* restated Python bookkeeping: Agent.temp_obs / pkt_tracking_dict (forwarder.py:153-159,334-350) */
   int32_t tracked;
   int32_t prev_node;
@@ -356,6 +357,8 @@ typedef struct
   uint64_t bps;
   double mean_s;
   uint64_t n_draw;        /* Philox draw ordinal */
+  int32_t big;            /* 1: BigSignalingGeneratorApplication (fixed gap), 0: Poisson source */
+  uint32_t seg_index, nn_index;
   int64_t trace_pos;      /* replay: index of this flow's next injection in the trace */
 } po_flow;
 
@@ -390,6 +393,8 @@ struct po_sim
   po_agent *agents;
   po_flow *flows; int32_t F;
   int32_t *flow_of;       /* [N*N] flow index or -1 */
+  int32_t *big_flow_of;   /* [N*N] big-signalling source index or -1 */
+  int64_t big_start_ns, big_gap_ns; uint32_t big_segs;
   double *opt_rejected;
   /* scheduler */
   po_hev *heap; int64_t heap_n, heap_cap;
@@ -767,6 +772,12 @@ agent_control_step (po_sim *s, int m, po_pkt *p)
   po_decision *d = new_decision (s);
   d->t_ns = s->now; d->node = a->node; d->overlay = m; d->uid = p->type == PO_SMALL_SIGN ? p->pkt_id : -1;
   d->ptype = p->type; d->nobs = 1; d->obs[0] = 1000; d->action = -1; d->prev_node = -1;
+  if (p->type == PO_BIG_SIGN)
+    {
+      /* info fields 18-20: NN Index, segment Index, NodeId Signaled (big-signaling-packet-manager.cc:104-121) */
+      d->uid = (int64_t) (((uint64_t) p->nn_index << 32) | p->seg_index);
+      d->prev_node = p->src;
+    }
   /* GetGameOver asks the DATA manager, whose m_destination still holds the last data packet seen at
    * this node (packet-routing-gym.cc:142-147, data-packet-manager.cc:224-227) */
   d->done = a->last_data_dst == a->node;
@@ -957,6 +968,23 @@ inject (po_sim *s, int f)
 {
   po_flow *fl = &s->flows[f];
   po_pkt *p = (po_pkt *) calloc (1, sizeof (po_pkt));
+  if (fl->big)
+    {
+      /* BigSignalingGeneratorApplication::SendPacket — big-signaling-application.cc:261-306: one 512-byte
+       * segment of the NN weights, addressed to the neighbour's traffic node, never a routed-by-agent packet */
+      p->type = PO_BIG_SIGN;
+      p->valable = 0; p->rejected = 0;
+      p->dst = fl->dst; p->src = fl->src; p->next_hop = fl->dst; p->last_hop = PO_LASTHOP_NONE;
+      p->seg_index = fl->seg_index; p->nn_index = fl->nn_index;
+      p->uid = -1;
+      p->birth_ns = s->now;
+      p->size = 512 + 8 + 20 + 2;
+      p->first_hop = 0;
+      p->ipdst = fl->dst;
+      dev_send (s, s->L + fl->src, p);
+      schedule_flow (s, f, 0);
+      return;
+    }
   p->type = PO_DATA;
   p->dst = fl->dst; p->src = fl->src; p->next_hop = fl->src; p->last_hop = PO_LASTHOP_NONE;
   p->start = (uint64_t) po_ns_to_seconds (s->now);
@@ -995,11 +1023,23 @@ static void
 schedule_flow (po_sim *s, int f, int first)
 {
   po_flow *fl = &s->flows[f];
+  if (fl->big)
+    {
+      /* BigSignalingGeneratorApplication::ScheduleNextTx — big-signaling-application.cc:236-258
+       * (StartApplication :223-232 zeroes both indices and calls it at AppStartTime, sim.cc:644) */
+      fl->seg_index++;
+      if (fl->seg_index >= s->big_segs) { fl->nn_index++; fl->seg_index = 0; }
+    }
   if (s->cfg.inject_mode == PO_INJECT_TRACE)
     {
       int64_t i = first ? fl->trace_pos : s->tr_next[fl->trace_pos];
       fl->trace_pos = i;
       if (i >= 0) heap_push (s, s->tr_t[i], EVK_INJ, f, 0);
+      return;
+    }
+  if (fl->big)
+    {
+      heap_push (s, (first ? s->big_start_ns : s->now) + s->big_gap_ns, EVK_INJ, f, 0);
       return;
     }
   uint32_t key[2] = { (uint32_t) s->cfg.seed, (uint32_t) (s->cfg.seed >> 32) };
@@ -1153,6 +1193,32 @@ po_create (const po_config *cfg)
             s->flow_of[i * N + j] = s->F++;
           }
       }
+  /* NN-weight segment sources, one per directed overlay edge that also carries traffic — sim.cc:634-647.
+   * They are kept after the Poisson sources; among themselves they keep the (i, j) creation order, which is
+   * the order of their simultaneous SendPacket events. */
+  s->big_flow_of = (int32_t *) malloc (sizeof (int32_t) * N * N);
+  for (int i = 0; i < N * N; i++) s->big_flow_of[i] = -1;
+  if (cfg->train && cfg->signaling && cfg->signaling_type == 1 && cfg->big_signaling_size >= 512 && cfg->sync_step > 0)
+    {
+      /* big-signaling-application.cc:247-250: uint32 * 8 / float -> float, widened; uint32 512*8 / double */
+      float sync = (float) cfg->sync_step;
+      double rate = (double) ((float) (uint32_t) (cfg->big_signaling_size * 8u) / sync);
+      s->big_gap_ns = po_seconds_to_ns ((double) (512u * 8u) / rate);
+      s->big_start_ns = po_seconds_to_ns (0.0001);                 /* AppStartTime, sim.cc:244,644 */
+      s->big_segs = cfg->big_signaling_size / 512u;                /* :243 */
+      int nf = s->F;
+      s->flows = (po_flow *) realloc (s->flows, sizeof (po_flow) * (size_t) (2 * N * N));
+      memset (s->flows + nf, 0, sizeof (po_flow) * (size_t) (2 * N * N - nf));
+      for (int i = 0; i < N; i++)
+        for (int j = 0; j < N; j++)
+          {
+            int mi = s->map_overlay[i], mj = s->map_overlay[j];
+            if (s->flow_of[i * N + j] < 0 || mi < 0 || mj < 0 || cfg->overlay_adj[mi * M + mj] != 1) continue;
+            po_flow *fl = &s->flows[s->F];
+            fl->src = i; fl->dst = j; fl->big = 1; fl->trace_pos = -1;
+            s->big_flow_of[i * N + j] = s->F++;
+          }
+    }
   s->policy = PO_POLICY_ZERO;
   return s;
 }
@@ -1170,7 +1236,7 @@ po_destroy (po_sim *s)
       free (s->agents[m].lost);
     }
   free (s->links); free (s->route); free (s->map_overlay); free (s->o2u); free (s->degree);
-  free (s->agents); free (s->flows); free (s->flow_of); free (s->opt_rejected); free (s->heap);
+  free (s->agents); free (s->flows); free (s->flow_of); free (s->big_flow_of); free (s->opt_rejected); free (s->heap);
   free (s->tr_t); free (s->tr_src); free (s->tr_dst); free (s->tr_uid); free (s->tr_val); free (s->tr_rej); free (s->tr_next);
   free (s->pol_data); free (s->ev); free (s->dec);
   free (s);
@@ -1182,6 +1248,13 @@ int32_t
 po_set_inject_trace (po_sim *s, int64_t n, const int64_t *t_ns, const int32_t *src, const int32_t *dst,
                      const int64_t *uid, const uint8_t *valable, const uint8_t *rejected)
 {
+  return po_set_inject_trace_typed (s, n, t_ns, src, dst, uid, valable, rejected, 0);
+}
+
+int32_t
+po_set_inject_trace_typed (po_sim *s, int64_t n, const int64_t *t_ns, const int32_t *src, const int32_t *dst,
+                           const int64_t *uid, const uint8_t *valable, const uint8_t *rejected, const uint8_t *ptype)
+{
   s->tr_n = n;
   s->tr_t = (int64_t *) malloc (sizeof (int64_t) * (n + 1)); memcpy (s->tr_t, t_ns, sizeof (int64_t) * n);
   s->tr_src = (int32_t *) malloc (sizeof (int32_t) * (n + 1)); memcpy (s->tr_src, src, sizeof (int32_t) * n);
@@ -1191,14 +1264,17 @@ po_set_inject_trace (po_sim *s, int64_t n, const int64_t *t_ns, const int32_t *s
   s->tr_rej = (uint8_t *) malloc (n + 1); memcpy (s->tr_rej, rejected, n);
   s->tr_next = (int64_t *) malloc (sizeof (int64_t) * (n + 1));
   /* per-flow chains: each SendPacket schedules the flow's next one (poisson-application.cc:357) */
-  int64_t *last = (int64_t *) malloc (sizeof (int64_t) * s->N * s->N);
-  for (int i = 0; i < s->N * s->N; i++) last[i] = -1;
+  int NN = s->N * s->N;
+  int64_t *last = (int64_t *) malloc (sizeof (int64_t) * 2 * NN);
+  for (int i = 0; i < 2 * NN; i++) last[i] = -1;
   for (int64_t i = 0; i < n; i++)
     {
       s->tr_next[i] = -1;
+      int big = ptype && ptype[i] == PO_BIG_SIGN;
       int key = src[i] * s->N + dst[i];
-      int f = s->flow_of[key];
-      if (f < 0) { free (last); return -1; }
+      int f = big ? s->big_flow_of[key] : s->flow_of[key];
+      if (f < 0 || (ptype && ptype[i] != PO_DATA && !big)) { free (last); return -1; }
+      key += big ? NN : 0;
       if (last[key] >= 0) s->tr_next[last[key]] = i; else s->flows[f].trace_pos = i;
       last[key] = i;
     }

@@ -63,6 +63,11 @@ typedef struct po_config
   int32_t inject_mode;             /* PO_INJECT_*                                            */
   uint64_t seed;                   /* PO_INJECT_PHILOX: stream key                           */
   uint64_t env_id;                 /* PO_INJECT_PHILOX: which environment of the batch       */
+  /* NN-weight segments between overlay neighbours (train && signaling && signalingType=="NN"):
+   * sim.cc:634-647, big-signaling-application.cc:223-310.  All zero = no such sources. */
+  int32_t signaling;               /* activateSignaling after sim.cc:374-376                 */
+  uint32_t big_signaling_size;     /* bigSignalingSize, bytes                sim.cc:144      */
+  double sync_step;                /* syncStep, seconds                      sim.cc:143      */
 } po_config;
 
 typedef struct po_event
@@ -82,7 +87,7 @@ typedef struct po_decision
   int64_t t_ns;
   int32_t node;       /* underlay id of the overlay node stepping */
   int32_t overlay;    /* overlay index (the Gym interface index)  */
-  int64_t uid;
+  int64_t uid;        /* data: packet uid; small signalling: uid it reports; big signalling: NNIndex << 32 | segIndex */
   int32_t ptype;
   int32_t done;
   int32_t action;     /* -1 when the Forwarder ignores the policy (forwarder.py:149-150) */
@@ -90,7 +95,7 @@ typedef struct po_decision
   int32_t obs[1 + PO_MAX_K];
   /* restated Forwarder bookkeeping (forwarder.py:334-379) */
   int32_t is_new;     /* first time the agents see this packet */
-  int32_t prev_node;  /* underlay id of the previous decision maker, -1 if new */
+  int32_t prev_node;  /* underlay id of the previous decision maker, -1 if new; big signalling: the signalling node */
   double hop_time;    /* now - time of previous decision, seconds (exact ns difference) */
   float e2e_delay;    /* info field 0: now_s - start_s (packet-manager.cc:121-122) */
   int32_t n_lost;     /* lost uids flushed with this step (data-packet-manager.cc:229-237) */
@@ -135,6 +140,10 @@ void po_destroy (po_sim *s);
 void po_set_event_log (po_sim *s, int32_t enable);
 int32_t po_set_inject_trace (po_sim *s, int64_t n, const int64_t *t_ns, const int32_t *src, const int32_t *dst,
                              const int64_t *uid, const uint8_t *valable, const uint8_t *rejected);
+/* the same with the packet type of every injection (PO_DATA / PO_BIG_SIGN); ptype == NULL: all data */
+int32_t po_set_inject_trace_typed (po_sim *s, int64_t n, const int64_t *t_ns, const int32_t *src, const int32_t *dst,
+                                   const int64_t *uid, const uint8_t *valable, const uint8_t *rejected,
+                                   const uint8_t *ptype);
 int32_t po_set_policy (po_sim *s, int32_t kind, const int32_t *data, int64_t n, uint64_t seed);
 int32_t po_run (po_sim *s, int64_t until_ns);
 void po_get_counters (po_sim *s, po_counters *out);

@@ -40,6 +40,7 @@ class PrbConfig(C.Structure):
         ("signaling_type", C.c_int32), ("opt_agent", C.c_int32),
         ("loss_penalty", C.c_double), ("seed", C.c_uint64), ("env_id_base", C.c_uint64),
         ("pool_capacity", C.c_int32), ("lanes_per_env", C.c_int32),
+        ("signaling", C.c_int32), ("big_signaling_size", C.c_uint32), ("sync_step", C.c_double),
     ]
 
 
@@ -117,6 +118,9 @@ def fill_config(cfg_struct, keep, p):
     stype = p.get("signaling_type", 0)
     cfg_struct.signaling_type = SIGNALING[stype] if isinstance(stype, str) else int(stype)
     cfg_struct.loss_penalty = float(p.get("loss_penalty", 0.0))
+    cfg_struct.signaling = int(p.get("signaling", 0))
+    cfg_struct.big_signaling_size = int(p.get("big_signaling_size", 0))
+    cfg_struct.sync_step = float(p.get("sync_step", 0.0))
     return cfg_struct
 
 
@@ -148,6 +152,8 @@ def lib():
         "prb_state_bytes": (C.c_int, [vp, C.POINTER(i64), C.POINTER(i64)]),
         "prb_set_inject_trace": (C.c_int, [vp, i64, C.POINTER(i64), C.POINTER(i32), C.POINTER(i32), C.POINTER(i64),
                                            C.POINTER(C.c_uint8), C.POINTER(C.c_uint8)]),
+        "prb_set_inject_trace_typed": (C.c_int, [vp, i64, C.POINTER(i64), C.POINTER(i32), C.POINTER(i32), C.POINTER(i64),
+                                                 C.POINTER(C.c_uint8), C.POINTER(C.c_uint8), C.POINTER(C.c_uint8)]),
         "prb_set_policy": (C.c_int, [vp, C.c_int, C.POINTER(i32), i64, u64]),
         "prb_enable_log": (C.c_int, [vp, i64, i64]),
         "prb_read_events": (C.c_int, [vp, i32, vp, i64, C.POINTER(i64)]),
@@ -184,7 +190,7 @@ def lib():
 
 EXPORTS = ["prb_last_error", "prb_version", "prb_seconds_to_ns", "prb_ns_to_seconds", "prb_tx_time_ns",
            "prb_build_links", "prb_global_routes", "prb_create", "prb_destroy", "prb_reset", "prb_num_links",
-           "prb_state_bytes", "prb_set_inject_trace", "prb_set_policy", "prb_enable_log", "prb_read_events",
+           "prb_state_bytes", "prb_set_inject_trace", "prb_set_inject_trace_typed", "prb_set_policy", "prb_enable_log", "prb_read_events",
            "prb_read_steps", "prb_run", "prb_step", "prb_step_host", "prb_counters_host", "prb_counters_dev",
            "prb_queue_bytes", "prb_sync", "prb_launch_count", "prb_set_engine", "prb_engine", "prb_round_stats", "prb_handovers",
            "prb_qnet_num_floats", "prb_qnet_load", "prb_qnet_act", "prb_step_qnet",

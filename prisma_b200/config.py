@@ -222,7 +222,9 @@ class EnvConfig:
                  moving_average_size=int(self.movingAverageObsSize), ping_as_obs=int(self.pingAsObs),
                  activate_underlay_traffic=int(self.activateUnderlayTraffic), train=int(self.train),
                  signaling_type=self.signaling_type, opt_agent=1 if self.agent_type == "opt" else 0,
-                 loss_penalty=self.derived_loss_penalty(a.n_overlay), seed=int(self.seed), env_id_base=0)
+                 loss_penalty=self.derived_loss_penalty(a.n_overlay), seed=int(self.seed), env_id_base=0,
+                 signaling=int(self.effective_signaling()), big_signaling_size=int(self.bigSignalingSize),
+                 sync_step=float(self.sync_step))
         p.update(over)
         return p
 

@@ -132,6 +132,7 @@ struct HostModel
   std::vector<uint16_t> szc_bytes;
   std::vector<double> flow_mean_s, opt_rejected;
   std::vector<int32_t> flow_of, flow_first;      /* flow_of: [N*N] flow index or -1 (host only) */
+  std::vector<int32_t> big_flow_of;              /* [N*N] NN-segment source index or -1 (host only) */
   std::vector<char> blob0;                       /* initial state of one environment */
   std::string error;
 };
@@ -303,7 +304,54 @@ build_model (const prb_config &c, HostModel &hm)
               }
           }
       }
+  const int FP = (int) hm.flow_src.size ();
+  /* NN-weight segment sources (sim.cc:634-647): one per directed overlay edge that carries traffic, created next
+   * to the Poisson source of the same pair.  They are kept after the Poisson sources; among themselves they keep
+   * the (i, j) creation order, which is the order of their simultaneous SendPacket events. */
+  hm.big_flow_of.assign ((size_t) N * N, -1);
+  int big_szc = 0;
+  if (c.train && c.signaling && c.signaling_type == 1 && c.big_signaling_size >= 512 && c.sync_step > 0)
+    {
+      for (int i = 0; i < N; i++)
+        for (int j = 0; j < N; j++)
+          {
+            int mi = c.map_overlay[i], mj = c.map_overlay[j];
+            if (hm.flow_of[(size_t) i * N + j] < 0 || mi < 0 || mj < 0 || c.overlay_adj[mi * M + mj] != 1) continue;
+            hm.big_flow_of[(size_t) i * N + j] = (int32_t) hm.flow_src.size ();
+            hm.flow_src.push_back ((int16_t) i);
+            hm.flow_dst.push_back ((int16_t) j);
+            hm.flow_mean_s.push_back (0.0);
+          }
+      /* big-signaling-application.cc:247-250: uint32 * 8 / float -> float, widened; uint32 512 * 8 / double */
+      float sync = (float) c.sync_step;
+      double rate = (double) ((float) (uint32_t) (c.big_signaling_size * 8u) / sync);
+      st.big_gap_ns = host_seconds_to_ns ((double) (512u * 8u) / rate);
+      st.big_start_ns = host_seconds_to_ns (0.0001);                        /* AppStartTime, sim.cc:244,644 */
+      st.big_segs = (int32_t) (c.big_signaling_size / 512u);                /* :243 */
+      const uint16_t wire = 512 + 30;
+      big_szc = SZC_SIGN0;
+      while (big_szc < n_szc && hm.szc_bytes[big_szc] != wire) big_szc++;
+      if (big_szc == n_szc)
+        {
+          if (n_szc == MAX_SZC)
+            {
+              hm.error = "too many distinct signalling sizes";
+              return false;
+            }
+          hm.szc_bytes[n_szc++] = wire;
+          for (size_t r = 0; r < rates.size (); r++)
+            hm.tx_ns[r * MAX_SZC + big_szc] = host_tx_time_ns (wire, rates[r]);
+        }
+      if (st.big_gap_ns <= 0)
+        {
+          hm.error = "sync_step / bigSignalingSize give a zero gap between NN segments";
+          return false;
+        }
+    }
+  st.big_szc = big_szc;
+  if (st.big_segs < 1) st.big_segs = 1;
   const int F = (int) hm.flow_src.size ();
+  st.FP = FP;
   hm.flow_first.assign (std::max (F, 1), -1);
   if (c.opt_rejected) hm.opt_rejected.assign (c.opt_rejected, c.opt_rejected + (size_t) N * N);
 
@@ -395,7 +443,7 @@ struct HostTrace
 
 inline bool
 build_trace (HostModel &hm, int64_t n, const int64_t *t_ns, const int32_t *src, const int32_t *dst, const int64_t *uid,
-             const uint8_t *valable, const uint8_t *rejected, HostTrace &tr)
+             const uint8_t *valable, const uint8_t *rejected, HostTrace &tr, const uint8_t *ptype = nullptr)
 {
   const int N = hm.st.N;
   tr.t.assign (t_ns, t_ns + n);
@@ -405,9 +453,12 @@ build_trace (HostModel &hm, int64_t n, const int64_t *t_ns, const int32_t *src, 
   for (int64_t i = 0; i < n; i++)
     {
       if (src[i] < 0 || src[i] >= N || dst[i] < 0 || dst[i] >= N) return false;
-      int f = hm.flow_of[(size_t) src[i] * N + dst[i]];
+      const bool big = ptype && ptype[i] == PRB_BIG_SIGN;
+      if (ptype && ptype[i] != PRB_DATA && !big) return false;
+      int f = big ? hm.big_flow_of[(size_t) src[i] * N + dst[i]] : hm.flow_of[(size_t) src[i] * N + dst[i]];
       if (f < 0) return false;
-      tr.uid[i] = (uint32_t) uid[i];
+      /* an NN segment carries no uid: its slot holds the ordinal of the segment within its source */
+      tr.uid[i] = big ? (last[f] >= 0 ? tr.uid[last[f]] + 1u : 1u) : (uint32_t) uid[i];
       tr.flags[i] = (uint8_t) ((valable[i] ? 1 : 0) | (rejected && rejected[i] ? 2 : 0));
       if (last[f] >= 0) tr.next[last[f]] = (int32_t) i; else hm.flow_first[f] = (int32_t) i;
       tr.prev[i] = last[f];
@@ -445,6 +496,12 @@ build_pmodel (const prb_config &c, const HostModel &hm, PModel &pm)
   memset (&ps, 0, sizeof (ps));
   const int N = st.N, M = st.M, L = st.L, LA = st.LA, F = st.F;
   pm.supported = false;
+  if (st.F > st.FP)
+    {
+      /* training with NN-weight segments is Gym-mode work: the event-serial engine runs it */
+      pm.why = "big-signalling sources run on the event-serial engine";
+      return false;
+    }
   /* lookahead: the smallest packet that can be put on a switch link */
   int64_t tx_min = INT64_MAX;
   for (int k = 0; k < st.n_szc; k++) tx_min = std::min (tx_min, hm.tx_ns[k]);

@@ -1324,6 +1324,13 @@ int
 prb_set_inject_trace (prb_env *env, int64_t n, const int64_t *t_ns, const int32_t *src, const int32_t *dst,
                       const int64_t *uid, const uint8_t *valable, const uint8_t *rejected)
 {
+  return prb_set_inject_trace_typed (env, n, t_ns, src, dst, uid, valable, rejected, nullptr);
+}
+
+int
+prb_set_inject_trace_typed (prb_env *env, int64_t n, const int64_t *t_ns, const int32_t *src, const int32_t *dst,
+                            const int64_t *uid, const uint8_t *valable, const uint8_t *rejected, const uint8_t *ptype)
+{
   if (!env) return fail (PRB_EINVAL, "null handle");
   CUDA_TRY (cudaSetDevice (env->device));
   Static &st = env->dst;
@@ -1334,7 +1341,7 @@ prb_set_inject_trace (prb_env *env, int64_t n, const int64_t *t_ns, const int32_
       return PRB_OK;
     }
   if (n >= (1ll << 31)) return fail (PRB_EINVAL, "trace too long");
-  if (!build_trace (env->hm, n, t_ns, src, dst, uid, valable, rejected, env->tr))
+  if (!build_trace (env->hm, n, t_ns, src, dst, uid, valable, rejected, env->tr, ptype))
     return fail (PRB_EINVAL, "injection trace names a flow that the configuration does not have");
   size_t o_t = 0, o_uid = o_t + 8 * n, o_next = o_uid + 4 * n, o_fl = o_next + 4 * n, total = o_fl + n + 16;
   cudaFree (env->d_trace);

@@ -63,7 +63,8 @@ struct Pkt
   int64_t prev_t;    /* time of the previous agent decision on this packet (Agent.temp_obs[...]['time']) */
   int64_t rcv_ts;    /* while on the wire: arrival time and scheduler uid of its Receive event */
   uint32_t rcv_seq;
-  uint32_t uid;      /* data: packet uid; small signalling: uid it reports; ping: ping index */
+  uint32_t uid;      /* data: packet uid; small signalling: uid it reports; ping: ping index;
+                        big signalling: ordinal c of the segment (NNIndex = c / segs, segIndex = c % segs) */
   uint32_t aux;      /* data: start time, whole s; ping fwd: start, ms; ping back: float bits of the delay */
   uint16_t next;     /* FIFO link (queue or wire) / free list */
   uint16_t pad;
@@ -94,6 +95,9 @@ PRB_FIELD (p_prev_node, 56, 8)
 struct Static
 {
   int32_t E, N, M, L, LA, F, K, S, P, MA;
+  int32_t FP;                          /* flows [0,FP) are Poisson sources, [FP,F) NN-segment sources (big signalling) */
+  int32_t big_segs, big_szc;           /* segments per NN (bigSignalingSize / 512), wire size class of a segment */
+  int64_t big_start_ns, big_gap_ns;    /* Seconds (AppStartTime) and Seconds (512*8 / (size*8/syncStep)) */
   int32_t NK, NKP;                     /* non-flow timer slots (2*LA + M) and their count padded to 32 */
   int32_t n_szc, n_rc;
   int64_t link_delay_ns, sim_time_ns, ping_interval_ns;
@@ -1051,6 +1055,13 @@ struct Sim
     r->ptype = p_type (p); r->nobs = 1; r->obs[0] = 1000;
     for (int i = 1; i < 1 + PRB_MAX_K; i++) r->obs[i] = 0;
     r->action = -1; r->prev_node = -1; r->is_new = 0; r->hop_time = 0.0; r->e2e_delay = 0.0f; r->n_lost = 0;
+    if (p_type (p) == PRB_BIG_SIGN)
+      {
+        /* info fields 18-20: NN Index, segment Index, NodeId Signaled (big-signaling-packet-manager.cc:104-121) */
+        uint32_t segs = (uint32_t) st.big_segs;
+        r->uid = (int64_t) (((uint64_t) (p.uid / segs) << 32) | (uint64_t) (p.uid % segs));
+        r->prev_node = p_src (p);
+      }
     for (int i = 0; i < PRB_MAX_LOST; i++) r->lost_uid[i] = 0;
     /* GetGameOver asks the DATA manager, whose m_destination is the last data packet seen here */
     r->done = d.last_dst[m] == x;
@@ -1161,6 +1172,14 @@ struct Sim
         if (i >= 0) set_timer (slot, st.tr_t[i]); else clear_timer (slot);
         return;
       }
+    if (f >= st.FP)
+      {
+        /* BigSignalingGeneratorApplication::ScheduleNextTx — big-signaling-application.cc:236-258: a fixed
+         * gap after StartApplication at AppStartTime (sim.cc:644); f_pos = ordinal of the pending segment */
+        d.f_pos[f] = first ? 1u : d.f_pos[f] + 1u;
+        set_timer (slot, (first ? st.big_start_ns : sc->now) + st.big_gap_ns);
+        return;
+      }
     uint64_t eid = st.env_id_base + (uint64_t) env;
     uint32_t k0 = (uint32_t) st.seed, k1 = (uint32_t) (st.seed >> 32);
     uint32_t fkey = (uint32_t) (st.flow_src[f] * st.N + st.flow_dst[f]);
@@ -1190,6 +1209,20 @@ struct Sim
     int pi = alloc ();
     Pkt p;
     p.w0 = 0; p.prev_t = 0; p.rcv_ts = 0; p.rcv_seq = 0; p.pad = 0; p.next = NIL;
+    if (f >= st.FP)
+      {
+        /* BigSignalingGeneratorApplication::SendPacket — big-signaling-application.cc:261-306 */
+        set_p_type (p, PRB_BIG_SIGN);
+        set_p_dst (p, dst); set_p_src (p, src); set_p_next_hop (p, dst); set_p_last_hop (p, NODE_NONE);
+        set_p_prev_node (p, NODE_NONE);
+        set_p_szc (p, st.big_szc);
+        set_p_ipdst (p, dst);
+        p.aux = 0;
+        p.uid = st.inject_mode == PRB_INJECT_TRACE ? st.tr_uid[(int32_t) d.f_pos[f]] : d.f_pos[f];
+        if (pi >= 0) post_send (st.L + src, pi, p);
+        post_kind = 1; post_arg = f;
+        return;
+      }
     set_p_type (p, PRB_DATA);
     set_p_dst (p, dst); set_p_src (p, src); set_p_next_hop (p, src); set_p_last_hop (p, NODE_NONE);
     set_p_prev_node (p, NODE_NONE);

@@ -127,14 +127,17 @@ class BatchedRoutingEnv:
         return a.value, b.value
 
     # ---- traffic / agents ----
-    def set_inject_trace(self, t_ns, src, dst, uid, valable, rejected=None):
+    def set_inject_trace(self, t_ns, src, dst, uid, valable, rejected=None, ptype=None):
+        """Recorded injections shared by every environment; ptype: 0 data (default), 1 big-signalling segment."""
         a = [np.ascontiguousarray(t_ns, dtype=np.int64), np.ascontiguousarray(src, dtype=np.int32),
              np.ascontiguousarray(dst, dtype=np.int32), np.ascontiguousarray(uid, dtype=np.int64),
              np.ascontiguousarray(valable, dtype=np.uint8),
              np.ascontiguousarray(rejected if rejected is not None else np.zeros(len(t_ns)), dtype=np.uint8)]
-        _abi.check(self.lib.prb_set_inject_trace(self.h, len(a[0]), _abi.ptr(a[0], C.c_int64), _abi.ptr(a[1], C.c_int32),
-                                                 _abi.ptr(a[2], C.c_int32), _abi.ptr(a[3], C.c_int64),
-                                                 _abi.ptr(a[4], C.c_uint8), _abi.ptr(a[5], C.c_uint8)))
+        a.append(np.ascontiguousarray(ptype if ptype is not None else np.zeros(len(a[0])), dtype=np.uint8))
+        _abi.check(self.lib.prb_set_inject_trace_typed(self.h, len(a[0]), _abi.ptr(a[0], C.c_int64),
+                                                       _abi.ptr(a[1], C.c_int32), _abi.ptr(a[2], C.c_int32),
+                                                       _abi.ptr(a[3], C.c_int64), _abi.ptr(a[4], C.c_uint8),
+                                                       _abi.ptr(a[5], C.c_uint8), _abi.ptr(a[6], C.c_uint8)))
 
     def set_policy(self, kind: str, data=None, seed: int = 1):
         d = np.ascontiguousarray(data if data is not None else [], dtype=np.int32).ravel()
@@ -356,10 +359,13 @@ class Ns3EnvGroup:
             return -1 if self._ended else int(self._rec["overlay"])
 
     def info_string(self, rec, c) -> str:
-        """PacketManager::getInfo + DataPacketManager::getInfo field order
-        (prisma/ns3/packet-manager.cc:119-176, data-packet-manager.cc:229-248), parsed by
-        Forwarder.treat_info (prisma/source/forwarder.py:197-289)."""
+        """PacketManager::getInfo (prisma/ns3/packet-manager.cc:119-176, fields 0-17) followed by the fields of the
+        packet's own manager — data: Packet Lost / Source / Destination / node (data-packet-manager.cc:229-248);
+        small signalling: PacketIdSignaled / Arrived at final dest (small-signaling-packet-manager.cc:109-119);
+        big signalling: NN Index / segment Index / NodeId Signaled (big-signaling-packet-manager.cc:110-122) —
+        in the positions Forwarder.treat_info reads them from (prisma/source/forwarder.py:197-289)."""
         size = self.benv.cfg.packet_size + 28 if rec["ptype"] == 0 else 0
+        mo = self.benv.arrays.map_overlay
         lost = "".join("%d;" % int(u) for u in rec["lost_uid"][:min(int(rec["n_lost"]), 8)])
         buffered_o = int(c["overlay_injected"] - c["overlay_arrived"] - c["overlay_lost"])
         buffered_u = int(c["underlay_injected"] - c["underlay_arrived"] - c["underlay_lost"])
@@ -371,8 +377,16 @@ class Ns3EnvGroup:
              ("Overlay Pkts Delivered", int(c["overlay_arrived"])), ("Overlay Pkts Injected", int(c["overlay_injected"])),
              ("Overlay Pkts Buffered", buffered_o), ("Underlay Pkts Dropped", int(c["underlay_lost"])),
              ("Underlay Pkts Delivered", int(c["underlay_arrived"])), ("Underlay Pkts Injected", int(c["underlay_injected"])),
-             ("Underlay Pkts Buffered", buffered_u), ("Signaling Overhead", "%f" % c["signaling_overhead"]),
-             ("Packet Lost", lost)]
+             ("Underlay Pkts Buffered", buffered_u), ("Signaling Overhead", "%f" % c["signaling_overhead"])]
+        if rec["ptype"] == 1:
+            f += [("NN Index", int(rec["uid"]) >> 32), ("segment Index", int(rec["uid"]) & 0xFFFFFFFF),
+                  ("NodeId Signaled", int(mo[int(rec["prev_node"])]))]
+            f[3] = ("Pkt ID", -1)
+        elif rec["ptype"] == 2:
+            f += [("PacketIdSignaled", int(rec["uid"])), ("Arrived at final dest", 1)]
+        else:
+            # Source is not carried by the step record (no consumer: treat_info stops at token 18 for data)
+            f += [("Packet Lost", lost), ("Source", -1), ("Destination", int(rec["obs"][0])), ("node", int(rec["overlay"]))]
         return ",".join("%s=%s" % kv for kv in f)
 
 

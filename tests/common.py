@@ -64,7 +64,9 @@ def oracle_params(cfg, arrays, oracle_mod, **over):
              moving_average_size=cfg.movingAverageObsSize, ping_as_obs=cfg.pingAsObs,
              activate_underlay_traffic=cfg.activateUnderlayTraffic, train=cfg.train,
              signaling_type=cfg.signaling_type, opt_agent=1 if cfg.agent_type == "opt" else 0,
-             loss_penalty=cfg.derived_loss_penalty(m), seed=cfg.seed)
+             loss_penalty=cfg.derived_loss_penalty(m), seed=cfg.seed,
+             signaling=int(cfg.effective_signaling()), big_signaling_size=cfg.bigSignalingSize,
+             sync_step=cfg.sync_step)
     p.update(over)
     return p
 
@@ -137,10 +139,21 @@ def assert_counters_equal(oc, pc):
     assert int(pc["errors"]) == 0
 
 
+def assert_big_signaling_fields(big, uid, prev_node, map_overlay):
+    """Golden (NN Index, segment Index, NodeId Signaled) of every big-signalling step against the record fields
+    that carry them: uid = NNIndex << 32 | segIndex, prev_node = underlay id of the signalling node."""
+    sel = big[:, 0] >= 0
+    assert sel.any()
+    assert np.array_equal(np.asarray(uid)[sel] >> 32, big[sel, 0])
+    assert np.array_equal(np.asarray(uid)[sel] & 0xFFFFFFFF, big[sel, 1])
+    assert np.array_equal(np.asarray(map_overlay)[np.asarray(prev_node)[sel]], big[sel, 2])
+
+
 def replay_inputs(g):
     """(injection arrays, policy kind, policy data, seed) of a golden fixture."""
     inj = g.injections
-    return (inj["t_ns"], inj["src"], inj["dst"], inj["uid"], inj["valable"], inj["rejected"]), g.policy, g.table, g.policy_seed
+    return ((inj["t_ns"], inj["src"], inj["dst"], inj["uid"], inj["valable"], inj["rejected"], inj["type"]),
+            g.policy, g.table, g.policy_seed)
 
 
 def oracle_run(cfg, arrays, oracle_mod, policy="table", table=None, seed=7, env_id=0, until_ns=None, inject=None, **over):

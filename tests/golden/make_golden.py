@@ -25,6 +25,10 @@ GOLDEN = {
                                                                      activateUnderlayTraffic=1), "random"),
     "abilene_train_nn_2s": ("abilene", dict(simTime=2, load_factor=1.2, pingAsObs=0, train=1, signaling_type="NN",
                                             agent_type="dqn_buffer", activateUnderlayTraffic=1), "random"),
+    # NN-weight segments between overlay neighbours on top of the small signalling (sim.cc:634-647)
+    "abilene_train_nn_bigsig_2s": ("abilene", dict(simTime=2, load_factor=1.0, pingAsObs=0, train=1, signaling_type="NN",
+                                                   signalingSim=1, sync_step=0.5, bigSignalingSize=8192,
+                                                   agent_type="dqn_buffer", activateUnderlayTraffic=1), "random"),
     "geant_sp_2s": ("geant", dict(simTime=2, load_factor=1.0, pingAsObs=0, activateUnderlayTraffic=1), "table"),
 }
 COUNTERS = ("overlay_injected", "overlay_arrived", "overlay_lost", "underlay_injected", "underlay_arrived",
@@ -32,8 +36,16 @@ COUNTERS = ("overlay_injected", "overlay_arrived", "overlay_lost", "underlay_inj
 FLOATS = ("avg_e2e_delay", "avg_cost", "avg_underlay_e2e_delay", "avg_underlay_cost", "signaling_overhead")
 
 
-def main():
+def big_info(info):
+    """(NN Index, segment Index, NodeId Signaled) of a big-signalling step (big-signaling-packet-manager.cc:104-121)."""
+    f = dict(t.strip().split("=") for t in info.split(",") if "=" in t)
+    return int(f["NN Index"]), int(f["segment Index"]), int(f["NodeId Signaled"])
+
+
+def main(only=()):
     for name, (topo, over, policy) in GOLDEN.items():
+        if only and name not in only:
+            continue
         cfg = common.env_config(topo, **over)
         arrays = cfg.load()
         table = common.sp_table(arrays)
@@ -48,12 +60,14 @@ def main():
                         moving_average=cfg.movingAverageObsSize,
                         activate_underlay_traffic=bool(cfg.activateUnderlayTraffic), ping_as_obs=bool(cfg.pingAsObs),
                         ping_interval=cfg.pingPacketIntervalTime, policy=policy, policy_data=table, policy_seed=7,
-                        seed=cfg.seed)
+                        seed=cfg.seed, signaling=cfg.effective_signaling(), sync_step=cfg.sync_step,
+                        big_signaling_size=cfg.bigSignalingSize, log_info=True)
             summ = run_ref.parse_summary(out)
             fr, to = oracle.build_links(arrays.phys_adj)
             _, route = run_ref.link_maps(summ, fr, to)
             ev = run_ref.parse_events(out, summ, fr, to)
-            dec = [d for d in run_ref.parse_decisions(out) if d["ptype"] >= 0]
+            dec = [d for d in run_ref.parse_decisions(out, with_info=True) if d["ptype"] >= 0]
+        big = np.array([big_info(d["info"]) if d["ptype"] == 1 else (-1, -1, -1) for d in dec], dtype=np.int32)
         kmax = max(len(d["obs"]) for d in dec)
         obs = np.full((len(dec), kmax), -1, dtype=np.int32)
         for i, d in enumerate(dec):
@@ -68,10 +82,11 @@ def main():
             dec_done=np.array([d["done"] for d in dec], dtype=np.int32),
             dec_action=np.array([d["action"] for d in dec], dtype=np.int32),
             dec_nobs=np.array([len(d["obs"]) for d in dec], dtype=np.int32), dec_obs=obs,
+            **({"dec_big": big} if (big[:, 0] >= 0).any() else {}),
             counters=np.array([summ[k] for k in COUNTERS], dtype=np.int64),
             float_bits=np.array([summ[k + "_bits"] for k in FLOATS], dtype=np.uint32))
         print(name, len(ev), "events", len(dec), "steps")
 
 
 if __name__ == "__main__":
-    main()
+    main(sys.argv[1:])

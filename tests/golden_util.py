@@ -13,8 +13,11 @@ COUNTERS = ("overlay_injected", "overlay_arrived", "overlay_lost", "underlay_inj
 FLOATS = ("avg_e2e", "avg_cost", "avg_underlay_e2e", "avg_underlay_cost", "signaling_overhead")
 
 
-def names():
-    return sorted(os.path.basename(p)[:-4] for p in glob.glob(os.path.join(HERE, "*.npz")))
+def names(parallel=False):
+    """parallel: only the fixtures the node-parallel engine takes (NN-weight segment sources run on the
+    event-serial engine)."""
+    n = sorted(os.path.basename(p)[:-4] for p in glob.glob(os.path.join(HERE, "*.npz")))
+    return [x for x in n if not (parallel and "bigsig" in x)]
 
 
 class Golden:

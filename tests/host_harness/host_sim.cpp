@@ -57,9 +57,9 @@ void hs_destroy (hs_sim *s) { delete s; }
 
 int
 hs_set_inject_trace (hs_sim *s, int64_t n, const int64_t *t_ns, const int32_t *src, const int32_t *dst, const int64_t *uid,
-                     const uint8_t *valable, const uint8_t *rejected)
+                     const uint8_t *valable, const uint8_t *rejected, const uint8_t *ptype)
 {
-  if (!build_trace (s->hm, n, t_ns, src, dst, uid, valable, rejected, s->tr)) return -1;
+  if (!build_trace (s->hm, n, t_ns, src, dst, uid, valable, rejected, s->tr, ptype)) return -1;
   Static &st = s->hm.st;
   st.inject_mode = PRB_INJECT_TRACE;
   st.tr_n = n; st.tr_t = s->tr.t.data (); st.tr_uid = s->tr.uid.data (); st.tr_flags = s->tr.flags.data ();

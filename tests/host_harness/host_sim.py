@@ -35,7 +35,7 @@ def lib():
         L.hs_create.argtypes = [C.POINTER(_abi.PrbConfig), C.c_int, i64, i64]
         L.hs_destroy.argtypes = [vp]
         L.hs_set_inject_trace.argtypes = [vp, i64, C.POINTER(i64), C.POINTER(i32), C.POINTER(i32), C.POINTER(i64),
-                                          C.POINTER(C.c_uint8), C.POINTER(C.c_uint8)]
+                                          C.POINTER(C.c_uint8), C.POINTER(C.c_uint8), C.POINTER(C.c_uint8)]
         L.hs_set_policy.argtypes = [vp, C.c_int, C.POINTER(i32), i64, C.c_uint64]
         L.hs_run.argtypes = [vp, i64]
         L.hs_run_nolog.argtypes = [vp, i64]
@@ -62,7 +62,7 @@ def lib():
         L.hp_create.restype = vp
         L.hp_create.argtypes = [C.POINTER(_abi.PrbConfig), C.c_int, i64, C.c_int]
         L.hp_destroy.argtypes = [vp]
-        L.hp_set_inject_trace.argtypes = L.hs_set_inject_trace.argtypes
+        L.hp_set_inject_trace.argtypes = L.hs_set_inject_trace.argtypes[:-1]
         L.hp_set_policy.argtypes = [vp, C.c_int, C.POINTER(i32), i64]
         L.hp_run.argtypes = [vp, i64, C.c_int]
         L.hp_counters.argtypes = [vp, C.POINTER(_abi.PrbCounters)]
@@ -114,13 +114,14 @@ class HostSim:
         except Exception:
             pass
 
-    def set_inject_trace(self, t_ns, src, dst, uid, valable, rejected):
+    def set_inject_trace(self, t_ns, src, dst, uid, valable, rejected, ptype=None):
         a = [np.ascontiguousarray(t_ns, dtype=np.int64), np.ascontiguousarray(src, dtype=np.int32),
              np.ascontiguousarray(dst, dtype=np.int32), np.ascontiguousarray(uid, dtype=np.int64),
-             np.ascontiguousarray(valable, dtype=np.uint8), np.ascontiguousarray(rejected, dtype=np.uint8)]
+             np.ascontiguousarray(valable, dtype=np.uint8), np.ascontiguousarray(rejected, dtype=np.uint8),
+             np.ascontiguousarray(ptype if ptype is not None else np.zeros(len(t_ns)), dtype=np.uint8)]
         rc = lib().hs_set_inject_trace(self.h, len(a[0]), _abi.ptr(a[0], C.c_int64), _abi.ptr(a[1], C.c_int32),
                                        _abi.ptr(a[2], C.c_int32), _abi.ptr(a[3], C.c_int64),
-                                       _abi.ptr(a[4], C.c_uint8), _abi.ptr(a[5], C.c_uint8))
+                                       _abi.ptr(a[4], C.c_uint8), _abi.ptr(a[5], C.c_uint8), _abi.ptr(a[6], C.c_uint8))
         if rc != 0:
             raise ValueError("bad injection trace")
 
@@ -184,7 +185,8 @@ class HostParSim:
         except Exception:
             pass
 
-    def set_inject_trace(self, t_ns, src, dst, uid, valable, rejected):
+    def set_inject_trace(self, t_ns, src, dst, uid, valable, rejected, ptype=None):
+        assert ptype is None or not np.any(ptype), "data injections only"
         a = [np.ascontiguousarray(t_ns, dtype=np.int64), np.ascontiguousarray(src, dtype=np.int32),
              np.ascontiguousarray(dst, dtype=np.int32), np.ascontiguousarray(uid, dtype=np.int64),
              np.ascontiguousarray(valable, dtype=np.uint8), np.ascontiguousarray(rejected, dtype=np.uint8)]

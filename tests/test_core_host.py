@@ -30,6 +30,8 @@ def test_core_replays_reference_golden(name):
     k = g.dec["obs"].shape[1]
     mask = np.arange(k)[None, :] < g.dec["nobs"][:, None]
     assert np.array_equal(np.where(mask, st["obs"][:, :k], -1), g.dec["obs"])
+    if "big" in g.dec:
+        common.assert_big_signaling_fields(g.dec["big"], st["uid"], st["prev_node"], g.arrays.map_overlay)
     c = hs.counters()
     assert c["errors"] == 0
     for key, v in g.counters.items():
@@ -45,6 +47,9 @@ PHILOX_CASES = [
                                           train=1, signaling_type="target", agent_type="dqn_buffer",
                                           max_out_buffer_size=3000), "random", 123456789012),
     ("geant", dict(simTime=1.5, load_factor=1.3, pingAsObs=0, activateUnderlayTraffic=1), "table", 77),
+    # NN-weight segment sources (big signalling) next to Philox traffic
+    ("abilene", dict(simTime=2.5, load_factor=0.8, pingAsObs=0, activateUnderlayTraffic=1, train=1, signaling_type="NN",
+                     signalingSim=1, sync_step=0.25, bigSignalingSize=4096, agent_type="dqn_buffer"), "random", 2),
 ]
 
 

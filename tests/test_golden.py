@@ -15,7 +15,7 @@ def test_oracle_reproduces_golden(name):
     assert np.array_equal(oracle.global_routes(g.arrays.phys_adj), g.route)
     sim = oracle.OracleSim(common.oracle_params(g.cfg, g.arrays, oracle))
     inj = g.injections
-    sim.set_inject_trace(inj["t_ns"], inj["src"], inj["dst"], inj["uid"], inj["valable"], inj["rejected"])
+    sim.set_inject_trace(inj["t_ns"], inj["src"], inj["dst"], inj["uid"], inj["valable"], inj["rejected"], inj["type"])
     sim.set_policy(g.policy, g.table, seed=g.policy_seed)
     sim.run()
     oe = sim.events()
@@ -32,6 +32,8 @@ def test_oracle_reproduces_golden(name):
     k = g.dec["obs"].shape[1]
     mask = np.arange(k)[None, :] < g.dec["nobs"][:, None]
     assert np.array_equal(np.where(mask, od["obs"][:, :k], -1), g.dec["obs"])
+    if "big" in g.dec:
+        common.assert_big_signaling_fields(g.dec["big"], od["uid"], od["prev_node"], g.arrays.map_overlay)
     c = sim.counters()
     for key, v in g.counters.items():
         assert c[key] == v, key

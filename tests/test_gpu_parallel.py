@@ -26,7 +26,7 @@ def node_trace(g):
 
 
 @pytest.mark.parametrize("team", [0, 32])
-@pytest.mark.parametrize("name", golden_util.names())
+@pytest.mark.parametrize("name", golden_util.names(parallel=True))
 def test_parallel_engine_replays_reference_golden(name, team):
     g = golden_util.Golden(name)
     g.cfg.num_envs = 5

@@ -45,6 +45,8 @@ def test_cuda_replays_reference_golden(name, lanes):
     k = g.dec["obs"].shape[1]
     mask = np.arange(k)[None, :] < g.dec["nobs"][:, None]
     assert np.array_equal(np.where(mask, st["obs"][:, :k], -1), g.dec["obs"])
+    if "big" in g.dec:
+        common.assert_big_signaling_fields(g.dec["big"], st["uid"], st["prev_node"], g.arrays.map_overlay)
     c = cs[0]
     for key, v in g.counters.items():
         assert int(c[key]) == v, key
@@ -62,6 +64,9 @@ PHILOX_CASES = [
     ("overlay_full_mesh_3n_abilene", dict(simTime=8, load_factor=2.5, pingAsObs=1, activateUnderlayTraffic=1, train=1,
                                           signaling_type="target", agent_type="dqn_buffer", max_out_buffer_size=3000), "random"),
     ("geant", dict(simTime=1.5, load_factor=1.3, pingAsObs=0, activateUnderlayTraffic=1), "table"),
+    # NN-weight segment sources (big signalling) next to Philox traffic
+    ("abilene", dict(simTime=2.5, load_factor=0.8, pingAsObs=0, activateUnderlayTraffic=1, train=1, signaling_type="NN",
+                     signalingSim=1, sync_step=0.25, bigSignalingSize=4096, agent_type="dqn_buffer"), "random"),
 ]
 
 
@@ -244,6 +249,45 @@ def test_sparse_timers_beyond_key_range():
     env.close()
 
 
+def test_gym_mode_surfaces_big_signaling_steps():
+    """prb_step with NN-weight segment sources: every segment that reaches its neighbour is a Gym step with obs
+    [1000] whose record carries NN Index / segment Index / the signalling node, and the reference's info string
+    holds them in the positions Forwarder.treat_info reads (forwarder.py:251-254)."""
+    from prisma_b200.env import Ns3EnvGroup
+    cfg = common.env_config("abilene", num_envs=4, simTime=0.6, load_factor=0.8, pingAsObs=0, activateUnderlayTraffic=1,
+                            train=1, signaling_type="NN", signalingSim=1, sync_step=0.1, bigSignalingSize=2048,
+                            agent_type="dqn_buffer")
+    arrays = cfg.load()
+    env = make_env(cfg, arrays=arrays)
+    osim = common.oracle_run(cfg, arrays, oracle, policy="zero", env_id=2)
+    od = osim.decisions()
+    grp = Ns3EnvGroup(env, 2)
+    acts = np.zeros(cfg.num_envs, dtype=np.int32)
+    n = n_big = 0
+    while True:
+        rec = env.step_host(acts)[2]
+        if not rec["valid"]:
+            break
+        o = od[n]
+        assert rec["t_ns"] == o["t_ns"] and rec["ptype"] == o["ptype"] and rec["node"] == o["node"], (n, rec, o)
+        if rec["ptype"] == 1:
+            assert rec["uid"] == o["uid"] and rec["prev_node"] == o["prev_node"] and rec["obs"][0] == 1000
+            tok = grp.info_string(rec, env.counters()[2]).split(",") if n_big < 5 else None
+            if tok:
+                assert int(tok[4].split("=")[-1]) == 1
+                assert int(tok[18].split("=")[-1]) == rec["uid"] >> 32
+                assert int(tok[19].split("=")[-1]) == rec["uid"] & 0xFFFFFFFF
+                assert int(tok[20].split("=")[-1]) == arrays.map_overlay[rec["prev_node"]]
+            n_big += 1
+        n += 1
+    assert n == len(od) and n_big == int((od["ptype"] == 1).sum()) and n_big > 100
+    # segments per NN = 2048 / 512: the segment index wraps at 4 and the NN index advances
+    big = od[od["ptype"] == 1]
+    assert (big["uid"] & 0xFFFFFFFF).max() == 3 and (big["uid"] >> 32).max() >= 1
+    common.assert_counters_equal(osim.counters(), env.counters()[2])
+    env.close()
+
+
 def test_compat_per_node_view():
     """Ns3EnvCompat: the reference's per-node reset/step surface over env 0, driven the way
     prisma/main.py:117-127 does — one thread per overlay node running a Forwarder-style loop."""
@@ -269,7 +313,7 @@ def test_compat_per_node_view():
                 obs, reward, done, info = node.step(a, timeout=120)
                 counts[m] += 1
                 if obs[0] != -1:
-                    assert reward == 1.0 and info.startswith("End to End Delay=") and len(info.split(",")) == 19
+                    assert reward == 1.0 and info.startswith("End to End Delay=") and len(info.split(",")) == 22
         except Exception as ex:   # pragma: no cover
             errors.append(ex)
             with grp._cv:

@@ -26,6 +26,10 @@ CASES = {
     "abilene_train_small_signaling": ("abilene", dict(simTime=5, load_factor=1.2, pingAsObs=0, train=1,
                                                       signaling_type="NN", agent_type="dqn_buffer",
                                                       activateUnderlayTraffic=1), "random"),
+    "abilene_train_nn_big_signaling": ("abilene", dict(simTime=4, load_factor=1.1, pingAsObs=0, train=1,
+                                                       signaling_type="NN", signalingSim=1, sync_step=1.0,
+                                                       bigSignalingSize=35328, agent_type="dqn_buffer",
+                                                       activateUnderlayTraffic=1), "random"),
     "overlay_train_target": ("overlay_full_mesh_3n_abilene", dict(simTime=10, load_factor=3.0, pingAsObs=1, train=1,
                                                                   signaling_type="target", agent_type="dqn_buffer",
                                                                   activateUnderlayTraffic=1,
@@ -47,15 +51,17 @@ def run_case(name, tmp):
                 signaling_type=cfg.signaling_type, train=bool(cfg.train), loss_penalty=lp,
                 moving_average=cfg.movingAverageObsSize, activate_underlay_traffic=bool(cfg.activateUnderlayTraffic),
                 ping_as_obs=bool(cfg.pingAsObs), ping_interval=cfg.pingPacketIntervalTime,
-                policy=policy, policy_data=table, policy_seed=7, seed=cfg.seed)
+                policy=policy, policy_data=table, policy_seed=7, seed=cfg.seed,
+                signaling=cfg.effective_signaling(), sync_step=cfg.sync_step, big_signaling_size=cfg.bigSignalingSize,
+                log_info=True)
     summ = run_ref.parse_summary(out)
     fr, to = oracle.build_links(arrays.phys_adj)
     _, route = run_ref.link_maps(summ, fr, to)
     ev = run_ref.parse_events(out, summ, fr, to)
-    dec = [d for d in run_ref.parse_decisions(out) if d["ptype"] >= 0]
+    dec = [d for d in run_ref.parse_decisions(out, with_info=True) if d["ptype"] >= 0]
     sim = oracle.OracleSim(common.oracle_params(cfg, arrays, oracle))
     inj = ev[ev["kind"] == 0]
-    sim.set_inject_trace(inj["t_ns"], inj["src"], inj["dst"], inj["uid"], inj["valable"], inj["rejected"])
+    sim.set_inject_trace(inj["t_ns"], inj["src"], inj["dst"], inj["uid"], inj["valable"], inj["rejected"], inj["type"])
     sim.set_policy(policy, table, seed=7)
     sim.run()
     return cfg, arrays, summ, route, ev, dec, sim
@@ -81,6 +87,11 @@ def test_restatement_matches_reference(name, tmp_path):
         assert r["obs"] == list(o["obs"][:o["nobs"]]), (i, r, o)
         if r["ptype"] == 0:
             assert r["uid"] == o["uid"]
+        if r["ptype"] == 1:
+            # info fields 18-20 of the reference against the record fields that carry them
+            f = dict(t.strip().split("=") for t in r["info"].split(",") if "=" in t)
+            assert int(f["NN Index"]) == o["uid"] >> 32 and int(f["segment Index"]) == o["uid"] & 0xFFFFFFFF, (i, r, o)
+            assert int(f["NodeId Signaled"]) == arrays.map_overlay[o["prev_node"]], (i, r, o)
     # counters and the float32 statistics, bit for bit
     c = sim.counters()
     for k in ("overlay_injected", "overlay_arrived", "overlay_lost", "underlay_injected", "underlay_arrived",

@@ -57,7 +57,7 @@ def assert_same_multiset(ref_ev, par_ev, uid_map=None):
 
 
 @pytest.mark.parametrize("team", [16, 32])
-@pytest.mark.parametrize("name", golden_util.names())
+@pytest.mark.parametrize("name", golden_util.names(parallel=True))
 def test_parallel_engine_replays_reference_golden(name, team):
     """Real ns-3 outputs: same injections, the agents' actions replayed per node."""
     g = golden_util.Golden(name)
