@@ -8,8 +8,14 @@ cases = [("abilene", dict(load_factor=0.9, pingAsObs=0), 4096),
          ("geant", dict(load_factor=0.9, pingAsObs=0), 4096),
          ("geant", dict(load_factor=1.5, pingAsObs=0), 4096),
          ("overlay_full_mesh_3n_abilene", dict(load_factor=0.9, pingAsObs=1), 16384),
-         ("abilene", dict(load_factor=0.9, pingAsObs=0, train=1, signaling_type="target", agent_type="dqn_buffer"), 4096)]
+         ("abilene", dict(load_factor=0.9, pingAsObs=0, train=1, signaling_type="target", agent_type="dqn_buffer"), 4096),
+         # BASELINE.json configs[4]: 100-node random underlay, 4-packet buffers (drop-heavy), control packets
+         ("synthetic100", dict(load_factor=1.3, pingAsObs=0, max_out_buffer_size=2168, train=1, signaling_type="NN",
+                               agent_type="dqn_buffer"), 4096)]
+only = sys.argv[1:]
 for topo, over, E in cases:
+    if only and topo not in only:
+        continue
     for eng in ("parallel", "serial"):
         cfg = common.env_config(topo, num_envs=E, simTime=8.0, activateUnderlayTraffic=1, **over)
         arrays = cfg.load()

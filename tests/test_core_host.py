@@ -47,6 +47,9 @@ PHILOX_CASES = [
                                           train=1, signaling_type="target", agent_type="dqn_buffer",
                                           max_out_buffer_size=3000), "random", 123456789012),
     ("geant", dict(simTime=1.5, load_factor=1.3, pingAsObs=0, activateUnderlayTraffic=1), "table", 77),
+    # BASELINE.json configs[4]: 100-node random underlay, 4-packet buffers (drop-heavy), control packets
+    ("synthetic100", dict(simTime=1.5, load_factor=1.4, max_out_buffer_size=2168, pingAsObs=0, train=1,
+                          signaling_type="NN", agent_type="dqn_buffer", activateUnderlayTraffic=1), "random", 9),
     # NN-weight segment sources (big signalling) next to Philox traffic
     ("abilene", dict(simTime=2.5, load_factor=0.8, pingAsObs=0, activateUnderlayTraffic=1, train=1, signaling_type="NN",
                      signalingSim=1, sync_step=0.25, bigSignalingSize=4096, agent_type="dqn_buffer"), "random", 2),

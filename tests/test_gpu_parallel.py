@@ -57,6 +57,9 @@ CASES = [
     ("overlay_full_mesh_3n_abilene", dict(simTime=8, load_factor=2.5, pingAsObs=1, activateUnderlayTraffic=1, train=1,
                                           signaling_type="target", agent_type="dqn_buffer", max_out_buffer_size=3000)),
     ("geant", dict(simTime=1.5, load_factor=1.3, pingAsObs=0, activateUnderlayTraffic=1)),
+    # BASELINE.json configs[4]: 100-node random underlay, 4-packet buffers (drop-heavy), control packets
+    ("synthetic100", dict(simTime=1.5, load_factor=1.4, max_out_buffer_size=2168, pingAsObs=0, train=1,
+                          signaling_type="NN", agent_type="dqn_buffer", activateUnderlayTraffic=1)),
 ]
 
 

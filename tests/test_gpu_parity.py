@@ -64,6 +64,9 @@ PHILOX_CASES = [
     ("overlay_full_mesh_3n_abilene", dict(simTime=8, load_factor=2.5, pingAsObs=1, activateUnderlayTraffic=1, train=1,
                                           signaling_type="target", agent_type="dqn_buffer", max_out_buffer_size=3000), "random"),
     ("geant", dict(simTime=1.5, load_factor=1.3, pingAsObs=0, activateUnderlayTraffic=1), "table"),
+    # BASELINE.json configs[4]: 100-node random underlay, 4-packet buffers (drop-heavy), control packets
+    ("synthetic100", dict(simTime=1.5, load_factor=1.4, max_out_buffer_size=2168, pingAsObs=0, train=1,
+                          signaling_type="NN", agent_type="dqn_buffer", activateUnderlayTraffic=1), "random"),
     # NN-weight segment sources (big signalling) next to Philox traffic
     ("abilene", dict(simTime=2.5, load_factor=0.8, pingAsObs=0, activateUnderlayTraffic=1, train=1, signaling_type="NN",
                      signalingSim=1, sync_step=0.25, bigSignalingSize=4096, agent_type="dqn_buffer"), "random"),
@@ -78,7 +81,7 @@ def test_cuda_matches_oracle_synthetic_traffic(topo, over, policy):
     arrays = cfg.load()
     table = common.sp_table(arrays)
     env = make_env(cfg, arrays=arrays, env_id_base=1000)
-    env.enable_log(200000, 80000)
+    env.enable_log(400000, 120000)
     env.reset()
     env.set_policy(policy, table, seed=11)
     env.run()

@@ -30,6 +30,12 @@ CASES = {
                                                        signaling_type="NN", signalingSim=1, sync_step=1.0,
                                                        bigSignalingSize=35328, agent_type="dqn_buffer",
                                                        activateUnderlayTraffic=1), "random"),
+    # BASELINE.json configs[4] (random underlay, 4-packet buffers = drop-heavy, control packets) at the largest size the
+    # reference can run: it numbers all switch devices out of one /24 (sim.cc:446-447), so 100 nodes abort in ns-3
+    "c5_synthetic56_drop_heavy_signaling": ("synthetic56", dict(simTime=1.5, load_factor=1.3, max_out_buffer_size=2168,
+                                                                  pingAsObs=0, train=1, signaling_type="NN",
+                                                                  agent_type="dqn_buffer", activateUnderlayTraffic=1),
+                                             "random"),
     "overlay_train_target": ("overlay_full_mesh_3n_abilene", dict(simTime=10, load_factor=3.0, pingAsObs=1, train=1,
                                                                   signaling_type="target", agent_type="dqn_buffer",
                                                                   activateUnderlayTraffic=1,

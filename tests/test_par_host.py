@@ -84,6 +84,13 @@ CASES = [
                                           max_out_buffer_size=3000), 123456789012, 8),
     ("geant", dict(simTime=1.5, load_factor=1.3, pingAsObs=0, activateUnderlayTraffic=1), 77, 32),
     ("geant", dict(simTime=1.0, load_factor=1.0, pingAsObs=0, activateUnderlayTraffic=1), 3, 8),   # 3 nodes per lane
+    # BASELINE.json configs[4]: 100-node random underlay (4 nodes per lane), 4-packet buffers, control packets;
+    # and the same construction at 56 nodes, the largest the reference itself can address (pinned in test_oracle_vs_ref)
+    ("synthetic100", dict(simTime=1.5, load_factor=1.4, max_out_buffer_size=2168, pingAsObs=0, train=1,
+                          signaling_type="NN", agent_type="dqn_buffer", activateUnderlayTraffic=1), 11, 32),
+    ("synthetic56", dict(simTime=1.5, load_factor=1.4, max_out_buffer_size=2168, pingAsObs=0, train=1,
+                          signaling_type="NN", agent_type="dqn_buffer", activateUnderlayTraffic=1), 4, 32),
+    ("synthetic100", dict(simTime=1.2, load_factor=1.0, pingAsObs=1, activateUnderlayTraffic=1), 5, 32),
     # a source whose next packet follows 4 ns after the previous one (the access link's serialisation time): the
     # arrival at the node and the next injection fall into the same nanosecond (found by the 8-GPU bench)
     ("abilene", dict(simTime=1.3, load_factor=0.9, pingAsObs=0, activateUnderlayTraffic=1, agent_type="dqn_routing",
