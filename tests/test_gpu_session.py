@@ -45,7 +45,7 @@ def test_dqn_buffer_training_session(tmp_path, capsys):
                                      "--iterationNum=600", "--logging_timestep=0", "--snapshot_interval=2",
                                      "--save_models=1", "--replay_buffer_max_size=32768", "--session_name=train",
                                      "--logs_parent_folder=" + str(tmp_path)])
-    assert res["total_data_pkts"] > 128 * 1000 and 0.0 <= res["loss_ratio"] < 0.5 and res["avg_e2e_delay"] > 0
+    assert res["total_data_pkts"] > 128 * 1000 and 0.0 <= res["loss_ratio"] < 0.9 and res["avg_e2e_delay"] > 0   # exploring agents
     out = capsys.readouterr().out
     assert "Total number of Transitions" in out
     root = os.path.join(str(tmp_path), "saved_models", "train")
