@@ -236,6 +236,12 @@ int prb_step_qnet (prb_env *env, int32_t n_steps, float eps, uint64_t seed, prb_
  * prb_replay_read: the stored rows of one node to the host (ReplayBuffer.save). */
 int prb_replay_enable (prb_env *env, int64_t rows_per_node, int32_t pending_slots);
 int prb_replay_record (prb_env *env, const prb_step_rec *rec_dev, const int32_t *actions_dev);
+/* `target` signalling (prisma/source/trainer.py:52-55, forwarder.py:389-431 with signalingSim = 0): the reward column
+ * of a transit transition holds the TD target that the NEXT node computes with its own (current) network when the
+ * packet reaches it, hop_time + gamma * min over its actions that do not lead back (learner.py:232-255); terminal and
+ * lost-packet transitions keep the plain reward.  Needs the device-side agents (prb_qnet_act before
+ * prb_replay_record, or prb_step_qnet). */
+int prb_replay_set_target_mode (prb_env *env, int on, float gamma);
 int prb_replay_counts (prb_env *env, int64_t *rows_written /* host [M] */, int64_t *missed /* host, may be NULL */);
 int prb_replay_read (prb_env *env, int32_t node, float *rows_host, int64_t max_rows, int64_t *n_rows);
 int prb_replay_sample (prb_env *env, int32_t node, int32_t batch, uint64_t seed, float *obs_dev, int32_t *action_dev,

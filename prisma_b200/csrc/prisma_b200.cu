@@ -76,7 +76,7 @@ elu_ (float x)
 /* all 32 lanes of a warp: action for the pending data step *r of environment-id eid (every lane returns it) */
 __device__ __forceinline__ int
 qnet_forward (const Static &st, const float *w, const prb_step_rec *r, int lane, float eps, uint64_t seed, uint64_t step, uint64_t eid,
-              float *q_row)
+              float *q_row, float *tmin = nullptr)
 {
   const int m = r->overlay, K = st.K, M = st.M;
   const int k = st.agent_k[m];
@@ -142,6 +142,15 @@ qnet_forward (const Static &st, const float *w, const prb_step_rec *r, int lane,
     }
   q = elu_ (q);
   if (q_row && lane < K) q_row[lane] = lane < k ? q : 0.0f;
+  if (tmin)
+    {
+      /* `target` signalling: what this node reports back to the previous decision maker is the smallest Q-value
+       * over its actions except the one that leads back there (trainer.py:58-60 filtered_indices,
+       * learner.py:232-255); +inf when no action is left */
+      float tq = (lane < k && (int) st.agent_nbr[(size_t) m * K + lane] != r->prev_node) ? q : INFINITY;
+      for (int o = 16; o > 0; o >>= 1) tq = fminf (tq, __shfl_xor_sync (0xFFFFFFFFu, tq, o));
+      *tmin = tq;
+    }
   /* argmin, first index on equal values (tf.argmin) */
   float bq = lane < k ? q : INFINITY;
   int bi = lane;
@@ -168,7 +177,7 @@ qnet_forward (const Static &st, const float *w, const prb_step_rec *r, int lane,
 
 __global__ void __launch_bounds__ (128)
 k_qnet_act (const __grid_constant__ Static st, const float *w, const prb_step_rec *rec, int32_t *actions, float *q_out,
-            float eps, uint64_t seed, uint64_t step)
+            float eps, uint64_t seed, uint64_t step, float *tmin_out)
 {
   const int lane = threadIdx.x & 31;
   const int e = blockIdx.x * (blockDim.x / 32) + (threadIdx.x >> 5);
@@ -179,8 +188,14 @@ k_qnet_act (const __grid_constant__ Static st, const float *w, const prb_step_re
       if (lane == 0) actions[e] = 0;
       return;
     }
-  int action = qnet_forward (st, w, r, lane, eps, seed, step, st.env_id_base + (uint64_t) e, q_out ? q_out + (size_t) e * st.K : nullptr);
-  if (lane == 0) actions[e] = action;
+  float tmin = INFINITY;
+  int action = qnet_forward (st, w, r, lane, eps, seed, step, st.env_id_base + (uint64_t) e, q_out ? q_out + (size_t) e * st.K : nullptr,
+                             tmin_out ? &tmin : nullptr);
+  if (lane == 0)
+    {
+      actions[e] = action;
+      if (tmin_out) tmin_out[e] = tmin;
+    }
 }
 
 /* ------------------------------------------------------------------------------------------------
@@ -198,6 +213,11 @@ struct ReplayArgs
   int32_t *pending;           /* [E][pcap][PW]: uid lo, uid hi, node, action, obs[1+K] */
   int64_t cap;
   int32_t pcap, R, PW;
+  /* `target` signalling (trainer.py:52-55): the reward column holds the TD target the NEXT node computes with its
+   * own network when the packet reaches it: hop time + gamma * min over its actions that do not lead back */
+  int32_t target_mode;
+  float gamma;
+  float *tmin;                /* [E]: that minimum for the pending step of every environment (unfused path) */
 };
 
 __device__ inline void
@@ -216,7 +236,7 @@ replay_push (const Static &st, const ReplayArgs &ra, int node, const int32_t *en
 
 /* the bookkeeping of one step record (one thread) */
 __device__ inline void
-replay_record_one (const Static &st, const ReplayArgs &ra, int e, const prb_step_rec *r, int32_t action)
+replay_record_one (const Static &st, const ReplayArgs &ra, int e, const prb_step_rec *r, int32_t action, float tmin = INFINITY)
 {
   if (!r->valid || r->ptype != PRB_DATA) return;
   int32_t *tab = ra.pending + (size_t) e * ra.pcap * ra.PW;
@@ -247,7 +267,9 @@ replay_record_one (const Static &st, const ReplayArgs &ra, int e, const prb_step
     {
       if (ent[0] == (int32_t) r->uid && ent[1] == (int32_t) (r->uid >> 32) && ent[2] >= 0)
         {
-          replay_push (st, ra, ent[2], ent, (float) r->hop_time, r->obs, r->nobs, r->done);
+          float rew = (float) r->hop_time;
+          if (ra.target_mode && r->need_action && tmin < 1e37f) rew = rew + ra.gamma * tmin;
+          replay_push (st, ra, ent[2], ent, rew, r->obs, r->nobs, r->done);
           ent[2] = -1;
         }
       else
@@ -266,7 +288,7 @@ k_replay_record (const __grid_constant__ Static st, const ReplayArgs ra, const p
 {
   const int e = blockIdx.x * blockDim.x + threadIdx.x;
   if (e >= st.E) return;
-  replay_record_one (st, ra, e, &rec[e], actions[e]);
+  replay_record_one (st, ra, e, &rec[e], actions[e], ra.target_mode && ra.tmin ? ra.tmin[e] : INFINITY);
 }
 
 __global__ void
@@ -382,9 +404,11 @@ k_advance (const __grid_constant__ Static st, const LaunchArgs a)
       if (pend)
         {
           int32_t act = 0;
+          float tmin = INFINITY;
           if (rec->need_action)
-            act = qnet_forward (st, a.qw, rec, lane, a.eps, a.seed, a.step0, st.env_id_base + (uint64_t) env, nullptr);
-          if (gl == 0 && a.replay.rows) replay_record_one (st, a.replay, env, rec, act);
+            act = qnet_forward (st, a.qw, rec, lane, a.eps, a.seed, a.step0, st.env_id_base + (uint64_t) env, nullptr,
+                                a.replay.target_mode ? &tmin : nullptr);
+          if (gl == 0 && a.replay.rows) replay_record_one (st, a.replay, env, rec, act, tmin);
           __syncwarp (gmask);
           own_action = act;
         }
@@ -459,10 +483,11 @@ k_advance (const __grid_constant__ Static st, const LaunchArgs a)
           if (!go && status == ST_PAUSE && ++steps_done < a.steps)
             {
               int32_t act = 0;
+              float tmin = INFINITY;
               if (rec->need_action)
                 act = qnet_forward (st, a.qw, rec, lane, a.eps, a.seed, a.step0 + (uint64_t) steps_done, st.env_id_base + (uint64_t) env,
-                                    nullptr);
-              if (gl == 0 && a.replay.rows) replay_record_one (st, a.replay, env, rec, act);
+                                    nullptr, a.replay.target_mode ? &tmin : nullptr);
+              if (gl == 0 && a.replay.rows) replay_record_one (st, a.replay, env, rec, act, tmin);
               __syncwarp (gmask);
               own_action = act;
               active_resume = 1;
@@ -1102,7 +1127,7 @@ prb_destroy (prb_env *env)
   cudaFree (env->d_scratch);
   cudaFree (env->d_ptables); cudaFree (env->d_pblob0); cudaFree (env->d_pblobs); cudaFree (env->d_rings);
   cudaFree (env->d_tr_prev); cudaFree (env->d_round_stats); cudaFree (env->d_qw); cudaFree (env->d_tied_list); cudaFree (env->d_tied_flags);
-  cudaFree (env->rp.rows); cudaFree (env->rp.cursor); cudaFree (env->rp.pending);
+  cudaFree (env->rp.rows); cudaFree (env->rp.cursor); cudaFree (env->rp.pending); cudaFree (env->rp.tmin);
   delete env;
   return PRB_OK;
 }
@@ -1587,7 +1612,8 @@ prb_qnet_act (prb_env *env, const prb_step_rec *rec_dev, int32_t *actions_dev, f
   if (!env->d_qw) return fail (PRB_ESTATE, "no Q-network loaded (prb_qnet_load)");
   CUDA_TRY (cudaSetDevice (env->device));
   const Static &st = env->dst;
-  k_qnet_act<<<(st.E + 3) / 4, 128, 0, env->stream>>> (st, env->d_qw, rec_dev, actions_dev, q_out_dev, eps, seed, env->q_step++);
+  k_qnet_act<<<(st.E + 3) / 4, 128, 0, env->stream>>> (st, env->d_qw, rec_dev, actions_dev, q_out_dev, eps, seed, env->q_step++,
+                                                       env->rp.target_mode ? env->rp.tmin : nullptr);
   CUDA_TRY (cudaGetLastError ());
   env->launches++;
   return PRB_OK;
@@ -1610,9 +1636,21 @@ prb_replay_enable (prb_env *env, int64_t rows_per_node, int32_t pending_slots)
   CUDA_TRY (cudaMalloc (&ra.cursor, sizeof (unsigned long long) * (st.M + 1)));
   CUDA_TRY (cudaMalloc (&ra.pending, pend_b));
   ra.missed = ra.cursor + st.M;
+  CUDA_TRY (cudaMalloc (&ra.tmin, sizeof (float) * (size_t) st.E));
+  CUDA_TRY (cudaMemsetAsync (ra.tmin, 0x7F, sizeof (float) * (size_t) st.E, env->stream));    /* 3.39e38: "none" until written */
   CUDA_TRY (cudaMemsetAsync (ra.rows, 0, rows_b, env->stream));
   CUDA_TRY (cudaMemsetAsync (ra.cursor, 0, sizeof (unsigned long long) * (st.M + 1), env->stream));
   CUDA_TRY (cudaMemsetAsync (ra.pending, 0xFF, pend_b, env->stream));
+  return PRB_OK;
+}
+
+int
+prb_replay_set_target_mode (prb_env *env, int on, float gamma)
+{
+  if (!env) return fail (PRB_EINVAL, "null handle");
+  if (!env->rp.rows) return fail (PRB_ESTATE, "replay buffers not enabled (prb_replay_enable)");
+  env->rp.target_mode = on ? 1 : 0;
+  env->rp.gamma = gamma;
   return PRB_OK;
 }
 

@@ -230,6 +230,11 @@ class BatchedRoutingEnv:
         _abi.check(self.lib.prb_replay_enable(self.h, int(rows_per_node), int(pending_slots)))
         self._replay_k = max(len(n) for n in self.neighbors)
 
+    def replay_set_target_mode(self, on: bool = True, gamma: float = 1.0):
+        """`target` signalling: transit transitions store the TD target computed by the next node's network
+        (hop time + gamma * min Q over the actions that do not lead back) instead of the hop time."""
+        _abi.check(self.lib.prb_replay_set_target_mode(self.h, 1 if on else 0, C.c_float(gamma)))
+
     def replay_record(self, actions):
         """Feed the records of the last `step` and the actions that answer them (before the next `step`)."""
         _abi.check(self.lib.prb_replay_record(self.h, C.c_void_p(self._out.data_ptr()), C.c_void_p(actions.data_ptr())))

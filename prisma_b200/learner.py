@@ -1,11 +1,15 @@
 """DQN learner for the dqn_buffer agents (learner half), above the device-side environment.
 
-Mirrors prisma/source/learner.py:160-255 and prisma/source/trainer.py:45-100 for `signaling_type` "ideal":
-node i samples (s, a, r, s', done) from its replay ring (HBM, prb_replay_sample), the TD target of a transition
+Mirrors prisma/source/learner.py:160-255 and prisma/source/trainer.py:45-100.  `signaling_type` "ideal" (and "NN",
+whose neighbour copies are refreshed by `sync_targets` every `sync_step`): node i samples (s, a, r, s', done) from its replay ring (HBM, prb_replay_sample), the TD target of a transition
 whose action pointed at neighbour j is  r + gamma * (1 - done) * min_{a' != back to i} Q_target_j (s'),  the
 loss is Huber (Q_i (s)[a] - target), the optimiser Adam (one state per node, as in the reference).  The M
 networks live in ONE flat float32 tensor [M, P] in exactly the layout prb_qnet_load takes
 (prisma_b200/qnet.py), so that
+
+With `signaling_type` "target" (trainer.py:52-55) the stored reward already IS the target — the next node computed
+it with its own current network when the packet reached it (prb_replay_set_target_mode) — and no target network
+is consulted.
 
 * acting on the device needs no conversion (`env.qnet_load (learner.weights ())`),
 * the data-parallel gradient exchange is a single all-reduce over one bucket (torch.distributed, NCCL over
@@ -54,9 +58,12 @@ def huber(x: torch.Tensor, delta: float = 1.0) -> torch.Tensor:
 
 class DQNLearner:
     def __init__(self, neighbors: Sequence[Sequence[int]], lr: float = 1e-3, gamma: float = 1.0, seed: int = 0,
-                 device: str = "cpu", betas=(0.9, 0.999), adam_eps: float = 1e-7):
+                 device: str = "cpu", betas=(0.9, 0.999), adam_eps: float = 1e-7, signaling_type: str = "ideal"):
         """neighbors[i] = overlay neighbours of node i in action order (BatchedRoutingEnv.neighbors mapped to overlay
         indices).  Adam defaults are Keras' (learner.py:103: tf.keras.optimizers.Adam (lr))."""
+        if signaling_type not in ("ideal", "NN", "target"):
+            raise ValueError("signaling_type must be ideal, NN or target")
+        self.signaling_type = signaling_type
         self.neighbors = [list(n) for n in neighbors]
         self.m = len(self.neighbors)
         self.degrees = [len(n) for n in self.neighbors]
@@ -88,6 +95,8 @@ class DQNLearner:
     def targets(self, node: int, act, rew, nxt, done) -> torch.Tensor:
         """get_neighbor_target_value (learner.py:232-255) for a batch of node `node`."""
         t = rew.clone().float()
+        if self.signaling_type == "target":
+            return t                      # trainer.py:52-53: targets_t = rewards_t
         with torch.no_grad():
             for a, j in enumerate(self.neighbors[node]):
                 sel = (act == a).nonzero(as_tuple=True)[0]

@@ -234,13 +234,13 @@ def main(argv=None) -> dict:
         if params["agent_type"] != "dqn_buffer":
             raise SystemExit("device-side agents exist for dqn_buffer; %s is served through prb_step with the "
                              "caller's own network" % params["agent_type"])
-        if params["prioritizedReplayBuffer"] or params["signaling_type"] != "ideal" and params["train"]:
-            print("note: the learner implements uniform replay and `ideal` target exchange; the simulated control "
-                  "packets of `%s` signalling are generated all the same" % params["signaling_type"], file=sys.stderr)
+        if params["prioritizedReplayBuffer"] and params["train"]:
+            print("note: replay is uniform; the reference's prioritized variant (gradient-step staleness weights) is "
+                  "not built", file=sys.stderr)
         from . import learner as learner_mod, qnet
         nbrs = overlay_neighbor_indices(env)
         learner = learner_mod.DQNLearner(nbrs, lr=params["lr"], gamma=params["gamma"], seed=params["seed"],
-                                         device="cuda:%d" % params["device"])
+                                         device="cuda:%d" % params["device"], signaling_type=params["signaling_type"])
         if params["load_path"]:
             nets = metrics.load_model(params["load_path"])
             import torch
@@ -250,6 +250,9 @@ def main(argv=None) -> dict:
             learner.sync_targets()
         if params["train"]:
             env.replay_enable(rows_per_node=int(params["replay_buffer_max_size"]))
+            if params["signaling_type"] == "target":
+                # the next node computes the target with its own network when the packet reaches it (trainer.py:52-55)
+                env.replay_set_target_mode(True, params["gamma"])
     stats = None
     for episode in range(params["numEpisodes"]):
         t0 = time.time()

@@ -112,3 +112,77 @@ def test_ring_overwrites_oldest_and_fused_loop_feeds_it():
         assert (rows[:, 1 + max(degrees) + 1] > 0).all()  # every stored reward is a positive hop time
     env.check_errors()
     env.close()
+
+
+def test_target_signalling_rows_hold_the_next_nodes_target():
+    """prb_replay_set_target_mode: the reward column of a transit transition is hop_time + gamma * min Q of the NEXT
+    node over its actions that do not lead back (trainer.py:52-60, learner.py:232-255), from the same Q-values that
+    choose the action; terminal and lost-packet rows keep the plain reward.  Checked against the Q-values the
+    device reports (q_out), 1e-6 relative (one fp32 multiply-add); the fused loop stores the same rows."""
+    import torch
+    from prisma_b200 import qnet
+    from prisma_b200.env import BatchedRoutingEnv
+    gamma = 0.9
+    cfg = common.env_config("abilene", num_envs=32, simTime=1.0, load_factor=1.5, pingAsObs=0, activateUnderlayTraffic=1,
+                            max_out_buffer_size=4000)
+    arrays = cfg.load()
+    results = []
+    for fused in (False, True):
+        env = BatchedRoutingEnv(cfg, arrays=arrays)
+        degrees = [len(n) for n in env.neighbors]
+        k_max, m = max(degrees), len(degrees)
+        env.qnet_load(qnet.pack_weights(qnet.init_weights(m, degrees, k_max, seed=3)))
+        env.replay_enable(rows_per_node=1 << 15, pending_slots=4096)
+        env.replay_set_target_mode(True, gamma)
+        if fused:
+            env.step(None)
+            env.step_qnet(800, eps=0.0, seed=5)
+            results.append([env.replay_rows(n) for n in range(m)])
+            env.close()
+            continue
+        q = torch.zeros((env.num_envs, k_max), dtype=torch.float32, device="cuda")
+        history, tmins = [], []
+        batch = env.step(None)
+        for it in range(800):
+            actions = env.qnet_act(eps=0.0, seed=5, q_out=q)
+            env.replay_record(actions)
+            torch.cuda.synchronize()
+            rec = batch.numpy().copy()
+            qq = q.cpu().numpy()
+            tm = np.full(env.num_envs, np.inf, dtype=np.float32)
+            for e in range(env.num_envs):
+                if rec["valid"][e] and rec["need_action"][e]:
+                    me = int(rec["overlay"][e])
+                    ok = [a for a, nb in enumerate(env.neighbors[me]) if int(nb) != int(rec["prev_node"][e])]
+                    if ok:
+                        tm[e] = qq[e, ok].min()
+            history.append((rec, actions.cpu().numpy().copy()))
+            tmins.append(tm)
+            batch = env.step(actions)
+        env.check_errors()
+        # expected rows: the `ideal` bookkeeping with the transit reward replaced by the target
+        for (rec, _), tm in zip(history, tmins):
+            for e in range(env.num_envs):
+                if rec["valid"][e] and rec["ptype"][e] == 0 and not rec["is_new"][e] and rec["need_action"][e] and np.isfinite(tm[e]):
+                    rec["hop_time"][e] = np.float32(np.float32(rec["hop_time"][e]) + np.float32(gamma) * tm[e])
+        exp = expected_rows(history, k_max, degrees, cfg.derived_loss_penalty(arrays.n_overlay), cfg.num_envs, m)
+        counts, missed = env.replay_counts()
+        assert missed == 0 and counts.sum() > 3000
+        n_target = 0
+        for node in range(m):
+            got = env.replay_rows(node)
+            a, b = canon(exp[node], 2 * (1 + k_max) + 3).view(np.float32), canon(got, 2 * (1 + k_max) + 3).view(np.float32)
+            assert a.shape == b.shape
+            rc = 1 + k_max + 1
+            keep = [c for c in range(a.shape[1]) if c != rc]
+            # sort by everything except the reward, then compare rewards within tolerance
+            oa = np.lexsort(np.round(a, 4).T[::-1])
+            ob = np.lexsort(np.round(b, 4).T[::-1])
+            assert np.array_equal(a[oa][:, keep], b[ob][:, keep]), node
+            assert np.allclose(a[oa][:, rc], b[ob][:, rc], rtol=1e-6, atol=1e-7), node
+            n_target += int((got[:, -1] == 0).sum())
+        assert n_target > 1000                       # non-terminal transitions carry targets
+        results.append([env.replay_rows(n) for n in range(m)])
+        env.close()
+    for a, b in zip(*results):
+        assert np.array_equal(canon(a, a.shape[1]), canon(b, b.shape[1]))     # fused loop == explicit loop, bit for bit

@@ -61,3 +61,12 @@ def test_dqn_buffer_training_session(tmp_path, capsys):
                                       "--activateUnderlayTraffic=1", "--pingAsObs=0", "--session_name=eval",
                                       "--load_path=" + os.path.join(root, "final"), "--logs_parent_folder=" + str(tmp_path)])
     assert res2["total_arrived_pkts"] > 0
+
+
+def test_target_signalling_training_session(tmp_path):
+    from prisma_b200 import main as session
+    res = session.main(TOPO_FLAGS + ["--train=1", "--agent_type=dqn_buffer", "--signaling_type=target", "--simTime=2",
+                                     "--num_envs=64", "--activateUnderlayTraffic=1", "--pingAsObs=0", "--batch_size=128",
+                                     "--training_step=0.25", "--lr=0.001", "--iterationNum=400", "--gamma=0.95",
+                                     "--session_name=target", "--logs_parent_folder=" + str(tmp_path)])
+    assert res["total_data_pkts"] > 64 * 500 and res["signaling_overhead"] > 0      # 24-byte target packets per hop

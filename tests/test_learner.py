@@ -163,3 +163,22 @@ def test_gradient_all_reduce_world2_gloo(tmp_path):
         L.W.grad = None
         L.step([None] * L.m, world_size=2, all_reduce=fake_all_reduce)
     assert np.allclose(L.weights(), w0, rtol=1e-5, atol=1e-7)
+
+
+def test_target_signalling_uses_the_stored_targets():
+    """signaling_type "target" (trainer.py:52-53): targets_t = rewards_t, no target network is consulted."""
+    import torch
+    from prisma_b200 import learner
+    L = learner.DQNLearner([[1, 2], [0, 2], [0, 1]], lr=1e-2, seed=1, signaling_type="target")
+    obs = torch.tensor([[2.0, 100.0, 0.0], [1.0, 0.0, 542.0]])
+    act = torch.tensor([0, 1])
+    rew = torch.tensor([0.25, 0.5])
+    nxt = torch.tensor([[2.0, 0.0, 0.0], [1.0, 0.0, 0.0]])
+    done = torch.tensor([0.0, 0.0])
+    assert torch.equal(L.targets(0, act, rew, nxt, done), rew)
+    L.W_target.add_(100.0)                       # would change every ideal-mode target
+    loss, td = L.loss(0, obs, act, rew, nxt, done)
+    q = L.q_values(0, obs).detach()
+    assert torch.allclose(td, q[torch.arange(2), act] - rew)
+    with pytest.raises(ValueError):
+        learner.DQNLearner([[1], [0]], signaling_type="digital_twin")
