@@ -751,6 +751,23 @@ struct PSim
     return b;
   }
 
+  /* the record the handler of c will read first (a packet at the head of a wire or of a queue): ask for its line
+   * while the team still agrees on the round (select -> execute is a few thousand cycles; the record was written by
+   * a lane of this warp and sits in L2) */
+  PRB_HD void
+  prefetch_record (const PCand &c) const
+  {
+#if defined(__CUDA_ARCH__) && !defined(PRB_NO_PREFETCH)
+    if (c.kind == PK_RCV || c.kind == PK_TXC)
+      {
+        const int l = c.idx;
+        uint16_t i = c.kind == PK_RCV ? d.head[l] : d.mid[l];
+        const PRec *p = &d.rings[ps.ring_off[l] + (i & ps.ring_mask[l])];
+        asm volatile ("prefetch.global.L1 [%0];" ::"l"(p));
+      }
+#endif
+  }
+
   /* does c lie before the end of this run and of the simulation? */
   PRB_HD bool
   in_time (const PCand &c) const

@@ -629,6 +629,7 @@ k_run_par (const __grid_constant__ Static st, const __grid_constant__ PStatic ps
       for (int x = gl; x < N; x += T)
         {
           PCand c = sim.select (x);
+          sim.prefetch_record (c);
           d.t_next[x] = c.ts;
           d.cand[x] = (c.kind << 24) | (c.idx & 0xFFFFFF);
           mt = c.ts < mt ? c.ts : mt;
