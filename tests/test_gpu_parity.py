@@ -335,3 +335,42 @@ def test_compat_per_node_view():
     assert counts == [int((od["overlay"] == m).sum()) for m in range(arrays.n_overlay)]
     common.assert_counters_equal(osim.counters(), env.counters()[0])
     env.close()
+
+
+def test_c1_full_length_episode_against_the_restatement():
+    """BASELINE.json configs[0] at its full length: Abilene, sp agent, one 60-second episode.  The event-serial engine's
+    complete ordered log (every injection, enqueue, drop, transmission and reception with nanosecond timestamps and
+    queue bytes), every Gym step and all counters against the restatement; the node-parallel engine's counters and
+    final queues on the same episode; and the conservation law of compute-stats-v2.cc (injected = arrived + lost +
+    still buffered) on both."""
+    cfg = common.env_config("abilene", num_envs=2, simTime=60, load_factor=1.0, pingAsObs=0, activateUnderlayTraffic=1)
+    arrays = cfg.load()
+    table = common.sp_table(arrays)
+    osim = common.oracle_run(cfg, arrays, oracle, policy="table", table=table, env_id=1)
+    oe, oc = osim.events(), osim.counters()
+    assert len(oe) > 400_000 and oc["overlay_injected"] > 40_000
+    env = make_env(cfg, arrays=arrays)
+    env.enable_log(len(oe) * 5 // 4, len(osim.decisions()) * 5 // 4)      # env 0 draws other traffic
+    env.reset()
+    env.set_policy("table", table)
+    env.run()
+    cs = env.counters()
+    env.check_errors(cs)
+    assert env.engine == "serial"
+    assert common.first_event_mismatch(oe, env.events(1)) is None
+    common.assert_steps_equal(osim.decisions(), env.steps(1))
+    common.assert_counters_equal(oc, cs[1])
+    env.close()
+    par = make_env(cfg, arrays=arrays)
+    par.set_engine("parallel")
+    par.set_policy("table", table)
+    par.run()
+    cp = par.counters()
+    par.check_errors(cp)
+    assert par.engine == "parallel"
+    common.assert_counters_equal(oc, cp[1])
+    assert np.array_equal(osim.queue_bytes(), par.queue_bytes(1))
+    for c in (cs[1], cp[1]):
+        buffered = int(c["overlay_injected"] - c["overlay_arrived"] - c["overlay_lost"])
+        assert 0 <= buffered < 400
+    par.close()
