@@ -844,7 +844,7 @@ struct prb_env
   int device = 0;
   cudaStream_t stream = nullptr;
   int G = 32;
-  int max_smem = 0, smem_per_sm = 0;
+  int max_smem = 0, smem_per_sm = 0, num_sms = 148;
   char *d_tables = nullptr;   /* one allocation for all read-only tables */
   char *d_blob0 = nullptr;
   char *d_blobs = nullptr;
@@ -984,19 +984,26 @@ launch_par_t (prb_env *env, const ParArgs &a)
   const Static &st = env->dst;
   const PStatic &ps = env->dps;
   /* block size: the one that keeps the most environments resident per SM (shared memory holds the state
-   * of every team of a block; 1 KB per block is reserved by the system) */
-  int threads = 0, best = -1;
+   * of every team of a block; 1 KB per block is reserved by the system); among equals the one that leaves the
+   * fewest environments on the busiest SM — the step ends with the slowest SM, and warps of one SM slow each
+   * other down through the instruction cache (4096 Abilene environments: 128-thread blocks put 32 on 68 of the
+   * 148 SMs, 64-thread blocks at most 28: 12.49 -> 12.28 ms) */
+  int threads = 0, best = -1, best_peak = 0;
+  const char *forced = getenv ("PRB_PAR_THREADS");          /* experiments: block size of k_run_par */
   for (int t = 128; t >= 32 && t >= T; t >>= 1)
     {
+      if (forced && atoi (forced) != t) continue;
       int teams = t / T;
       size_t per_block = (size_t) teams * ps.pblob_bytes + 1024;
       if (per_block > (size_t) env->max_smem) continue;
       int blocks_sm = (int) std::min<size_t> ((size_t) env->smem_per_sm / per_block, 32);
       blocks_sm = std::min (blocks_sm, PRB_PAR_MINB * 128 / t);  /* registers: __launch_bounds__ of k_run_par */
       int resident = blocks_sm * teams;
-      if (resident > best)
+      int blocks_total = (st.E + teams - 1) / teams;
+      int peak = std::min ((blocks_total + env->num_sms - 1) / std::max (env->num_sms, 1), blocks_sm) * teams;
+      if (resident > best || (resident == best && peak < best_peak))
         {
-          best = resident; threads = t;
+          best = resident; threads = t; best_peak = peak;
         }
     }
   if (threads > 0)
@@ -1163,6 +1170,7 @@ prb_create (const prb_config *cfg, int device, void *cuda_stream, prb_env **out)
   if (cudaSetDevice (device) != cudaSuccess) return guard (fail (PRB_ECUDA, "cudaSetDevice failed"));
   cudaDeviceGetAttribute (&env->max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, device);
   cudaDeviceGetAttribute (&env->smem_per_sm, cudaDevAttrMaxSharedMemoryPerMultiprocessor, device);
+  cudaDeviceGetAttribute (&env->num_sms, cudaDevAttrMultiProcessorCount, device);
   if ((rc = upload_tables (env)) != PRB_OK) return guard (rc);
   build_pmodel (*cfg, env->hm, env->pm);      /* pm.supported says whether prb_run may use the parallel engine */
   env->team = env->hm.st.N <= 8 ? 8 : (env->hm.st.N <= 16 ? 16 : 32);

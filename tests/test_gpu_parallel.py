@@ -222,3 +222,34 @@ def test_handover_to_the_serial_engine(topo, over, num_envs, times, probe):
             x, y = a[k].astype(np.float64), b[k].astype(np.float64)
             assert np.all(np.abs(x - y) <= 1e-6 * np.maximum(np.abs(x), 1e-30)), k
         assert np.array_equal(qa, qb) and np.array_equal(ra, rb)
+
+
+def test_bench_size_batch_engines_agree_and_conserve_packets():
+    """BASELINE.json configs[1] at its full size (4096 Abilene environments, load 0.9, next-hop table): the two engines
+    agree on every integer counter of every environment after one simulated second, and every environment obeys
+    the conservation law of compute-stats-v2.cc (injected = arrived + lost + still in the network)."""
+    cfg = common.env_config("abilene", num_envs=4096, simTime=1.0, load_factor=0.9, pingAsObs=0, activateUnderlayTraffic=1,
+                            agent_type="dqn_routing")
+    arrays = cfg.load()
+    table = common.sp_table(arrays)
+    res = {}
+    for mode in ("serial", "parallel"):
+        env = make_env(cfg, arrays=arrays)
+        env.set_engine(mode)
+        env.set_policy("table", table)
+        env.run()
+        cs = env.counters()
+        env.check_errors(cs)
+        res[mode] = cs
+        env.close()
+    a, b = res["serial"], res["parallel"]
+    for k in common.COUNTER_INTS:
+        assert np.array_equal(a[k], b[k]), k
+    for c in (a, b):
+        for kind in ("overlay", "underlay"):
+            left = c[kind + "_injected"] - c[kind + "_arrived"] - c[kind + "_lost"]
+            assert (left >= 0).all() and (left < 400).all(), kind
+    assert int(b["packet_hops"].sum()) > 4_000_000 and len(np.unique(b["packet_hops"])) > 300
+    # env 4095 against the restatement
+    osim = common.oracle_run(cfg, arrays, oracle, policy="table", table=table, env_id=4095)
+    common.assert_counters_equal(osim.counters(), b[4095])
