@@ -1,0 +1,90 @@
+"""Differential fuzzing of the two simulator cores against the CPU restatement on random small networks: random
+connected underlays (4-14 nodes), all-overlay or a full-mesh overlay on a subset, random traffic matrices, loads,
+buffer sizes, packet sizes, delays, ping observations and signalling types.  Event-serial core (host build of
+sim_core.cuh): the complete ordered log, every Gym step, counters and queues.  Node-parallel core (host build of
+par_core.cuh): the log as a multiset, counters, float bits and queues — or a reported hand-over (an undecided
+tie is allowed, a wrong result is not)."""
+import numpy as np
+import pytest
+
+from oracle import oracle
+from prisma_b200.config import EnvConfig
+from tests import common
+from tests.host_harness import host_sim
+from tests.test_par_host import assert_same_multiset, oracle_uid_map
+
+PRB_ERR_TIE, PRB_ERR_POOL = 32, 1
+HANDED_OVER = []
+
+
+def random_case(seed):
+    rng = np.random.default_rng(1000 + seed)
+    n = int(rng.integers(4, 15))
+    adj = np.zeros((n, n), dtype=np.uint8)
+    for v in range(1, n):                                   # random tree, then a few chords
+        u = int(rng.integers(0, v))
+        adj[u, v] = adj[v, u] = 1
+    for _ in range(int(rng.integers(0, n))):
+        u, v = (int(x) for x in rng.integers(0, n, 2))
+        if u != v and adj[u].sum() < 5 and adj[v].sum() < 5:
+            adj[u, v] = adj[v, u] = 1
+    if rng.random() < 0.5:
+        mp = np.arange(n, dtype=np.int32)
+        ov = adj.copy()
+    else:
+        m = int(rng.integers(3, min(n, 6) + 1))
+        nodes = np.sort(rng.choice(n, size=m, replace=False))
+        mp = -np.ones(n, dtype=np.int32)
+        mp[nodes] = np.arange(m)
+        ov = (1 - np.eye(m)).astype(np.uint8)                # full mesh of tunnels, as in the reference's overlay example
+    tm = (rng.random((n, n)) * 60000).astype(np.uint64)
+    tm[rng.random((n, n)) < 0.3] = 0
+    np.fill_diagonal(tm, 0)
+    train = int(rng.integers(0, 2))
+    kw = dict(physical_adjacency_matrix=adj, overlay_adjacency_matrix=ov, map_overlay=mp, traffic_matrix_bps=tm,
+              load_factor=float(rng.choice([0.5, 1.0, 1.6, 2.5])) * 11.0 / n,
+              max_out_buffer_size=int(rng.choice([2168, 4000, 16260])), packet_size=int(rng.choice([300, 512, 1000])),
+              link_delay=int(rng.choice([1, 2])), simTime=float(rng.choice([1.0, 1.7, 2.5])),
+              pingAsObs=int(rng.integers(0, 2)), activateUnderlayTraffic=int(rng.integers(0, 2)), train=train,
+              signaling_type=str(rng.choice(["NN", "target", "ideal"])) if train else "ideal",
+              agent_type="dqn_buffer" if train else "sp", movingAverageObsSize=int(rng.choice([1, 5])))
+    return EnvConfig(**kw), int(rng.integers(0, 1 << 40))
+
+
+@pytest.mark.parametrize("seed", range(12))
+def test_random_network_both_cores_against_the_restatement(seed):
+    cfg, env_id = random_case(seed)
+    arrays = cfg.load()
+    table = common.sp_table(arrays)
+    # event-serial core, random agent
+    osim = common.oracle_run(cfg, arrays, oracle, policy="random", table=table, seed=5, env_id=env_id)
+    hs = host_sim.HostSim(cfg.abi_params(arrays, env_id_base=env_id))
+    hs.set_policy("random", table, seed=5)
+    hs.run()
+    oe = osim.events()
+    assert len(oe) > 200, len(oe)
+    assert common.first_event_mismatch(oe, hs.events()) is None
+    common.assert_steps_equal(osim.decisions(), hs.steps())
+    common.assert_counters_equal(osim.counters(), hs.counters())
+    assert np.array_equal(osim.queue_bytes(), hs.queue_bytes())
+    # node-parallel core, next-hop table
+    osim = common.oracle_run(cfg, arrays, oracle, policy="table", table=table, env_id=env_id)
+    try:
+        hp = host_sim.HostParSim(cfg.abi_params(arrays, env_id_base=env_id), team=16 if arrays.n_nodes <= 16 else 32)
+    except Exception as ex:          # a configuration build_pmodel refuses (it then runs on the serial core)
+        pytest.skip("parallel core refuses: %s" % ex)
+    hp.set_policy("table", table)
+    hp.run()
+    pc = hp.counters()
+    if pc["errors"] & (PRB_ERR_TIE | PRB_ERR_POOL):
+        HANDED_OVER.append(seed)
+        return                       # handed over to the serial core (prb_handovers): exact by replay
+    common.assert_counters_equal(osim.counters(), pc)
+    assert np.array_equal(osim.queue_bytes(), hp.queue_bytes())
+    umap, _ = oracle_uid_map(osim.events(), arrays, underlay_traffic=bool(cfg.activateUnderlayTraffic))
+    assert_same_multiset(osim.events(), hp.events(), umap)
+
+
+def test_hand_overs_are_the_exception():
+    """Runs after the cases above: an undecided tie must stay rare, or the parallel core would not be one."""
+    assert len(HANDED_OVER) <= 2, HANDED_OVER

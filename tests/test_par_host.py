@@ -26,14 +26,17 @@ def canon(ev, uid_map=None):
     return a[order]
 
 
-def oracle_uid_map(ev, arrays):
+def oracle_uid_map(ev, arrays, underlay_traffic=True):
     """Synthetic traffic: the oracle numbers packets in global injection order, the parallel engine as
-    ordinal * F + flow.  Map the former onto the latter through the injection records."""
+    ordinal * F + flow.  Map the former onto the latter through the injection records.  Without underlay
+    traffic only the pairs of overlay nodes have a source (sim.cc:505-507)."""
     flows = {}
     n = arrays.n_nodes
     f = 0
-    act = arrays.traffic_bps > 0
     m = arrays.map_overlay
+    act = arrays.traffic_bps > 0
+    if not underlay_traffic:
+        act = act & (m[:, None] >= 0) & (m[None, :] >= 0)
     for i in range(n):
         for j in range(n):
             if i != j and act[i, j]:
