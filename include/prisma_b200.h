@@ -125,7 +125,9 @@ typedef struct prb_step_rec
   float e2e_delay;      /*  64 info field 0 (packet-manager.cc:121-122)                                 */
   int32_t valid;        /*  68 1: this env produced a step; 0: it reached simTime (obs[0] == -1 sentinel) */
   int32_t obs[1 + PRB_MAX_K]; /* 72 */
-  int32_t pad_;         /* 140 */
+  int32_t src;          /* 140 underlay id of the packet's source (MyTag source; "Source" of DataPacketManager::getInfo
+                               is its overlay index): what an `opt` agent evaluated by the caller needs next to obs[0]
+                               (prisma/source/utils.py:161-199) */
   int64_t lost_uid[PRB_MAX_LOST]; /* 144 most recent first */
 } prb_step_rec;
 

@@ -56,7 +56,7 @@ class PrbStepRec(C.Structure):
                 ("node", C.c_int32), ("overlay", C.c_int32), ("ptype", C.c_int32), ("done", C.c_int32),
                 ("action", C.c_int32), ("need_action", C.c_int32), ("nobs", C.c_int32), ("is_new", C.c_int32),
                 ("prev_node", C.c_int32), ("n_lost", C.c_int32), ("e2e_delay", C.c_float), ("valid", C.c_int32),
-                ("obs", C.c_int32 * (1 + PRB_MAX_K)), ("pad_", C.c_int32), ("lost_uid", C.c_int64 * PRB_MAX_LOST)]
+                ("obs", C.c_int32 * (1 + PRB_MAX_K)), ("src", C.c_int32), ("lost_uid", C.c_int64 * PRB_MAX_LOST)]
 
 
 class PrbCounters(C.Structure):

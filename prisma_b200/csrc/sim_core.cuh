@@ -1042,7 +1042,7 @@ struct Sim
         r->prev_node = p_prev_node (p);
         r->hop_time = dmul_ ((double) (sc->now - p.prev_t), 1e-9);
       }
-    r->pad_ = 0;
+    r->src = p_src (p);
   }
 
   PRB_HD void
@@ -1065,7 +1065,7 @@ struct Sim
     for (int i = 0; i < PRB_MAX_LOST; i++) r->lost_uid[i] = 0;
     /* GetGameOver asks the DATA manager, whose m_destination is the last data packet seen here */
     r->done = d.last_dst[m] == x;
-    r->pad_ = 0;
+    r->src = p_src (p);
   }
 
   /* PacketRoutingEnv::ExecuteActions + DataPacketManager::sendPacket, then the rest of Receive */

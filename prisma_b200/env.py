@@ -390,8 +390,8 @@ class Ns3EnvGroup:
         elif rec["ptype"] == 2:
             f += [("PacketIdSignaled", int(rec["uid"])), ("Arrived at final dest", 1)]
         else:
-            # Source is not carried by the step record (no consumer: treat_info stops at token 18 for data)
-            f += [("Packet Lost", lost), ("Source", -1), ("Destination", int(rec["obs"][0])), ("node", int(rec["overlay"]))]
+            f += [("Packet Lost", lost), ("Source", int(mo[int(rec["src"])])), ("Destination", int(rec["obs"][0])),
+                  ("node", int(rec["overlay"]))]
         return ",".join("%s=%s" % kv for kv in f)
 
 

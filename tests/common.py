@@ -149,6 +149,15 @@ def assert_big_signaling_fields(big, uid, prev_node, map_overlay):
     assert np.array_equal(np.asarray(map_overlay)[np.asarray(prev_node)[sel]], big[sel, 2])
 
 
+def assert_step_sources(events, steps):
+    """prb_step_rec.src of every data step = the source its packet was injected with (INJ record of that uid)."""
+    inj = events[(events["kind"] == 0) & (events["type"] == 0)]
+    src_of = dict(zip(inj["uid"].tolist(), inj["src"].tolist()))
+    data = steps[steps["ptype"] == 0]
+    assert len(data) > 0
+    assert all(src_of[int(u)] == int(s) for u, s in zip(data["uid"], data["src"]))
+
+
 def replay_inputs(g):
     """(injection arrays, policy kind, policy data, seed) of a golden fixture."""
     inj = g.injections

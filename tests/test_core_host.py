@@ -71,6 +71,7 @@ def test_core_matches_oracle_synthetic_traffic(topo, over, policy, env_id):
     assert len(oe) > 1000
     assert common.first_event_mismatch(oe, he) is None
     common.assert_steps_equal(osim.decisions(), hs.steps())
+    common.assert_step_sources(oe, hs.steps())
     common.assert_counters_equal(osim.counters(), hs.counters())
     assert np.array_equal(osim.queue_bytes(), hs.queue_bytes())
 

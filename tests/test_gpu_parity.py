@@ -93,6 +93,7 @@ def test_cuda_matches_oracle_synthetic_traffic(topo, over, policy):
         assert len(oe) > 1000
         assert common.first_event_mismatch(oe, env.events(e)) is None
         common.assert_steps_equal(osim.decisions(), env.steps(e))
+        common.assert_step_sources(oe, env.steps(e))
         common.assert_counters_equal(osim.counters(), cs[e])
         assert np.array_equal(osim.queue_bytes(), env.queue_bytes(e))
     # different env ids draw different traffic
