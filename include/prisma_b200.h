@@ -244,6 +244,17 @@ int prb_replay_record (prb_env *env, const prb_step_rec *rec_dev, const int32_t 
  * lost-packet transitions keep the plain reward.  Needs the device-side agents (prb_qnet_act before
  * prb_replay_record, or prb_step_qnet). */
 int prb_replay_set_target_mode (prb_env *env, int on, float gamma);
+/* Prioritized variant (prisma/source/replay_buffer.py:393-534, used with `target` signalling: forwarder.py:494-505): draws
+ * stay uniform (replay_buffer.py:497); every row remembers the gradient step of the network that produced its target
+ * (prb_replay_set_gradient_steps: the learners' step counters, host [M]), every node the latest step it has seen per
+ * action, and prb_replay_sample_weighted returns weight = p / sum (p) * len with p = (row step / latest step) ^ alpha
+ * — the state the reference reaches after its next update_priorities (until then it keeps new rows at max priority).
+ * Without the prioritized variant the weights are 1.  prb_replay_read_priorities: row steps and latest steps of a node. */
+int prb_replay_enable_prioritized (prb_env *env, float alpha);
+int prb_replay_set_gradient_steps (prb_env *env, const int32_t *steps /* host [M] */);
+int prb_replay_sample_weighted (prb_env *env, int32_t node, int32_t batch, uint64_t seed, float *obs_dev, int32_t *action_dev,
+                                float *reward_dev, float *next_obs_dev, float *done_dev, float *weights_dev);
+int prb_replay_read_priorities (prb_env *env, int32_t node, float *gstep_host, int64_t max_rows, int32_t *latest_host /* [K] */);
 int prb_replay_counts (prb_env *env, int64_t *rows_written /* host [M] */, int64_t *missed /* host, may be NULL */);
 int prb_replay_read (prb_env *env, int32_t node, float *rows_host, int64_t max_rows, int64_t *n_rows);
 int prb_replay_sample (prb_env *env, int32_t node, int32_t batch, uint64_t seed, float *obs_dev, int32_t *action_dev,

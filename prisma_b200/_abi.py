@@ -177,6 +177,10 @@ def lib():
         "prb_replay_counts": (C.c_int, [vp, C.POINTER(i64), C.POINTER(i64)]),
         "prb_replay_read": (C.c_int, [vp, i32, vp, i64, C.POINTER(i64)]),
         "prb_replay_sample": (C.c_int, [vp, i32, i32, u64, vp, vp, vp, vp, vp]),
+        "prb_replay_sample_weighted": (C.c_int, [vp, i32, i32, u64, vp, vp, vp, vp, vp, vp]),
+        "prb_replay_enable_prioritized": (C.c_int, [vp, C.c_float]),
+        "prb_replay_set_gradient_steps": (C.c_int, [vp, C.POINTER(i32)]),
+        "prb_replay_read_priorities": (C.c_int, [vp, i32, vp, i64, C.POINTER(i32)]),
         "prb_engine": (C.c_int, [vp]),
         "prb_handovers": (C.c_int, [vp]),
         "prb_round_stats": (C.c_int, [vp, C.POINTER(i64), C.POINTER(i64)]),
@@ -195,7 +199,9 @@ EXPORTS = ["prb_last_error", "prb_version", "prb_seconds_to_ns", "prb_ns_to_seco
            "prb_read_steps", "prb_run", "prb_step", "prb_step_host", "prb_counters_host", "prb_counters_dev",
            "prb_queue_bytes", "prb_sync", "prb_launch_count", "prb_set_engine", "prb_engine", "prb_round_stats", "prb_handovers",
            "prb_qnet_num_floats", "prb_qnet_load", "prb_qnet_act", "prb_step_qnet",
-           "prb_replay_enable", "prb_replay_set_target_mode", "prb_replay_record", "prb_replay_counts", "prb_replay_read", "prb_replay_sample"]
+           "prb_replay_enable", "prb_replay_set_target_mode", "prb_replay_record", "prb_replay_counts", "prb_replay_read", "prb_replay_sample",
+           "prb_replay_sample_weighted", "prb_replay_enable_prioritized", "prb_replay_set_gradient_steps",
+           "prb_replay_read_priorities"]
 
 
 class PrbError(RuntimeError):

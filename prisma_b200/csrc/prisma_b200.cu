@@ -218,13 +218,29 @@ struct ReplayArgs
   int32_t target_mode;
   float gamma;
   float *tmin;                /* [E]: that minimum for the pending step of every environment (unfused path) */
+  /* prioritized variant (replay_buffer.py:393-534): a row remembers the gradient step of the network that produced
+   * its target, a node the latest gradient step it has seen per action; weight = (row / latest) ^ alpha */
+  float *row_gstep;           /* [M][cap] or null */
+  int32_t *latest;            /* [M][K] */
+  const int32_t *node_gstep;  /* [M] gradient steps taken by every node's learner (host-set) */
+  double *psum;               /* scratch: sum of the priorities of one node */
+  float alpha;
 };
 
 __device__ inline void
 replay_push (const Static &st, const ReplayArgs &ra, int node, const int32_t *ent, float reward, const int32_t *next_obs,
-             int next_n, int done)
+             int next_n, int done, int from_node = -1)
 {
   unsigned long long slot = atomicAdd (&ra.cursor[node], 1ull) % (unsigned long long) ra.cap;
+  if (ra.row_gstep)
+    {
+      /* forwarder.py:494-505: a transit transition carries the gradient step of the node that computed its target
+       * and raises the latest step seen for that action; :227-233: a lost packet is added with the latest one */
+      int32_t *lat = &ra.latest[(size_t) node * st.K + ent[3]];
+      int32_t g = from_node >= 0 ? ra.node_gstep[from_node] : *lat;
+      if (from_node >= 0) atomicMax (lat, g);
+      ra.row_gstep[(size_t) node * ra.cap + slot] = (float) g;
+    }
   float *row = ra.rows + ((size_t) node * ra.cap + slot) * ra.R;
   const int ow = 1 + st.K;
   for (int i = 0; i < ow; i++) row[i] = (float) ent[4 + i];
@@ -269,7 +285,7 @@ replay_record_one (const Static &st, const ReplayArgs &ra, int e, const prb_step
         {
           float rew = (float) r->hop_time;
           if (ra.target_mode && r->need_action && tmin < 1e37f) rew = rew + ra.gamma * tmin;
-          replay_push (st, ra, ent[2], ent, rew, r->obs, r->nobs, r->done);
+          replay_push (st, ra, ent[2], ent, rew, r->obs, r->nobs, r->done, r->overlay);
           ent[2] = -1;
         }
       else
@@ -291,9 +307,32 @@ k_replay_record (const __grid_constant__ Static st, const ReplayArgs ra, const p
   replay_record_one (st, ra, e, &rec[e], actions[e], ra.target_mode && ra.tmin ? ra.tmin[e] : INFINITY);
 }
 
+/* priority of row idx of a node: (gradient step of the row / latest step seen for its action) ^ alpha */
+__device__ __forceinline__ float
+replay_priority (const ReplayArgs &ra, int node, unsigned long long idx, int ow, int K)
+{
+  const float *row = ra.rows + ((size_t) node * ra.cap + idx) * ra.R;
+  int a = (int) row[ow];
+  float lat = (float) ra.latest[(size_t) node * K + a];
+  float g = ra.row_gstep[(size_t) node * ra.cap + idx];
+  return powf (g / (lat > 0.0f ? lat : 1.0f), ra.alpha);
+}
+
+__global__ void
+k_replay_priority_sum (const ReplayArgs ra, int node, int ow, int K)
+{
+  unsigned long long n = ra.cursor[node];
+  if (n > (unsigned long long) ra.cap) n = (unsigned long long) ra.cap;
+  double acc = 0.0;
+  for (unsigned long long i = (unsigned long long) blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (unsigned long long) gridDim.x * blockDim.x)
+    acc += (double) replay_priority (ra, node, i, ow, K);
+  for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync (0xFFFFFFFFu, acc, o);
+  if ((threadIdx.x & 31) == 0 && acc != 0.0) atomicAdd (ra.psum, acc);
+}
+
 __global__ void
 k_replay_sample (const ReplayArgs ra, int node, int batch, int ow, uint64_t seed, uint64_t call, float *obs, int32_t *act,
-                 float *rew, float *next_obs, float *done)
+                 float *rew, float *next_obs, float *done, float *weights = nullptr, int K = 0)
 {
   const int b = blockIdx.x * blockDim.x + threadIdx.x;
   if (b >= batch) return;
@@ -309,6 +348,8 @@ k_replay_sample (const ReplayArgs ra, int node, int batch, int ow, uint64_t seed
   rew[b] = row[ow + 1];
   for (int i = 0; i < ow; i++) next_obs[(size_t) b * ow + i] = row[ow + 2 + i];
   done[b] = row[2 * ow + 2];
+  /* PrioritizedReplayBuffer.sample: uniform draws, weight = priority / sum of priorities * len (replay_buffer.py:497-498) */
+  if (weights) weights[b] = ra.row_gstep ? (float) ((double) replay_priority (ra, node, idx, ow, K) / *ra.psum * (double) n) : 1.0f;
 }
 
 
@@ -1136,6 +1177,7 @@ prb_destroy (prb_env *env)
   cudaFree (env->d_ptables); cudaFree (env->d_pblob0); cudaFree (env->d_pblobs); cudaFree (env->d_rings);
   cudaFree (env->d_tr_prev); cudaFree (env->d_round_stats); cudaFree (env->d_qw); cudaFree (env->d_tied_list); cudaFree (env->d_tied_flags);
   cudaFree (env->rp.rows); cudaFree (env->rp.cursor); cudaFree (env->rp.pending); cudaFree (env->rp.tmin);
+  cudaFree (env->rp.row_gstep); cudaFree (env->rp.latest); cudaFree (env->rp.psum);
   delete env;
   return PRB_OK;
 }
@@ -1724,6 +1766,81 @@ prb_replay_sample (prb_env *env, int32_t node, int32_t batch, uint64_t seed, flo
                                                                   reward_dev, next_obs_dev, done_dev);
   CUDA_TRY (cudaGetLastError ());
   env->launches++;
+  return PRB_OK;
+}
+
+int
+prb_replay_enable_prioritized (prb_env *env, float alpha)
+{
+  if (!env || alpha < 0.0f) return fail (PRB_EINVAL, "bad argument");
+  if (!env->rp.rows) return fail (PRB_ESTATE, "replay buffers not enabled (prb_replay_enable)");
+  if (env->rp.row_gstep) return fail (PRB_ESTATE, "prioritized replay already enabled");
+  CUDA_TRY (cudaSetDevice (env->device));
+  const Static &st = env->dst;
+  ReplayArgs &ra = env->rp;
+  size_t rows = (size_t) st.M * (size_t) ra.cap;
+  std::vector<int32_t> ones ((size_t) st.M * st.K + st.M, 1);       /* latest_gradient_step = [1] * nb_neighbors (:411) */
+  int32_t *ints = nullptr;
+  CUDA_TRY (cudaMalloc (&ra.row_gstep, sizeof (float) * rows));
+  CUDA_TRY (cudaMalloc (&ints, sizeof (int32_t) * ones.size ()));
+  CUDA_TRY (cudaMalloc (&ra.psum, sizeof (double)));
+  CUDA_TRY (cudaMemsetAsync (ra.row_gstep, 0, sizeof (float) * rows, env->stream));
+  CUDA_TRY (cudaMemcpyAsync (ints, ones.data (), sizeof (int32_t) * ones.size (), cudaMemcpyHostToDevice, env->stream));
+  CUDA_TRY (cudaStreamSynchronize (env->stream));
+  ra.latest = ints;
+  ra.node_gstep = ints + (size_t) st.M * st.K;
+  ra.alpha = alpha;
+  return PRB_OK;
+}
+
+int
+prb_replay_set_gradient_steps (prb_env *env, const int32_t *steps /* host [M] */)
+{
+  if (!env || !steps) return fail (PRB_EINVAL, "null argument");
+  if (!env->rp.row_gstep) return fail (PRB_ESTATE, "prioritized replay not enabled (prb_replay_enable_prioritized)");
+  CUDA_TRY (cudaSetDevice (env->device));
+  CUDA_TRY (cudaMemcpyAsync (const_cast<int32_t *> (env->rp.node_gstep), steps, sizeof (int32_t) * env->dst.M, cudaMemcpyHostToDevice,
+                             env->stream));
+  CUDA_TRY (cudaStreamSynchronize (env->stream));
+  return PRB_OK;
+}
+
+int
+prb_replay_sample_weighted (prb_env *env, int32_t node, int32_t batch, uint64_t seed, float *obs_dev, int32_t *action_dev,
+                            float *reward_dev, float *next_obs_dev, float *done_dev, float *weights_dev)
+{
+  if (!env || !obs_dev || !action_dev || !reward_dev || !next_obs_dev || !done_dev || !weights_dev || batch < 1)
+    return fail (PRB_EINVAL, "bad argument");
+  if (!env->rp.rows) return fail (PRB_ESTATE, "replay buffers not enabled (prb_replay_enable)");
+  if (node < 0 || node >= env->dst.M) return fail (PRB_EINVAL, "node out of range");
+  CUDA_TRY (cudaSetDevice (env->device));
+  const int ow = 1 + env->dst.K;
+  if (env->rp.row_gstep)
+    {
+      CUDA_TRY (cudaMemsetAsync (env->rp.psum, 0, sizeof (double), env->stream));
+      k_replay_priority_sum<<<64, 256, 0, env->stream>>> (env->rp, node, ow, env->dst.K);
+      env->launches++;
+    }
+  k_replay_sample<<<(batch + 127) / 128, 128, 0, env->stream>>> (env->rp, node, batch, ow, seed, env->rp_call++, obs_dev, action_dev,
+                                                                  reward_dev, next_obs_dev, done_dev, weights_dev, env->dst.K);
+  CUDA_TRY (cudaGetLastError ());
+  env->launches++;
+  return PRB_OK;
+}
+
+int
+prb_replay_read_priorities (prb_env *env, int32_t node, float *gstep_host, int64_t max_rows, int32_t *latest_host /* [K] */)
+{
+  if (!env || !gstep_host || !latest_host) return fail (PRB_EINVAL, "null argument");
+  if (!env->rp.row_gstep) return fail (PRB_ESTATE, "prioritized replay not enabled (prb_replay_enable_prioritized)");
+  if (node < 0 || node >= env->dst.M) return fail (PRB_EINVAL, "node out of range");
+  CUDA_TRY (cudaSetDevice (env->device));
+  int64_t n = std::min<int64_t> (max_rows, env->rp.cap);
+  CUDA_TRY (cudaMemcpyAsync (gstep_host, env->rp.row_gstep + (size_t) node * env->rp.cap, sizeof (float) * (size_t) n, cudaMemcpyDeviceToHost,
+                             env->stream));
+  CUDA_TRY (cudaMemcpyAsync (latest_host, env->rp.latest + (size_t) node * env->dst.K, sizeof (int32_t) * env->dst.K,
+                             cudaMemcpyDeviceToHost, env->stream));
+  CUDA_TRY (cudaStreamSynchronize (env->stream));
   return PRB_OK;
 }
 

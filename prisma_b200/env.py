@@ -254,8 +254,31 @@ class BatchedRoutingEnv:
             _abi.check(self.lib.prb_replay_read(self.h, int(node), out.ctypes.data_as(C.c_void_p), n.value, C.byref(n)))
         return out
 
-    def replay_sample(self, node: int, batch: int, seed: int = 0):
-        """ReplayBuffer.sample on the device: (obs [B,1+K], action [B], reward [B], next_obs [B,1+K], done [B])."""
+    def replay_enable_prioritized(self, alpha: float = 1.0):
+        """PrioritizedReplayBuffer (replay_buffer.py:393-534): rows remember the gradient step of the network that
+        produced their target; `replay_sample (..., weighted=True)` returns the importance weights."""
+        _abi.check(self.lib.prb_replay_enable_prioritized(self.h, C.c_float(alpha)))
+        self._replay_prioritized = True
+
+    def replay_set_gradient_steps(self, steps):
+        """Gradient steps taken so far by every node's learner (int [M])."""
+        s = np.ascontiguousarray(steps, dtype=np.int32)
+        assert s.size == len(self.neighbors)
+        _abi.check(self.lib.prb_replay_set_gradient_steps(self.h, _abi.ptr(s, C.c_int32)))
+
+    def replay_priorities(self, node: int):
+        """(gradient step of every stored row of `node`, latest step seen per action)."""
+        n = len(self.replay_rows(node))
+        g = np.zeros(max(n, 1), dtype=np.float32)
+        lat = np.zeros(self._replay_k, dtype=np.int32)
+        _abi.check(self.lib.prb_replay_read_priorities(self.h, int(node), g.ctypes.data_as(C.c_void_p), n, _abi.ptr(lat, C.c_int32)))
+        return g[:n], lat
+
+    def replay_sample(self, node: int, batch: int, seed: int = 0, weighted: bool = False):
+        """ReplayBuffer.sample on the device: (obs [B,1+K], action [B], reward [B], next_obs [B,1+K], done [B]);
+        weighted: also the importance weights [B] of PrioritizedReplayBuffer.sample (ones without the prioritized variant)."""
+        if weighted:
+            return self._replay_sample_weighted(node, batch, seed)
         torch = self._torch
         dev, ow = self._out.device, 1 + self._replay_k
         obs = torch.zeros((batch, ow), dtype=torch.float32, device=dev)
@@ -267,6 +290,19 @@ class BatchedRoutingEnv:
                                               C.c_void_p(act.data_ptr()), C.c_void_p(rew.data_ptr()),
                                               C.c_void_p(nxt.data_ptr()), C.c_void_p(done.data_ptr())))
         return obs, act, rew, nxt, done
+
+    def _replay_sample_weighted(self, node, batch, seed):
+        torch = self._torch
+        dev, ow = self._out.device, 1 + self._replay_k
+        obs = torch.zeros((batch, ow), dtype=torch.float32, device=dev)
+        nxt = torch.zeros((batch, ow), dtype=torch.float32, device=dev)
+        act = torch.zeros(batch, dtype=torch.int32, device=dev)
+        rew, done, wts = (torch.zeros(batch, dtype=torch.float32, device=dev) for _ in range(3))
+        _abi.check(self.lib.prb_replay_sample_weighted(self.h, int(node), int(batch), int(seed), C.c_void_p(obs.data_ptr()),
+                                                       C.c_void_p(act.data_ptr()), C.c_void_p(rew.data_ptr()),
+                                                       C.c_void_p(nxt.data_ptr()), C.c_void_p(done.data_ptr()),
+                                                       C.c_void_p(wts.data_ptr())))
+        return obs, act, rew, nxt, done, wts
 
     # ---- read-out ----
     def counters(self) -> np.ndarray:

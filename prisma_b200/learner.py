@@ -164,8 +164,13 @@ class DQNLearner:
             if counts[i] < need:
                 batches.append(None)
                 continue
-            obs, act, rew, nxt, done = env.replay_sample(i, batch_size, seed=seed)
-            batches.append((obs, act, rew, nxt, done))
+            if getattr(env, "_replay_prioritized", False):
+                # PrioritizedReplayBuffer.sample: importance weights multiply the Huber errors (learner.py:176-179)
+                batches.append(env.replay_sample(i, batch_size, seed=seed, weighted=True))
+            else:
+                batches.append(env.replay_sample(i, batch_size, seed=seed))
         out = self.step(batches, world_size=world_size, all_reduce=all_reduce)
         env.qnet_load(self.weights())
+        if getattr(env, "_replay_prioritized", False):
+            env.replay_set_gradient_steps(self.steps.to(torch.int32).cpu().numpy())     # the targets computed from now on
         return out

@@ -234,9 +234,9 @@ def main(argv=None) -> dict:
         if params["agent_type"] != "dqn_buffer":
             raise SystemExit("device-side agents exist for dqn_buffer; %s is served through prb_step with the "
                              "caller's own network" % params["agent_type"])
-        if params["prioritizedReplayBuffer"] and params["train"]:
-            print("note: replay is uniform; the reference's prioritized variant (gradient-step staleness weights) is "
-                  "not built", file=sys.stderr)
+        if params["prioritizedReplayBuffer"] and params["train"] and params["signaling_type"] != "target":
+            print("note: the reference feeds its prioritized buffer from `target` signalling only (forwarder.py:494-505); "
+                  "with `%s` the weights stay 1" % params["signaling_type"], file=sys.stderr)
         from . import learner as learner_mod, qnet
         nbrs = overlay_neighbor_indices(env)
         learner = learner_mod.DQNLearner(nbrs, lr=params["lr"], gamma=params["gamma"], seed=params["seed"],
@@ -253,6 +253,8 @@ def main(argv=None) -> dict:
             if params["signaling_type"] == "target":
                 # the next node computes the target with its own network when the packet reaches it (trainer.py:52-55)
                 env.replay_set_target_mode(True, params["gamma"])
+            if params["prioritizedReplayBuffer"]:
+                env.replay_enable_prioritized(alpha=1.0)       # agent.py:67: PrioritizedReplayBuffer (size, 1, ...)
     stats = None
     for episode in range(params["numEpisodes"]):
         t0 = time.time()

@@ -186,3 +186,75 @@ def test_target_signalling_rows_hold_the_next_nodes_target():
         env.close()
     for a, b in zip(*results):
         assert np.array_equal(canon(a, a.shape[1]), canon(b, b.shape[1]))     # fused loop == explicit loop, bit for bit
+
+
+def test_prioritized_variant_weights_rows_by_gradient_step_staleness():
+    """PrioritizedReplayBuffer (replay_buffer.py:393-534) as the reference uses it with `target` signalling
+    (forwarder.py:494-505): rows remember the gradient step of the node that computed their target, the node the latest
+    step seen per action; sample = uniform draws with weight p / sum (p) * len, p = (row step / latest step) ^ alpha."""
+    import torch
+    from prisma_b200 import qnet
+    from prisma_b200.env import BatchedRoutingEnv
+    cfg = common.env_config("abilene", num_envs=32, simTime=1.0, load_factor=1.5, pingAsObs=0, activateUnderlayTraffic=1,
+                            max_out_buffer_size=4000)
+    arrays = cfg.load()
+    env = BatchedRoutingEnv(cfg, arrays=arrays)
+    degrees = [len(n) for n in env.neighbors]
+    k_max, m = max(degrees), len(degrees)
+    env.qnet_load(qnet.pack_weights(qnet.init_weights(m, degrees, k_max, seed=3)))
+    env.replay_enable(rows_per_node=1 << 15, pending_slots=4096)
+    env.replay_set_target_mode(True, 1.0)
+    alpha = 0.5
+    env.replay_enable_prioritized(alpha)
+    u2o = {int(u): i for i, u in enumerate(env.overlay_to_underlay)}
+    steps = np.ones(m, dtype=np.int32)
+    for phase in range(4):                       # the learners advance between collection phases, node i by i + 1 steps
+        env.replay_set_gradient_steps(steps)
+        env.step_qnet(250, eps=0.2, seed=phase)
+        steps = steps + np.arange(1, m + 1, dtype=np.int32)
+    env.check_errors()
+    counts, missed = env.replay_counts()
+    assert missed == 0
+    node = int(np.argmax(counts))
+    rows = env.replay_rows(node)
+    g, latest = env.replay_priorities(node)
+    assert len(g) == len(rows) > 500
+    act = rows[:, 1 + k_max].astype(int)
+    done_or_lost = rows[:, -1] == 1
+    # a transit row carries the step count of the neighbour its action pointed at, at the time the target was computed
+    for a, nb in enumerate(env.neighbors[node]):
+        j = u2o[int(nb)]
+        allowed = {1 + p * (j + 1) for p in range(4)} | {1}
+        sel = (act == a) & ~done_or_lost
+        assert sel.any() and set(np.unique(g[sel]).astype(int)) <= allowed, (a, np.unique(g[sel]))
+        assert latest[a] == g[act == a].max()
+    assert len(np.unique(g)) > 2
+    p = (g / latest[act]) ** alpha
+    obs, a_s, rew, nxt, done, w = env.replay_sample(node, 2048, seed=4, weighted=True)
+    torch.cuda.synchronize()
+    samp = np.concatenate([obs.cpu().numpy(), a_s.cpu().numpy()[:, None].astype(np.float32), rew.cpu().numpy()[:, None],
+                           nxt.cpu().numpy(), done.cpu().numpy()[:, None]], axis=1)
+    expect = {}
+    for r, pi in zip(rows, p):
+        expect.setdefault(r.tobytes(), set()).add(np.float32(pi / p.sum() * len(rows)))
+    w = w.cpu().numpy()
+    for r, wi in zip(samp, w):
+        cands = expect[r.tobytes()]
+        assert min(abs(float(c) - float(wi)) for c in cands) < 1e-4 * max(1.0, float(wi)), (cands, wi)
+    assert 0.5 < w.mean() < 1.5 and w.std() > 0.01          # the weights average to ~1 and do differ
+    # the learner multiplies the Huber errors by them (learner.py:176-179)
+    from prisma_b200 import learner
+    neigh = [[u2o[int(u)] for u in nb] for nb in env.neighbors]
+    L = learner.DQNLearner(neigh, lr=1e-3, seed=2, device="cuda", signaling_type="target")
+    mse = L.train_on_env(env, batch_size=256, seed=1)
+    assert all(v is not None and np.isfinite(v) for v in mse)
+    g2, _ = env.replay_priorities(node)
+    assert np.array_equal(g2, g)                 # sampling does not touch the stored steps
+    # without the prioritized variant the weights are 1
+    env2 = BatchedRoutingEnv(cfg, arrays=arrays)
+    env2.qnet_load(qnet.pack_weights(qnet.init_weights(m, degrees, k_max, seed=3)))
+    env2.replay_enable(rows_per_node=4096)
+    env2.step_qnet(200, eps=0.1, seed=0)
+    assert bool((env2.replay_sample(node, 64, weighted=True)[5] == 1).all())
+    env.close()
+    env2.close()

@@ -70,3 +70,12 @@ def test_target_signalling_training_session(tmp_path):
                                      "--training_step=0.25", "--lr=0.001", "--iterationNum=400", "--gamma=0.95",
                                      "--session_name=target", "--logs_parent_folder=" + str(tmp_path)])
     assert res["total_data_pkts"] > 64 * 500 and res["signaling_overhead"] > 0      # 24-byte target packets per hop
+
+
+def test_prioritized_target_training_session(tmp_path):
+    from prisma_b200 import main as session
+    res = session.main(TOPO_FLAGS + ["--train=1", "--agent_type=dqn_buffer", "--signaling_type=target",
+                                     "--prioritizedReplayBuffer=1", "--simTime=2", "--num_envs=64", "--pingAsObs=0",
+                                     "--activateUnderlayTraffic=1", "--batch_size=128", "--training_step=0.25", "--lr=0.001",
+                                     "--iterationNum=400", "--session_name=prio", "--logs_parent_folder=" + str(tmp_path)])
+    assert res["total_data_pkts"] > 64 * 500 and res["avg_e2e_delay"] > 0
