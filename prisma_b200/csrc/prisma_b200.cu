@@ -67,14 +67,28 @@ qnet_floats_per_node (int M, int K)
   return (int64_t) M * QH1 + QH1 + (int64_t) K * QH1 + QH1 + 2 * QH1 * QH2 + QH2 + QH2 * QH2 + QH2 + (int64_t) QH2 * K + K;
 }
 
-__device__ __forceinline__ float
+#ifndef PRB_ELU_ATTR
+#define PRB_ELU_ATTR __forceinline__
+#endif
+__device__ PRB_ELU_ATTR float
 elu_ (float x)
 {
   return x > 0.0f ? x : expm1f (x);
 }
 
-/* all 32 lanes of a warp: action for the pending data step *r of environment-id eid (every lane returns it) */
-__device__ __forceinline__ int
+/* all 32 lanes of a warp: action for the pending data step *r of environment-id eid (every lane returns it).
+ * One copy in the instruction stream and modest unrolling (4): fully unrolled and inlined at both call
+ * sites of k_advance it was 8 268 SASS instructions, and the 27 warps of an SM, each at its own point of a 50 KB hot
+ * loop, spent 18 of 25 cycles per issue waiting for instructions (profiles/r1_k_advance_gym_*).  The order of the
+ * additions of every accumulator is the loop order either way. */
+#ifndef PRB_QNET_ATTR
+#define PRB_QNET_ATTR __forceinline__
+#endif
+#ifndef PRB_QNET_UNROLL
+#define PRB_QNET_UNROLL 8
+#endif
+constexpr int QNET_UNROLL = PRB_QNET_UNROLL;
+__device__ PRB_QNET_ATTR int
 qnet_forward (const Static &st, const float *w, const prb_step_rec *r, int lane, float eps, uint64_t seed, uint64_t step, uint64_t eid,
               float *q_row, float *tmin = nullptr)
 {
@@ -101,12 +115,14 @@ qnet_forward (const Static &st, const float *w, const prb_step_rec *r, int lane,
   float hb = elu_ (acc);
   /* Dense(64) on [h_d, h_b]: lane j owns outputs j and j + 32 */
   float a0 = b1[lane], a1 = b1[lane + 32];
+#pragma unroll QNET_UNROLL
   for (int i = 0; i < QH1; i++)
     {
       float c = __shfl_sync (0xFFFFFFFFu, hd, i);
       a0 = fmaf (c, w1[(size_t) i * QH2 + lane], a0);
       a1 = fmaf (c, w1[(size_t) i * QH2 + lane + 32], a1);
     }
+#pragma unroll QNET_UNROLL
   for (int i = 0; i < QH1; i++)
     {
       float c = __shfl_sync (0xFFFFFFFFu, hb, i);
@@ -115,12 +131,14 @@ qnet_forward (const Static &st, const float *w, const prb_step_rec *r, int lane,
     }
   float h0 = elu_ (a0), h1 = elu_ (a1);
   a0 = b2[lane]; a1 = b2[lane + 32];
+#pragma unroll QNET_UNROLL
   for (int i = 0; i < 32; i++)
     {
       float c = __shfl_sync (0xFFFFFFFFu, h0, i);
       a0 = fmaf (c, w2[(size_t) i * QH2 + lane], a0);
       a1 = fmaf (c, w2[(size_t) i * QH2 + lane + 32], a1);
     }
+#pragma unroll QNET_UNROLL
   for (int i = 0; i < 32; i++)
     {
       float c = __shfl_sync (0xFFFFFFFFu, h1, i);
@@ -130,11 +148,13 @@ qnet_forward (const Static &st, const float *w, const prb_step_rec *r, int lane,
   h0 = elu_ (a0); h1 = elu_ (a1);
   /* Dense(k): lane j < k owns q_j */
   float q = lane < k ? b3[lane] : 0.0f;
+#pragma unroll QNET_UNROLL
   for (int i = 0; i < 32; i++)
     {
       float c = __shfl_sync (0xFFFFFFFFu, h0, i);
       if (lane < k) q = fmaf (c, w3[(size_t) i * K + lane], q);
     }
+#pragma unroll QNET_UNROLL
   for (int i = 0; i < 32; i++)
     {
       float c = __shfl_sync (0xFFFFFFFFu, h1, i);
