@@ -362,10 +362,14 @@ PRB_HD float fadd_ (float a, float b)
 }
 
 /* Philox-4x32-10 (Salmon et al., SC'11) */
+#ifndef PRB_PHILOX_UNROLL
+#define PRB_PHILOX_UNROLL 10
+#endif
+constexpr int PHILOX_UNROLL = PRB_PHILOX_UNROLL;
 PRB_HD void
 philox4x32 (uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, uint32_t k0, uint32_t k1, uint32_t out[4])
 {
-#pragma unroll
+#pragma unroll PHILOX_UNROLL
   for (int r = 0; r < 10; r++)
     {
       uint64_t p0 = (uint64_t) 0xD2511F53u * c0;
