@@ -591,7 +591,7 @@ struct ParArgs
   unsigned long long *round_stats;   /* optional: [0] rounds, [1] events executed (diagnostics) */
 };
 
-template <int T, bool LOG, bool SMEM>
+template <int T, bool LOG, bool SMEM, int CDEG = 0, int CW = 0>
 #ifndef PRB_PAR_MINB
 #define PRB_PAR_MINB 4          /* 128-thread blocks per SM the register allocation must allow */
 #endif
@@ -623,7 +623,7 @@ k_run_par (const __grid_constant__ Static st, const __grid_constant__ PStatic ps
   PScal *sc = d.sc;
   PAcc acc;
   memset (&acc, 0, sizeof (acc));
-  PSim<LOG> sim (st, ps, d, acc, env);
+  PSim<LOG, CDEG, CW> sim (st, ps, d, acc, env);
   const int N = st.N;
   const int64_t stop = st.sim_time_ns;
   const int64_t until = a.until_ns;
@@ -1072,7 +1072,10 @@ launch_par_t (prb_env *env, const ParArgs &a)
       const int teams = threads / T;
       const int blocks = (st.E + teams - 1) / teams;
       size_t smem = (size_t) teams * ps.pblob_bytes;
+      /* the common shape (row length 3, 8 wire slots: Abilene-like degrees at 1 ms / 500 kbit/s) has its own build of
+       * the throughput kernel with both as immediates */
       auto k = k_run_par<T, LOG, true>;
+      if (T == 16 && !LOG && ps.DEG == 3 && ps.W == 8) k = k_run_par<T, LOG, true, (T == 16 && !LOG) ? 3 : 0, (T == 16 && !LOG) ? 8 : 0>;
       CUDA_TRY (cudaFuncSetAttribute (k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
       k<<<blocks, threads, smem, env->stream>>> (st, ps, a);
     }
