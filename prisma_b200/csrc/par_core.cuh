@@ -531,27 +531,18 @@ struct PSim
     return c;
   }
 
-  /* history of the pending firing of ping timer m: idx earlier firings, one ping interval apart */
-  PRB_HDN PCtx
+  /* History of the pending firing of ping timer m.  Every ping timer fires at the same instants (round n at
+   * (n + 1) * ping_interval, sim.cc:519-560) and, round after round, in overlay-index order: two firings with one
+   * timestamp belong to the same round and their order is the timers' creation order.  The firing is therefore a
+   * terminal entry of a history (one entry of the ping code whatever the round, then the root m), not n entries. */
+  PRB_HD PCtx
   ping_ctx (int m, int64_t ts) const
   {
     PCtx c;
-    uint32_t n = d.ping_index[m];
-    c.sched = n == 0 ? -1 : ts - st.ping_interval_ns;
+    c.sched = d.ping_index[m] == 0 ? -1 : ts - st.ping_interval_ns;
     c.code = (uint32_t) ps.dcode_ping;
     c.flow = -1;
-    uint32_t e[6] = { 0, 0, 0, 0, 0, 0 };
-    uint32_t left = n;
-    for (int i = 0; i < 6 && left > 0; i++)
-      {
-        uint32_t r = left < 127u ? left : 127u;
-        e[i] = (c.code << 7) | r;
-        left -= r;
-      }
-    POrd o;
-    o.a = ((uint64_t) e[0] << 48) | ((uint64_t) e[1] << 32) | ((uint64_t) e[2] << 16) | (uint64_t) e[3];
-    o.b = ((uint64_t) e[4] << 48) | ((uint64_t) e[5] << 32) | ((uint64_t) (left > 0 ? P_NONE16 : (uint32_t) m) << 16) | P_NONE16;
-    c.ord = o;
+    c.ord = ord_empty ((uint32_t) m, P_NONE16);
     return c;
   }
 
