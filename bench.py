@@ -11,8 +11,11 @@ One "step" advances every environment by --chunk simulated seconds (one k_advanc
 environments are independent, each rank owns 4096 of them, no collective in the step ("weak" scaling);
 torch.distributed is used for the barrier and the max-over-ranks / sum reductions of the report only.
 
-Timing: W untimed warm-up steps, then K steps each bracketed by CUDA events on the launch stream, L2
-flushed (256 MB memset) between steps outside the event pairs; max over ranks of the summed step times.
+Timing: one episode of the reference's length (60 simulated seconds); its last K steps are timed, each bracketed
+by CUDA events on the launch stream with the hand-over check inside the pair, everything before is untimed
+warm-up (>= W steps); L2 flushed (256 MB memset) between steps outside the event pairs; max over ranks of the
+summed step times.  The e2e leg runs a second, identical episode through the host-buffer calls and times the
+same K steps by wall clock.
 """
 import argparse
 import json
@@ -52,6 +55,9 @@ def config_dict(args, world):
             "envs_per_gpu": args.envs, "total_envs": args.envs * world, "load_factor": 0.9,
             "sim_seconds_per_step": args.chunk, "link_cap": 500000, "link_delay_ms": 1, "packet_size": 512,
             "max_out_buffer_size": 16260, "traffic": "Philox-4x32-10 Poisson per flow",
+            "episode_sim_s": max(args.episode, (args.warmup + args.steps) * args.chunk),
+            "timed_window_sim_s": [max(args.episode, (args.warmup + args.steps) * args.chunk) - args.steps * args.chunk,
+                                   max(args.episode, (args.warmup + args.steps) * args.chunk)],
             "l2": "flushed between steps (256 MB memset outside the event pairs)", "parallelism": "env-sharded x%d" % world}
 
 
@@ -226,6 +232,8 @@ def main():
     ap.add_argument("--impl", default="prisma_b200", choices=["prisma_b200", "reference"])
     ap.add_argument("--envs", type=int, default=4096, help="environments per GPU")
     ap.add_argument("--chunk", type=float, default=1.0, help="simulated seconds per step")
+    ap.add_argument("--episode", type=float, default=60.0,
+                    help="simulated seconds per episode (the reference's simTime default); the timed steps are its last K")
     ap.add_argument("--lanes", type=int, default=0, help="serial engine: lanes per environment (0 = library default)")
     ap.add_argument("--engine", default="auto", choices=["auto", "serial", "parallel"])
     ap.add_argument("--team", type=int, default=0, help="parallel engine: lanes per environment (0 = from the node count)")
@@ -263,8 +271,12 @@ def main():
     from prisma_b200.env import BatchedRoutingEnv, sp_table
 
     K, W = args.steps, args.warmup
-    total_steps = W + 2 * K
-    cfg = workload_cfg(args.envs, total_steps * args.chunk + 1.0)
+    # One episode of the reference's own length (simTime = 60 s, argument_parser.py:35-37) in steps of --chunk simulated
+    # seconds; the K timed steps are the LAST K of the episode (queues saturated, drops, lock-step links), everything
+    # before them is untimed warm-up (>= W steps).
+    ep_steps = max(int(round(args.episode / args.chunk)), W + K)
+    lead = ep_steps - K
+    cfg = workload_cfg(args.envs, ep_steps * args.chunk)
     arrays = cfg.load()
     table = sp_table(arrays)
     kdeg = max(len(x) for x in arrays.overlay_neighbors())
@@ -281,13 +293,15 @@ def main():
         return int(c["packet_hops"].sum()), int(c["env_steps"].sum()), int(c["events"].sum())
 
     t_sim = 0.0
-    for _ in range(W):
+    for _ in range(lead):
         t_sim += args.chunk
         env.run(until_s=t_sim)
     torch.cuda.synchronize()
     hops0, steps0, events0 = hops_now()
+    window = [t_sim, t_sim + K * args.chunk]
 
-    # ---- timed region: K steps, device-resident ----
+    # ---- timed region: K steps, device-resident.  The hand-over check (which makes the serial engine replay what the
+    # parallel engine could not finish) sits INSIDE the event pair: no work whose hops are counted is left out. ----
     sampler = ClockSampler(local_rank)
     if world > 1:
         dist.barrier()
@@ -300,6 +314,7 @@ def main():
         t_sim += args.chunk
         ev[i][0].record()
         env.run(until_s=t_sim)
+        env.handovers()
         ev[i][1].record()
     torch.cuda.synchronize()
     launches = env.launch_count - launches0
@@ -310,11 +325,23 @@ def main():
     elapsed = sum(step_ms) / 1000.0
     hops1, steps1, events1 = hops_now()
     d_hops, d_steps, d_events = hops1 - hops0, steps1 - steps0, events1 - events0
+    run_engine = env.engine
+    round_stats = env.round_stats() if run_engine == "parallel" else (1, 1)
+    handovers, replay_ms = env.handover_stats() if run_engine == "parallel" else (0, 0.0)
 
-    # ---- e2e: the public host-buffer calls, copies inside the timed region ----
+    # ---- e2e: a second episode through the public host-buffer calls; the same K steps of it are timed by wall clock,
+    # host->device and device->host copies inside the timed region ----
     tab_host = np.ascontiguousarray(table, dtype=np.int32)
     cnt = np.empty(args.envs, dtype=env.counters().dtype)
     import ctypes as C
+    env.reset()
+    t_sim = 0.0
+    for _ in range(lead):
+        t_sim += args.chunk
+        env.set_policy("table", tab_host)
+        env.run(until_s=t_sim)
+        lib.prb_counters_host(h, cnt.ctypes.data_as(C.c_void_p))
+    hops_lead = int(cnt["packet_hops"].sum())
     if world > 1:
         dist.barrier()
     torch.cuda.synchronize()
@@ -329,13 +356,11 @@ def main():
         lib.prb_counters_host(h, cnt.ctypes.data_as(C.c_void_p))   # D2H: per-env statistics (synchronises)
         e2e_wall += time.perf_counter() - t0
     hops2 = int(cnt["packet_hops"].sum())
-    e2e_hops = hops2 - hops1
+    e2e_hops = hops2 - hops_lead
+    assert hops2 == hops1, "the two episodes are the same seeded traffic: %d vs %d packet hops" % (hops2, hops1)
     h2d = int(tab_host.nbytes)
     d2h = int(cnt.nbytes)
-
-    run_engine = env.engine
-    round_stats = env.round_stats() if run_engine == "parallel" else (1, 1)
-    handovers = env.handovers() if run_engine == "parallel" else 0
+    e2e_handovers, e2e_replay_ms = env.handover_stats() if run_engine == "parallel" else (0, 0.0)
 
     # ---- Gym mode with the dqn_buffer agents on the device (supplementary; single GPU runs only) ----
     gym = None
@@ -393,7 +418,10 @@ def main():
         if run_engine == "parallel":
             rounds, executed = round_stats
             line["engine"] = {"name": "node-parallel (k_run_par)", "events_per_round": executed / max(rounds, 1),
-                              "envs_replayed_by_the_serial_engine": handovers}
+                              "envs_replayed_by_the_serial_engine": handovers,
+                              "serial_replay_ms_in_episode": replay_ms,
+                              "e2e_envs_replayed_by_the_serial_engine": e2e_handovers,
+                              "e2e_serial_replay_ms_in_episode": e2e_replay_ms}
         else:
             line["engine"] = {"name": "event-serial (k_advance)"}
         if gym:

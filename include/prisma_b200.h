@@ -180,6 +180,11 @@ int prb_set_engine (prb_env *env, int mode, int team);
  * They are replayed from the reset state in global (timestamp, uid) order and kept up to date before every
  * read-out, so results stay exact; with an ordered log or a per-node action trace PRB_ERR_TIE is reported instead. */
 int prb_handovers (prb_env *env);
+/* The same count, and the device time (ms, CUDA events on the environment's stream) the serial engine has spent replaying
+ * those environments in this episode.  A table agent may be replaced between prb_run calls (prb_set_policy): the replay
+ * runs every stretch of simulated time with the table the parallel launches used for it.
+ * Replaces nothing in the reference (its single event list needs no such repair); diagnostics for bench.py. */
+int prb_handover_stats (prb_env *env, int64_t *envs, double *replay_ms);
 int prb_engine (prb_env *env);
 int prb_round_stats (prb_env *env, int64_t *rounds, int64_t *executed);
 int prb_num_links (prb_env *env);        /* L (switch<->switch, directed) */
@@ -203,7 +208,8 @@ int prb_enable_log (prb_env *env, int64_t event_capacity, int64_t step_capacity)
 int prb_read_events (prb_env *env, int32_t e, prb_event *out, int64_t capacity, int64_t *n);
 int prb_read_steps (prb_env *env, int32_t e, prb_step_rec *out, int64_t capacity, int64_t *n);
 
-/* fused-agent mode: advance every env until simulated time until_ns (or simTime) */
+/* fused-agent mode: advance every env until simulated time until_ns (or simTime); a call whose until_ns lies at or
+ * before the time already reached does nothing (both engines) */
 int prb_run (prb_env *env, int64_t until_ns);
 /* Gym mode: apply actions_dev[e] (int32, device; may be NULL on the first call) to the pending step of
  * every env that asked for one, then advance every env to its next valid Notify(); out_dev[e] (device,

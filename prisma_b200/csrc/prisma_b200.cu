@@ -942,6 +942,14 @@ struct prb_env
   uint8_t *d_tied_flags = nullptr;
   int64_t par_until_arg = 0;       /* until_ns of the last parallel launch */
   int64_t tied_until = 0;          /* until_ns the handed-over environments have been advanced to */
+  /* Table agents installed during this episode, by the simulated time from which the parallel launches used them:
+   * a replay by the serial engine walks the same segments (prb_set_policy between prb_run calls is legal). */
+  struct PolSeg { int64_t from_ns; std::vector<int32_t> table; };
+  std::vector<PolSeg> pol_segs;
+  std::vector<int32_t> pol_host;   /* host copy of the table policy in force */
+  int32_t *d_pol_replay = nullptr;
+  double replay_ms = 0.0;          /* device time of the serial replays of this episode */
+  cudaEvent_t rp_ev0 = nullptr, rp_ev1 = nullptr;
   /* dqn_buffer agents */
   float *d_qw = nullptr;
   uint64_t q_step = 0;
@@ -1110,6 +1118,17 @@ run_parallel (prb_env *env, int64_t until_ns)
   if (rc != PRB_OK) return rc;
   const int64_t stop = env->dst.sim_time_ns;
   int64_t target = std::min (until_ns, stop);
+  /* nothing lies before the frontier: times inside a launch are unsigned offsets from it and the frontier never
+   * moves backwards (the serial engine treats such a call as a no-op too) */
+  if (env->engine_active == PRB_ENGINE_PARALLEL && target <= env->par_front_ns) return PRB_OK;
+  if (env->dst.policy == PRB_POLICY_TABLE && (env->pol_segs.empty () || env->pol_segs.back ().table != env->pol_host))
+    {
+      prb_env::PolSeg s;
+      s.from_ns = env->engine_active == PRB_ENGINE_PARALLEL ? env->par_front_ns : 0;
+      s.table = env->pol_host;
+      if (!env->pol_segs.empty () && env->pol_segs.back ().from_ns == s.from_ns) env->pol_segs.pop_back ();
+      env->pol_segs.push_back (std::move (s));
+    }
   ParArgs a;
   a.pblobs = env->d_pblobs; a.rings = env->d_rings; a.ev_logs = env->d_ev; a.round_stats = env->d_round_stats;
   do
@@ -1198,7 +1217,8 @@ prb_destroy (prb_env *env)
   cudaFree (env->d_flow_first); cudaFree (env->d_counters); cudaFree (env->d_out); cudaFree (env->d_actions);
   cudaFree (env->d_scratch);
   cudaFree (env->d_ptables); cudaFree (env->d_pblob0); cudaFree (env->d_pblobs); cudaFree (env->d_rings);
-  cudaFree (env->d_tr_prev); cudaFree (env->d_round_stats); cudaFree (env->d_qw); cudaFree (env->d_tied_list); cudaFree (env->d_tied_flags);
+  cudaFree (env->d_tr_prev); cudaFree (env->d_round_stats); cudaFree (env->d_qw); cudaFree (env->d_tied_list); cudaFree (env->d_tied_flags); cudaFree (env->d_pol_replay);
+  if (env->rp_ev0) { cudaEventDestroy (env->rp_ev0); cudaEventDestroy (env->rp_ev1); }
   cudaFree (env->rp.rows); cudaFree (env->rp.cursor); cudaFree (env->rp.pending); cudaFree (env->rp.tmin);
   cudaFree (env->rp.row_gstep); cudaFree (env->rp.latest); cudaFree (env->rp.psum);
   delete env;
@@ -1296,7 +1316,54 @@ prb_reset (prb_env *env)
   env->tied.clear ();
   std::fill (env->tied_flag.begin (), env->tied_flag.end (), 0);
   env->tied_until = 0;
+  env->pol_segs.clear ();
+  env->replay_ms = 0.0;
   if (env->d_round_stats) CUDA_TRY (cudaMemsetAsync (env->d_round_stats + 2, 0, 8, env->stream));
+  return PRB_OK;
+}
+
+/* The serial engine advances the first n environments of d_tied_list from `from_ns` to `to_ns`, stretch by stretch
+ * with the table agent the parallel launches ran that stretch of simulated time with (pol_segs); the device time of
+ * these launches is accumulated in replay_ms (prb_handover_stats). */
+static int
+replay_span (prb_env *env, int32_t n, int64_t from_ns, int64_t to_ns)
+{
+  if (!env->rp_ev0)
+    {
+      CUDA_TRY (cudaEventCreate (&env->rp_ev0));
+      CUDA_TRY (cudaEventCreate (&env->rp_ev1));
+    }
+  CUDA_TRY (cudaEventRecord (env->rp_ev0, env->stream));
+  const size_t nseg = env->pol_segs.size ();
+  const int32_t *pol_saved = env->dst.pol_data;
+  for (size_t i = 0; i < std::max<size_t> (nseg, 1); i++)
+    {
+      int64_t seg_to = i + 1 < nseg ? std::min (env->pol_segs[i + 1].from_ns, to_ns) : to_ns;
+      if (seg_to <= from_ns) continue;
+      LaunchArgs a;
+      a.blobs = env->d_blobs; a.pools = env->d_pools; a.ev_logs = nullptr; a.st_logs = nullptr;
+      a.actions = nullptr; a.out = nullptr; a.until_ns = seg_to;
+      a.qw = nullptr; a.steps = 1; a.eps = 0.0f; a.seed = 0; a.step0 = 0; a.replay = ReplayArgs ();
+      a.env_list = env->d_tied_list; a.n_list = n;
+      if (nseg > 1)
+        {
+          const std::vector<int32_t> &t = env->pol_segs[i].table;
+          if (!env->d_pol_replay) CUDA_TRY (cudaMalloc (&env->d_pol_replay, sizeof (int32_t) * t.size ()));
+          CUDA_TRY (cudaMemcpyAsync (env->d_pol_replay, t.data (), sizeof (int32_t) * t.size (), cudaMemcpyHostToDevice, env->stream));
+          env->dst.pol_data = env->d_pol_replay;
+        }
+      env->dst.mode = MODE_RUN;
+      int rc = launch_advance (env, a);
+      env->dst.pol_data = pol_saved;
+      if (rc != PRB_OK) return rc;
+      if (nseg > 1) CUDA_TRY (cudaStreamSynchronize (env->stream));    /* d_pol_replay is reused by the next stretch */
+      if (seg_to >= to_ns) break;
+    }
+  CUDA_TRY (cudaEventRecord (env->rp_ev1, env->stream));
+  CUDA_TRY (cudaEventSynchronize (env->rp_ev1));
+  float ms = 0.0f;
+  CUDA_TRY (cudaEventElapsedTime (&ms, env->rp_ev0, env->rp_ev1));
+  env->replay_ms += ms;
   return PRB_OK;
 }
 
@@ -1339,15 +1406,8 @@ resolve_ties (prb_env *env)
       if (!fresh.empty () && env->tied_until > 0)
         {
           CUDA_TRY (cudaMemcpyAsync (env->d_tied_list, fresh.data (), sizeof (int32_t) * fresh.size (), cudaMemcpyHostToDevice, env->stream));
-          LaunchArgs a;
-          a.blobs = env->d_blobs; a.pools = env->d_pools; a.ev_logs = nullptr; a.st_logs = nullptr;
-          a.actions = nullptr; a.out = nullptr; a.until_ns = env->tied_until;
-          a.qw = nullptr; a.steps = 1; a.eps = 0.0f; a.seed = 0; a.step0 = 0; a.replay = ReplayArgs ();
-          a.env_list = env->d_tied_list; a.n_list = (int32_t) fresh.size ();
-          st.mode = MODE_RUN;
-          int rc = launch_advance (env, a);
+          int rc = replay_span (env, (int32_t) fresh.size (), 0, env->tied_until);
           if (rc != PRB_OK) return rc;
-          CUDA_TRY (cudaStreamSynchronize (env->stream));
         }
       env->tied.insert (env->tied.end (), fresh.begin (), fresh.end ());
       CUDA_TRY (cudaMemcpyAsync (env->d_tied_list, env->tied.data (), sizeof (int32_t) * env->tied.size (), cudaMemcpyHostToDevice, env->stream));
@@ -1355,13 +1415,7 @@ resolve_ties (prb_env *env)
     }
   if (env->tied_until != env->par_until_arg)
     {
-      LaunchArgs a;
-      a.blobs = env->d_blobs; a.pools = env->d_pools; a.ev_logs = nullptr; a.st_logs = nullptr;
-      a.actions = nullptr; a.out = nullptr; a.until_ns = env->par_until_arg;
-      a.qw = nullptr; a.steps = 1; a.eps = 0.0f; a.seed = 0; a.step0 = 0; a.replay = ReplayArgs ();
-      a.env_list = env->d_tied_list; a.n_list = (int32_t) env->tied.size ();
-      st.mode = MODE_RUN;
-      int rc = launch_advance (env, a);
+      int rc = replay_span (env, (int32_t) env->tied.size (), env->tied_until, env->par_until_arg);
       if (rc != PRB_OK) return rc;
       env->tied_until = env->par_until_arg;
     }
@@ -1405,6 +1459,17 @@ prb_handovers (prb_env *env)
   if (!env) return PRB_EINVAL;
   int rc = resolve_ties (env);
   return rc != PRB_OK ? rc : (int) env->tied.size ();
+}
+
+int
+prb_handover_stats (prb_env *env, int64_t *envs, double *replay_ms)
+{
+  if (!env) return fail (PRB_EINVAL, "null handle");
+  int rc = resolve_ties (env);
+  if (rc != PRB_OK) return rc;
+  if (envs) *envs = (int64_t) env->tied.size ();
+  if (replay_ms) *replay_ms = env->replay_ms;
+  return PRB_OK;
 }
 
 int prb_num_links (prb_env *env) { return env ? env->dst.L : PRB_EINVAL; }
@@ -1499,6 +1564,10 @@ prb_set_policy (prb_env *env, int kind, const int32_t *data, int64_t n, uint64_t
         }
       CUDA_TRY (cudaMemcpyAsync (env->d_pol, data, sizeof (int32_t) * n, cudaMemcpyHostToDevice, env->stream));
     }
+  if (kind == PRB_POLICY_TABLE)
+    env->pol_host.assign (data, data + n);
+  else
+    env->pol_host.clear ();
   st.policy = kind;
   st.pol_data = env->d_pol;
   st.pol_n = data ? n : 0;

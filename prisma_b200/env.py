@@ -178,6 +178,12 @@ class BatchedRoutingEnv:
             _abi.check(n)
         return int(n)
 
+    def handover_stats(self):
+        """(environments handed over, device milliseconds the serial engine spent replaying them) in this episode."""
+        n, ms = C.c_int64(), C.c_double()
+        _abi.check(self.lib.prb_handover_stats(self.h, C.byref(n), C.byref(ms)))
+        return int(n.value), float(ms.value)
+
     # ---- stepping ----
     def run(self, until_s: Optional[float] = None, until_ns: Optional[int] = None):
         if until_ns is None:

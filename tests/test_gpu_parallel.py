@@ -253,3 +253,63 @@ def test_bench_size_batch_engines_agree_and_conserve_packets():
     # env 4095 against the restatement
     osim = common.oracle_run(cfg, arrays, oracle, policy="table", table=table, env_id=4095)
     common.assert_counters_equal(osim.counters(), b[4095])
+
+
+def test_run_to_an_earlier_time_is_a_noop_on_both_engines():
+    """prb_run(until) with until at or before the time already reached does nothing (times inside a parallel launch are
+    unsigned offsets from the frontier, which never moves backwards): run(1.0); run(0.5); run(2.0) equals the
+    restatement at 2.0 on both engines."""
+    cfg = common.env_config("abilene", num_envs=8, simTime=3.0, load_factor=1.0, pingAsObs=0, activateUnderlayTraffic=1)
+    arrays = cfg.load()
+    table = common.sp_table(arrays)
+    osim = common.oracle_run(cfg, arrays, oracle, policy="table", table=table, env_id=5, until_ns=2_000_000_000)
+    for mode in ("serial", "parallel"):
+        env = make_env(cfg, arrays=arrays)
+        env.set_engine(mode)
+        env.set_policy("table", table)
+        env.run(until_s=1.0)
+        mid = env.counters()
+        env.run(until_s=0.5)
+        again = env.counters()
+        for k in common.COUNTER_INTS:
+            assert np.array_equal(mid[k], again[k]), (mode, k)
+        env.run(until_s=2.0)
+        cs = env.counters()
+        env.check_errors(cs)
+        assert env.engine == mode
+        common.assert_counters_equal(osim.counters(), cs[5])
+        assert np.array_equal(osim.queue_bytes(), env.queue_bytes(5))
+        env.close()
+
+
+def test_handover_replays_every_stretch_with_the_table_it_ran_with():
+    """prb_set_policy between prb_run calls of one episode (a periodically refreshed dq_routing table): an environment
+    handed over AFTER the change is replayed by the serial engine with the old table for the old stretch and the new one
+    from then on (GEANT load 1.5, environment 1558 hands over at 0.65 s; the table changes at 0.4 s and at 0.8 s)."""
+    cfg = common.env_config("geant", num_envs=1600, simTime=1.2, pingAsObs=0, activateUnderlayTraffic=1, load_factor=1.5)
+    arrays = cfg.load()
+    t0 = np.asarray(common.sp_table(arrays), dtype=np.int32)
+    deg = np.array([len(x) for x in arrays.overlay_neighbors()], dtype=np.int32)
+    t1 = (t0 + 1) % deg[:, None]          # every node deflects to its next neighbour: legal, and very different
+    t2 = t0.copy()
+    t2[::2] = t1[::2]
+    res = {}
+    for mode in ("serial", "parallel"):
+        env = make_env(cfg, arrays=arrays)
+        env.set_engine(mode)
+        out = []
+        for until, tab in ((0.4, t0), (0.8, t1), (1.2, t2)):
+            env.set_policy("table", tab)
+            env.run(until_s=until)
+            cs = env.counters()
+            env.check_errors(cs)
+            out.append((cs, env.queue_bytes(1558)))
+        if mode == "parallel":
+            n, ms = env.handover_stats()
+            assert n >= 1 and n == env.handovers() and ms > 0.0
+        res[mode] = out
+        env.close()
+    for (a, qa), (b, qb) in zip(res["serial"], res["parallel"]):
+        for k in common.COUNTER_INTS:
+            assert np.array_equal(a[k], b[k]), k
+        assert np.array_equal(qa, qb)
