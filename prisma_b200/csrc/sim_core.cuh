@@ -1444,7 +1444,10 @@ step_or_stop (const Static &st, Sim<LOG, GYM> &sim, int slot, int64_t until_ns, 
     }
   if (ts >= until_ns && until_ns < stop)
     {
-      sc->front_ts = until_ns; sc->front_seq = 0;
+      if (until_ns > sc->front_ts)       /* the frontier never moves backwards (prb_run to an earlier time: a no-op) */
+        {
+          sc->front_ts = until_ns; sc->front_seq = 0;
+        }
       return false;
     }
   status = sim.handle (slot, ts, seq, 0);
