@@ -269,6 +269,19 @@ int prb_replay_sample (prb_env *env, int32_t node, int32_t batch, uint64_t seed,
 int prb_counters_host (prb_env *env, prb_counters *out /* [E] */);
 int prb_counters_dev (prb_env *env, prb_counters *out_dev /* [E] device */);
 int prb_queue_bytes (prb_env *env, int32_t e, int32_t *out /* [L] */);
+/* prb_queue_bytes for callers that must not allocate (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ * Same result as prb_queue_bytes; the device-side staging buffer is a file-scope static __device__ array of
+ * PRB_NOALLOC_MAX_LINKS int32 (16 KB, held by every GPU that loads the library until exit) instead of a buffer owned
+ * by the handle, and the call performs no cudaMalloc / cudaFree / allocating library call.  out: host, at least L
+ * entries (out_capacity = its length).  Configurations with more than PRB_NOALLOC_MAX_LINKS switch links are
+ * rejected with PRB_EINVAL.  Environments handed over to the serial engine are brought up to date by prb_handovers
+ * (which may allocate); while some are pending this call returns PRB_ESTATE.  Every call on a device shares the one
+ * array, which keeps the previous call's contents (this call clears the part it uses first): calls that overlap on the
+ * GPU (different streams or handles) race; serialise them. */
+#define PRB_NOALLOC_MAX_LINKS 4096
+#define PRB_NOALLOC_MAX_DEVICES 64
+int prb_queue_bytes_noalloc (prb_env *env, int32_t e, int32_t *out /* [>= L] */, int32_t out_capacity);
 int prb_sync (prb_env *env);
 /* number of kernel launches issued by this handle so far */
 int64_t prb_launch_count (prb_env *env);

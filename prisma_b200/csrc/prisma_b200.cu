@@ -1188,6 +1188,23 @@ launch_advance (prb_env *env, const LaunchArgs &a)
 #undef PRB_DISPATCH
 }
 
+/* ---- prb_queue_bytes without any allocation: the scratch is a file-scope device array ----
+ * g_noalloc_scratch is a HOST-side stand-in in host code, not a device address: its device address is looked up once
+ * per device (noalloc_setup, from prb_create with that device current) and that pointer is what the kernels get. */
+static __device__ __align__ (256) int32_t g_noalloc_scratch[PRB_NOALLOC_MAX_LINKS];
+static int32_t *g_noalloc_ptr[PRB_NOALLOC_MAX_DEVICES];
+
+static int
+noalloc_setup (int device)
+{
+  if (device < 0 || device >= PRB_NOALLOC_MAX_DEVICES) return PRB_OK;     /* such a device gets PRB_ESTATE from the entry point */
+  if (g_noalloc_ptr[device]) return PRB_OK;
+  int32_t *p = nullptr;
+  CUDA_TRY (cudaGetSymbolAddress ((void **) &p, g_noalloc_scratch));
+  g_noalloc_ptr[device] = p;
+  return PRB_OK;
+}
+
 extern "C" {
 
 const char *prb_last_error (void) { return g_err.c_str (); }
@@ -1253,6 +1270,7 @@ prb_create (const prb_config *cfg, int device, void *cuda_stream, prb_env **out)
   int rc = PRB_OK;
   auto guard = [&] (int r) { if (r != PRB_OK) { prb_destroy (env); } return r; };
   if (cudaSetDevice (device) != cudaSuccess) return guard (fail (PRB_ECUDA, "cudaSetDevice failed"));
+  if ((rc = noalloc_setup (device)) != PRB_OK) return guard (rc);       /* prb_queue_bytes_noalloc: address of the static scratch */
   cudaDeviceGetAttribute (&env->max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, device);
   cudaDeviceGetAttribute (&env->smem_per_sm, cudaDevAttrMaxSharedMemoryPerMultiprocessor, device);
   cudaDeviceGetAttribute (&env->num_sms, cudaDevAttrMultiProcessorCount, device);
@@ -2018,6 +2036,41 @@ prb_queue_bytes (prb_env *env, int32_t e, int32_t *out)
     k_queue_bytes<<<(st.L + 127) / 128, 128, 0, env->stream>>> (st, env->d_blobs, e, (int32_t *) env->d_scratch);
   CUDA_TRY (cudaGetLastError ());
   CUDA_TRY (cudaMemcpyAsync (out, env->d_scratch, sizeof (int32_t) * st.L, cudaMemcpyDeviceToHost, env->stream));
+  CUDA_TRY (cudaStreamSynchronize (env->stream));
+  return PRB_OK;
+}
+
+int
+prb_queue_bytes_noalloc (prb_env *env, int32_t e, int32_t *out, int32_t out_capacity)
+{
+  if (!env || !out) return fail (PRB_EINVAL, "null argument");
+  CUDA_TRY (cudaSetDevice (env->device));
+  const Static &st = env->dst;
+  if (e < 0 || e >= st.E) return fail (PRB_EINVAL, "env index out of range");
+  if (st.L > PRB_NOALLOC_MAX_LINKS)
+    return fail (PRB_EINVAL, "prb_queue_bytes_noalloc: " + std::to_string (st.L) + " links exceed the static scratch of "
+                                 + std::to_string (PRB_NOALLOC_MAX_LINKS) + " (use prb_queue_bytes)");
+  if (out_capacity < st.L) return fail (PRB_EINVAL, "prb_queue_bytes_noalloc: the output holds fewer than L entries");
+  int32_t *scratch = env->device < PRB_NOALLOC_MAX_DEVICES ? g_noalloc_ptr[env->device] : nullptr;
+  if (!scratch) return fail (PRB_ESTATE, "prb_queue_bytes_noalloc: no static scratch on this device (device index beyond the table)");
+  bool tied_env = false;
+  if (env->engine_active == PRB_ENGINE_PARALLEL && env->d_pblobs && !(env->log_on || st.policy == PRB_POLICY_NODE_TRACE))
+    {
+      /* hand-overs are brought up to date by calls that may allocate (prb_handovers): this one only checks */
+      unsigned long long n = 0;
+      CUDA_TRY (cudaMemcpyAsync (&n, env->d_round_stats + 2, sizeof (n), cudaMemcpyDeviceToHost, env->stream));
+      CUDA_TRY (cudaStreamSynchronize (env->stream));
+      if ((size_t) n != env->tied.size () || (n > 0 && env->tied_until != env->par_until_arg))
+        return fail (PRB_ESTATE, "prb_queue_bytes_noalloc: environments handed over to the serial engine are pending; call prb_handovers first");
+      tied_env = e < (int) env->tied_flag.size () && env->tied_flag[(size_t) e];
+    }
+  CUDA_TRY (cudaMemsetAsync (scratch, 0, sizeof (int32_t) * (size_t) st.L, env->stream));   /* the array keeps the last call's contents */
+  if (env->engine_active == PRB_ENGINE_PARALLEL && !tied_env)
+    k_queue_bytes_par<<<(st.L + 127) / 128, 128, 0, env->stream>>> (st, env->dps, env->d_pblobs, e, scratch);
+  else
+    k_queue_bytes<<<(st.L + 127) / 128, 128, 0, env->stream>>> (st, env->d_blobs, e, scratch);
+  CUDA_TRY (cudaGetLastError ());
+  CUDA_TRY (cudaMemcpyAsync (out, scratch, sizeof (int32_t) * st.L, cudaMemcpyDeviceToHost, env->stream));
   CUDA_TRY (cudaStreamSynchronize (env->stream));
   return PRB_OK;
 }

@@ -331,6 +331,13 @@ class BatchedRoutingEnv:
         _abi.check(self.lib.prb_queue_bytes(self.h, int(e), _abi.ptr(out, C.c_int32)))
         return out
 
+    def queue_bytes_noalloc(self, e: int = 0) -> np.ndarray:
+        """queue_bytes through the allocation-free entry point (static device scratch; include/prisma_b200.h)."""
+        L = self.lib.prb_num_links(self.h)
+        out = np.zeros(L, dtype=np.int32)
+        _abi.check(self.lib.prb_queue_bytes_noalloc(self.h, int(e), _abi.ptr(out, C.c_int32), L))
+        return out
+
     def enable_log(self, event_capacity: int, step_capacity: int):
         _abi.check(self.lib.prb_enable_log(self.h, int(event_capacity), int(step_capacity)))
         self._ev_cap, self._st_cap = int(event_capacity), int(step_capacity)
