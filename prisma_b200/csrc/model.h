@@ -474,7 +474,7 @@ struct PModel
   PStatic ps;                      /* table pointers are HOST pointers into the vectors below */
   std::vector<int16_t> in_links, out_links;
   std::vector<int32_t> ring_off, flow_begin, pol_off;
-  std::vector<uint16_t> ring_mask, dcode_rcv, dcode_txc;
+  std::vector<uint16_t> ring_mask;
   std::vector<char> pblob0;
   bool supported = false;
   std::string why;                 /* why the configuration has to run on the serial engine */
@@ -557,12 +557,22 @@ build_pmodel (const prb_config &c, const HostModel &hm, PModel &pm)
   int64_t per = c.max_out_buffer_size / std::max<int> (hm.szc_bytes[SZC_DATA_FWD], 38) + 2 + ps.W;
   if (c.train) per *= 2;
   int32_t rc = std::min (std::max (pow2_ceil (per), 8), 4096);
+  /* Lineage retention (par_core.cuh, PRec): consumed records stay readable until the ring wraps, so the rings are
+   * longer than the live packets need — PRB_LINEAGE_RECORDS per switch link (default 256), an eighth of it per access
+   * link — as long as the rings of all environments stay within PRB_RING_BUDGET_MB (default 24576) of device memory. */
+  int32_t lin = 256;
+  if (const char *e = getenv ("PRB_LINEAGE_RECORDS")) lin = std::max (8, std::min (pow2_ceil (atoi (e)), 16384));
+  int64_t budget = 24576;
+  if (const char *e = getenv ("PRB_RING_BUDGET_MB")) budget = std::max<int64_t> (atoll (e), 1);
+  auto ring_bytes = [&] (int32_t sw, int32_t ac) { return (int64_t) sizeof (PRec) * ((int64_t) L * sw + (int64_t) (LA - L) * ac) * std::max<int64_t> (c.num_envs, 1); };
+  while (lin > rc && ring_bytes (std::max (rc, lin), std::max (8, lin / 8)) > budget * (1ll << 20)) lin /= 2;
+  const int32_t rc_sw = std::max (rc, lin), rc_ac = std::max (8, lin / 8);
   pm.ring_off.assign (LA, 0);
   pm.ring_mask.assign (LA, 0);
   int32_t off = 0;
   for (int l = 0; l < LA; l++)
     {
-      int32_t cap = l < L ? rc : 8;
+      int32_t cap = l < L ? rc_sw : rc_ac;
       pm.ring_off[l] = off;
       pm.ring_mask[l] = (uint16_t) (cap - 1);
       off += cap;
@@ -578,42 +588,11 @@ build_pmodel (const prb_config &c, const HostModel &hm, PModel &pm)
         return false;
       }
   pm.pol_off.assign (M + 1, 0);
-  /* distance codes: every value ts(event) - ts(parent) that a Receive, a TransmitComplete or a ping timer
-   * can have, ranked largest first (par_core.cuh, POrd) */
-  {
-    std::vector<int64_t> dist;
-    const int nrc = st.n_rc;
-    for (int r = 0; r < nrc; r++)
-      for (int k = 0; k < st.n_szc; k++)
-        {
-          dist.push_back (hm.tx_ns[(size_t) r * MAX_SZC + k]);
-          dist.push_back (hm.tx_ns[(size_t) r * MAX_SZC + k] + (r == 0 ? st.link_delay_ns : 0));
-        }
-    dist.push_back (st.ping_interval_ns);
-    std::sort (dist.begin (), dist.end (), [] (int64_t a, int64_t b) { return a > b; });
-    dist.erase (std::unique (dist.begin (), dist.end ()), dist.end ());
-    if (dist.size () >= P_CODE_FLOW)
-      {
-        pm.why = "too many distinct transmission times";
-        return false;
-      }
-    auto code = [&] (int64_t v) { return (uint16_t) (std::find (dist.begin (), dist.end (), v) - dist.begin ()); };
-    pm.dcode_rcv.assign ((size_t) nrc * MAX_SZC, 0);
-    pm.dcode_txc.assign ((size_t) nrc * MAX_SZC, 0);
-    for (int r = 0; r < nrc; r++)
-      for (int k = 0; k < st.n_szc; k++)
-        {
-          pm.dcode_txc[(size_t) r * MAX_SZC + k] = code (hm.tx_ns[(size_t) r * MAX_SZC + k]);
-          pm.dcode_rcv[(size_t) r * MAX_SZC + k] = code (hm.tx_ns[(size_t) r * MAX_SZC + k] + (r == 0 ? st.link_delay_ns : 0));
-        }
-    ps.dcode_ping = code (st.ping_interval_ns);
-  }
   /* state layout */
   int32_t o = 0;
   ps.off_scal = o; o += align_up ((int32_t) sizeof (PScal), 8);
   ps.off_t_ping = o; o += 8 * M;
   ps.off_f_ts = o; o += 8 * std::max (F, 1);
-  ps.off_fly_ord = o; o += (int32_t) sizeof (POrd) * LA;
   ps.off_t_next = o; o += 4 * N;
   ps.off_fmin_ts = o; o += 4 * N;
   ps.off_busy = o; o += 4 * LA;
@@ -646,7 +625,6 @@ build_pmodel (const prb_config &c, const HostModel &hm, PModel &pm)
   ps.in_links = pm.in_links.data (); ps.out_links = pm.out_links.data ();
   ps.ring_off = pm.ring_off.data (); ps.ring_mask = pm.ring_mask.data ();
   ps.flow_begin = pm.flow_begin.data (); ps.tr_prev = nullptr; ps.pol_off = pm.pol_off.data ();
-  ps.dcode_rcv = pm.dcode_rcv.data (); ps.dcode_txc = pm.dcode_txc.data ();
   pm.supported = true;
   return true;
 }

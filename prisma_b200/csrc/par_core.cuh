@@ -64,23 +64,22 @@ constexpr int P_SR = 8;                  /* statistics-ring records per node */
 constexpr int64_t P_FAR = INT64_MAX;
 constexpr uint32_t P_FAR32 = 0xFFFFFFFFu;   /* no event: times inside a run are 32-bit offsets from PScal::base */
 constexpr uint32_t P_NONE16 = 0xFFFFu;
-constexpr uint32_t P_CODE_FLOW = 510;      /* scheduled by a source: the distance to its parent is arbitrary */
 
-/* Scheduling history of an event, for the order of simultaneous events (tie_before).
- * An event's scheduler uid is the order of its Schedule call, i.e. (timestamp of the parent event, uid of
- * the parent, position inside the parent's handler), recursively.  The distance ts(e) - ts(parent(e)) of
- * almost every event is one of a few values (a transmission time, plus the link delay for a Receive, or
- * the ping interval); the host ranks those values (largest first) and an event carries the ranks of its
- * ancestors, most recent first, run-length coded: six 16-bit entries (code << 7 | run), then the creation
- * rank of the setup event the chain started from (0xFFFF once history has been shed) and the position of the
- * chain among the transmissions of one ping round.  Comparing two histories entry by entry is comparing
- * the ancestors' timestamps generation by generation, which is how ns-3's uids compare. */
-struct POrd
-{
-  uint64_t a;        /* e0 (bits 48..63) e1 e2 e3 */
-  uint64_t b;        /* e4 e5 root branch */
-};
-
+/* Lineage of an event, for the order of simultaneous events (tie_before).
+ * An event's scheduler uid is the order of its Schedule call, i.e. (timestamp of the parent event, uid of the parent,
+ * position inside the parent's handler), recursively (scheduler.h:153-169).  Every Receive and every TransmitComplete
+ * is scheduled by a transmission start (point-to-point-net-device.cc:272-302), and a transmission start happens inside
+ * one event X: the Receive, injection or ping timer that called Send on an idle device, or the TransmitComplete that
+ * took the next packet from the queue.  The ring record of a packet therefore doubles as the node of a lineage tree:
+ * it keeps the time s of its transmission start and a reference to X (kind, link / flow / timer, ring index or
+ * ordinal, position of the Send inside X's handler).  Two simultaneous events are ordered by walking both lineages
+ * upwards, parent by parent, until the parents' timestamps differ (the earlier parent ran first) or the parents are
+ * one and the same event (the Schedule call that came first inside its handler wins); source and ping-timer events
+ * recompute their parents (previous injection: Philox / trace; previous firing: one ping interval earlier; every ping
+ * timer fires at the same instants in overlay-index order, sim.cc:519-560).  Records stay readable in their ring
+ * after they have been consumed, until the ring wraps (PStatic: rings are sized for the live packets plus a lineage
+ * retention); a walk that meets an overwritten record cannot decide and sets PRB_ERR_TIE.  Nothing of this is touched
+ * by an event that has no simultaneous rival: the hot path only stores (s, X) with the record it writes anyway. */
 enum { PK_NONE = 0, PK_RCV = 1, PK_TXC = 2, PK_FLOW = 3, PK_PING = 4 };
 enum { PS_OVERLAY_ARRIVED = 0, PS_UNDERLAY_ARRIVED = 1, PS_OVERLAY_DROP = 2, PS_UNDERLAY_DROP = 3 };
 
@@ -90,8 +89,29 @@ struct PRec
   uint64_t w0;       /* same packing as Pkt::w0 */
   uint32_t uid;
   uint32_t aux;
-  POrd ord;          /* history of the transmission that carries the packet (tie_before) */
+  int64_t s;         /* absolute time of the transmission start that carries the packet (written when it starts) */
+  uint64_t xw;       /* the event that started it: kind 3 | position 5 | idx 16 | seq 24 | own ring index 16 */
 };
+
+/* reference to an event: RCV / TXC (idx = link, seq = ring index of the record), FLOW (idx = flow, seq = f_pos at the
+ * injection), PING (idx = overlay index, seq = round); t = its timestamp */
+struct PEv
+{
+  int32_t kind, idx;
+  uint32_t seq;
+  int64_t t;
+};
+
+constexpr uint64_t P_XW_QUEUED = ~0ull;      /* a record that waits in the queue: no transmission start yet */
+constexpr int P_POS_LAST = 255;              /* the Schedule call a handler makes after all its Sends */
+constexpr int P_WALK_MAX = 8192;             /* generations a lineage walk may climb */
+
+PRB_HD uint64_t
+xw_pack (int kind, uint32_t pos, int idx, uint32_t seq, uint32_t self)
+{
+  return ((uint64_t) (uint32_t) kind << 61) | ((uint64_t) (pos & 31u) << 56) | ((uint64_t) ((uint32_t) idx & 0xFFFFu) << 40)
+         | ((uint64_t) (seq & 0xFFFFFFu) << 16) | (uint64_t) (self & 0xFFFFu);
+}
 
 struct PStat
 {
@@ -115,11 +135,8 @@ struct PStatic
   const int32_t *flow_begin; /* [N+1] flows with source x: [flow_begin[x], flow_begin[x+1]) */
   const int32_t *tr_prev;    /* trace mode: previous injection of the same flow, -1 for the first */
   const int32_t *pol_off;    /* per-node action trace: [M+1] offsets into pol_data */
-  const uint16_t *dcode_rcv; /* [n_rc*MAX_SZC] rank of tx + delay of a Receive on a link of that rate class */
-  const uint16_t *dcode_txc; /* [n_rc*MAX_SZC] rank of tx */
-  int32_t dcode_ping, pad1;
   int32_t off_scal, off_t_next, off_t_ping, off_fmin_ts, off_f_ts, off_busy, off_w_ts, off_sring, off_q_bytes, off_f_pos,
-      off_ping_index, off_pol_pos, off_fmin_f, off_head, off_mid, off_tail, off_s_head, off_s_tail, off_fly_szc, off_fly_ord, off_cand;
+      off_ping_index, off_pol_pos, off_fmin_f, off_head, off_mid, off_tail, off_s_head, off_s_tail, off_fly_szc, off_cand;
   int32_t pblob_bytes;
 };
 
@@ -143,7 +160,6 @@ struct PDyn
   uint32_t *q_bytes, *f_pos, *ping_index, *pol_pos;
   int32_t *fmin_f, *cand;
   uint16_t *head, *mid, *tail;
-  POrd *fly_ord;
   uint8_t *s_head, *s_tail, *fly_szc;
   PRec *rings;
   prb_event *ev_log;
@@ -172,7 +188,6 @@ p_bind_state (const PStatic &ps, char *blob, PDyn &d)
   d.s_head = (uint8_t *) (blob + ps.off_s_head);
   d.s_tail = (uint8_t *) (blob + ps.off_s_tail);
   d.fly_szc = (uint8_t *) (blob + ps.off_fly_szc);
-  d.fly_ord = (POrd *) (blob + ps.off_fly_ord);
 }
 
 /* per-lane counters of one launch (registers on the device) */
@@ -205,84 +220,12 @@ rel32 (int64_t t, int64_t base)
   return dlt > 0xFFFFFFFEull ? P_FAR32 : (uint32_t) dlt;
 }
 
-/* ---- scheduling histories ---- */
-PRB_HD POrd
-ord_empty (uint32_t root, uint32_t branch)
-{
-  POrd o;
-  o.a = 0;
-  o.b = ((uint64_t) (root & 0xFFFFu) << 16) | (uint64_t) (branch & 0xFFFFu);
-  return o;
-}
-
-/* history of a child of an event with history o whose own distance code is `code` */
-PRB_HD POrd
-ord_push (POrd o, uint32_t code)
-{
-  uint32_t e0 = (uint32_t) (o.a >> 48);
-  if ((e0 >> 7) == code && (e0 & 127u) != 0 && (e0 & 127u) < 127u)
-    {
-      o.a += 1ull << 48;
-      return o;
-    }
-  uint32_t e3 = (uint32_t) (o.a & 0xFFFFu), e4 = (uint32_t) (o.b >> 48), e5 = (uint32_t) ((o.b >> 32) & 0xFFFFu);
-  uint64_t tail = o.b & 0xFFFFFFFFull;
-  if (e5 & 127u) tail |= 0xFFFF0000ull;          /* an entry falls off the end: the root is no longer known */
-  o.b = ((uint64_t) e3 << 48) | ((uint64_t) e4 << 32) | tail;
-  o.a = (o.a >> 16) | ((uint64_t) ((code << 7) | 1u) << 48);
-  return o;
-}
-
-PRB_HD uint32_t
-ord_entry (const POrd &o, int i)
-{
-  return i < 4 ? (uint32_t) ((o.a >> (48 - 16 * i)) & 0xFFFFu) : (uint32_t) ((o.b >> (48 - 16 * (i - 4))) & 0xFFFFu);
-}
-
-/* -1: x was scheduled first, +1: y, 0: the histories do not tell */
-PRB_HDN inline int
-ord_compare (const POrd &x, const POrd &y)
-{
-  int ix = 0, iy = 0;
-  uint32_t ex = ord_entry (x, 0), ey = ord_entry (y, 0);
-  uint32_t rx = ex & 127u, ry = ey & 127u;
-  for (;;)
-    {
-      if (rx == 0 || ry == 0)
-        {
-          if (rx != 0 || ry != 0) return 0;
-          /* both histories end here: at setup, unless entries have been shed */
-          uint32_t rootx = (uint32_t) ((x.b >> 16) & 0xFFFFu), rooty = (uint32_t) ((y.b >> 16) & 0xFFFFu);
-          if (rootx == P_NONE16 || rooty == P_NONE16) return 0;
-          if (rootx != rooty) return rootx < rooty ? -1 : 1;
-          uint32_t bx = (uint32_t) (x.b & 0xFFFFu), by = (uint32_t) (y.b & 0xFFFFu);
-          if (bx != by) return bx < by ? -1 : 1;
-          return 0;
-        }
-      uint32_t cx = ex >> 7, cy = ey >> 7;
-      if (cx == P_CODE_FLOW || cy == P_CODE_FLOW) return 0;
-      if (cx != cy) return cx < cy ? -1 : 1;    /* the larger distance (smaller code) was scheduled earlier */
-      uint32_t m = rx < ry ? rx : ry;
-      rx -= m; ry -= m;
-      /* past the sixth entry a history is complete exactly when its root is still known (nothing was shed) */
-      if (rx == 0)
-        {
-          ex = ++ix < 6 ? ord_entry (x, ix) : 0u; rx = ex & 127u;
-        }
-      if (ry == 0)
-        {
-          ey = ++iy < 6 ? ord_entry (y, iy) : 0u; ry = ey & 127u;
-        }
-    }
-}
-
-/* the running event as a parent: when it was scheduled, its history, and its own distance code */
+/* the running event as a parent: when it was scheduled, and which event it is */
 struct PCtx
 {
   int64_t sched;     /* P_SCHED_LAZY: an injection, whose scheduling time is recomputed only if somebody asks */
-  POrd ord;
-  uint32_t code;
-  int32_t flow;
+  int32_t kind, idx; /* PEv fields of the running event */
+  uint32_t seq;
 };
 constexpr int64_t P_SCHED_LAZY = INT64_MIN + 1;
 
@@ -320,7 +263,7 @@ struct PSim
   PRB_HD static void
   to_rec (const Pkt &p, PRec &r)
   {
-    r.w0 = p.w0; r.uid = p.uid; r.aux = p.aux; r.ord.a = 0; r.ord.b = 0;
+    r.w0 = p.w0; r.uid = p.uid; r.aux = p.aux; r.s = 0; r.xw = P_XW_QUEUED;
   }
 
   PRB_HD void
@@ -378,10 +321,10 @@ struct PSim
 
   /* One request of the running event to a device of its node: mode 0 = PointToPointNetDevice::Send +
    * Queue::DoEnqueue, mode 1 = the TransmitComplete of link l starts the packet at the head of its queue
-   * (already in the ring).  cur: the running event; branch: position among the transmissions of a ping
-   * round (0xFFFF: inherit).  There is ONE call site (execute), so one copy in the instruction stream. */
+   * (already in the ring).  cur: the running event; pos: position of this Send among the Sends of its handler
+   * (the tunnel index inside a ping round).  There is ONE call site (execute), so one copy in the instruction stream. */
   PRB_HD void
-  dev_send (int x, int l, uint32_t now, const Pkt &p, const PCtx &cur, uint32_t branch, int mode)
+  dev_send (int x, int l, uint32_t now, const Pkt &p, const PCtx &cur, uint32_t pos, int mode)
   {
     const int64_t now_abs = base + now;
     int node = st.link_from[l];
@@ -434,40 +377,39 @@ struct PSim
         qb -= size;
         d.q_bytes[l] = qb;
       }
-    /* PointToPointNetDevice::TransmitStart + PointToPointChannel::TransmitStart */
-    POrd o = ord_push (cur.ord, cur.code);
-    if (branch != P_NONE16) o.b = (o.b & ~0xFFFFull) | branch;
+    /* PointToPointNetDevice::TransmitStart + PointToPointChannel::TransmitStart; the record keeps who started it */
+    const uint64_t xw = xw_pack (cur.kind, pos, cur.idx, cur.seq, m);
     if (mode == 0)
       {
         PRec r;
         to_rec (p, r);
-        r.ord = o;
+        r.s = now_abs; r.xw = xw;
         *slot = r;
       }
     else
-      slot->ord = o;
+      {
+        slot->s = now_abs; slot->xw = xw;
+      }
     if (l < st.L) log_event (now_abs, PRB_EV_TXB, node, l, p, (int) qb);
     int szc = p_szc (p);
     uint32_t tx = (uint32_t) st.tx_ns[st.link_rc[l] * MAX_SZC + szc];
     uint32_t delay = l < st.L ? (uint32_t) st.link_delay_ns : 0u;
     d.busy[l] = now + tx + 1;
     d.fly_szc[l] = (uint8_t) szc;
-    d.fly_ord[l] = o;
     if ((uint16_t) (m - d.head[l]) >= (uint16_t) P_W) acc.errors |= PRB_ERR_POOL;
     d.w_ts[l * P_W + (m & (P_W - 1))] = now + tx + delay;
     d.mid[l] = (uint16_t) (m + 1);
     acc.tx_started++;
   }
 
+  /* the pending TransmitComplete of link l: scheduled by the transmission start of the record in front of mid */
   PRB_HD PCtx
   txc_ctx (int l, int64_t ts) const
   {
     PCtx c;
     int k = st.link_rc[l] * MAX_SZC + d.fly_szc[l];
     c.sched = ts - st.tx_ns[k];
-    c.ord = d.fly_ord[l];
-    c.code = ps.dcode_txc[k];
-    c.flow = -1;
+    c.kind = PK_TXC; c.idx = l; c.seq = (uint16_t) (d.mid[l] - 1);
     return c;
   }
 
@@ -478,8 +420,7 @@ struct PSim
   completes_later (int l, int64_t now, const PCtx &cur)
   {
     PCtx tc = txc_ctx (l, now);
-    int64_t cs = cur.sched == P_SCHED_LAZY ? flow_sched_time (cur.flow) : cur.sched;
-    int r = tc.sched != cs ? (tc.sched < cs ? -1 : 1) : ord_compare (tc.ord, cur.ord);
+    int r = lineage_cmp (ev_of (tc, now), ev_of (cur, now));
     if (r == 0) acc.errors |= PRB_ERR_TIE;
     return r >= 0;
   }
@@ -519,30 +460,24 @@ struct PSim
     set_p_szc (q, szc);
   }
 
+  /* the Receive of the record at ring index i of link l */
   PRB_HD PCtx
-  rcv_ctx (int l, int64_t ts, const PRec &r) const
+  rcv_ctx (int l, int64_t ts, const PRec &r, uint32_t i) const
   {
     PCtx c;
     int k = st.link_rc[l] * MAX_SZC + (int) ((r.w0 >> 7) & 15);
     c.sched = ts - st.tx_ns[k] - (l < st.L ? st.link_delay_ns : 0);
-    c.ord = r.ord;
-    c.code = ps.dcode_rcv[k];
-    c.flow = -1;
+    c.kind = PK_RCV; c.idx = l; c.seq = i & 0xFFFFu;
     return c;
   }
 
-  /* History of the pending firing of ping timer m.  Every ping timer fires at the same instants (round n at
-   * (n + 1) * ping_interval, sim.cc:519-560) and, round after round, in overlay-index order: two firings with one
-   * timestamp belong to the same round and their order is the timers' creation order.  The firing is therefore a
-   * terminal entry of a history (one entry of the ping code whatever the round, then the root m), not n entries. */
+  /* the pending firing of ping timer m (round ping_index[m]) */
   PRB_HD PCtx
   ping_ctx (int m, int64_t ts) const
   {
     PCtx c;
     c.sched = d.ping_index[m] == 0 ? -1 : ts - st.ping_interval_ns;
-    c.code = (uint32_t) ps.dcode_ping;
-    c.flow = -1;
-    c.ord = ord_empty ((uint32_t) m, P_NONE16);
+    c.kind = PK_PING; c.idx = m; c.seq = d.ping_index[m];
     return c;
   }
 
@@ -601,13 +536,98 @@ struct PSim
   flow_ctx (int f, int64_t prev) const
   {
     PCtx c;
-    bool first = st.inject_mode == PRB_INJECT_TRACE ? ps.tr_prev[(int32_t) d.f_pos[f]] < 0 : d.f_pos[f] <= 2u;
-    c.sched = first ? -1 : prev;
-    c.code = P_CODE_FLOW;
-    c.flow = f;
-    c.ord = ord_empty (first ? (uint32_t) (st.M + f) : P_NONE16, P_NONE16);
-    if (!first) c.ord.a = (uint64_t) ((P_CODE_FLOW << 7) | 1u) << 48;
+    c.sched = prev;
+    c.kind = PK_FLOW; c.idx = f; c.seq = d.f_pos[f];
     return c;
+  }
+
+  /* ---- lineage (see PRec) ---- */
+  PRB_HD static PEv
+  ev_of (const PCtx &c, int64_t t)
+  {
+    PEv e;
+    e.kind = c.kind; e.idx = c.idx; e.seq = c.seq; e.t = t;
+    return e;
+  }
+
+  /* The event that scheduled e.  Returns 1 and fills p (with its timestamp) and pos (the place of the Schedule call
+   * inside p's handler: Send number * 2, + 1 for the peer's Receive, which TransmitStart schedules after the
+   * TransmitComplete, point-to-point-net-device.cc:295-296; P_POS_LAST for what a source or a ping timer schedules after
+   * its Sends, poisson-application.cc:331,357); 2 when e was scheduled before Simulator::Run (p.idx = creation rank: ping
+   * timers in overlay-index order, then the sources, sim.cc:519-560,599-632); 0 when the record has been overwritten. */
+  PRB_HD int
+  parent_of (const PEv &e, PEv &p, int &pos) const
+  {
+    if (e.kind == PK_RCV || e.kind == PK_TXC)
+      {
+        const PRec &r = d.rings[ps.ring_off[e.idx] + (e.seq & ps.ring_mask[e.idx])];
+        const uint64_t xw = r.xw;
+        const int kind = (int) (xw >> 61);
+        if ((uint32_t) (xw & 0xFFFFu) != (e.seq & 0xFFFFu) || kind == PK_NONE || kind > PK_PING) return 0;
+        p.kind = kind; p.idx = (int32_t) ((xw >> 40) & 0xFFFFu); p.seq = (uint32_t) ((xw >> 16) & 0xFFFFFFu); p.t = r.s;
+        pos = (int) ((xw >> 56) & 31u) * 2 + (e.kind == PK_RCV ? 1 : 0);
+        return 1;
+      }
+    pos = P_POS_LAST;
+    if (e.kind == PK_FLOW)
+      {
+        const int f = e.idx;
+        if (st.inject_mode == PRB_INJECT_TRACE)
+          {
+            int32_t pv = ps.tr_prev[(int32_t) e.seq];
+            if (pv < 0)
+              {
+                p.kind = PK_NONE; p.idx = st.M + f; p.seq = 0; p.t = -1;
+                return 2;
+              }
+            p.kind = PK_FLOW; p.idx = f; p.seq = (uint32_t) pv; p.t = st.tr_t[pv];
+            return 1;
+          }
+        uint32_t nd = e.seq - 1;          /* ordinal of the gap that produced e.t */
+        if (nd <= 1)
+          {
+            p.kind = PK_NONE; p.idx = st.M + f; p.seq = 0; p.t = -1;
+            return 2;
+          }
+        p.kind = PK_FLOW; p.idx = f; p.seq = e.seq - 1; p.t = e.t - philox_gap (f, nd);
+        return 1;
+      }
+    /* ping timer */
+    if (e.seq == 0)
+      {
+        p.kind = PK_NONE; p.idx = e.idx; p.seq = 0; p.t = -1;
+        return 2;
+      }
+    p.kind = PK_PING; p.idx = e.idx; p.seq = e.seq - 1; p.t = e.t - st.ping_interval_ns;
+    return 1;
+  }
+
+  /* Scheduler order of two events with one timestamp: -1 a first, +1 b first, 0 undecided (a record on the way up has
+   * been overwritten, or the walk is longer than P_WALK_MAX generations). */
+  PRB_HDN int
+  lineage_cmp (PEv a, PEv b) const
+  {
+    for (int depth = 0; depth < P_WALK_MAX; depth++)
+      {
+        if (a.kind == b.kind && a.idx == b.idx && a.seq == b.seq) return 0;       /* one event */
+        /* every ping timer fires at the same instants: two firings with one timestamp belong to one round and run in
+         * the order the timers were created */
+        if (a.kind == PK_PING && b.kind == PK_PING) return a.idx < b.idx ? -1 : 1;
+        PEv pa, pb;
+        int posa, posb;
+        const int ra = parent_of (a, pa, posa), rb = parent_of (b, pb, posb);
+        if (ra == 0 || rb == 0) return 0;
+        if (pa.t != pb.t) return pa.t < pb.t ? -1 : 1;
+        if (ra == 2 || rb == 2)
+          {
+            if (ra != rb) return ra == 2 ? -1 : 1;       /* cannot happen (setup time is -1); keep the order total */
+            return pa.idx < pb.idx ? -1 : (pa.idx > pb.idx ? 1 : 0);
+          }
+        if (pa.kind == pb.kind && pa.idx == pb.idx && pa.seq == pb.seq)
+          return posa < posb ? -1 : (posa > posb ? 1 : 0);
+        a = pa; b = pb;
+      }
+    return 0;
   }
 
   /* earliest injection among the flows of node x; equal times: the one scheduled first */
@@ -646,7 +666,7 @@ struct PSim
     switch (c.kind)
       {
       case PK_RCV:
-        return rcv_ctx (c.idx, base + c.ts, d.rings[ps.ring_off[c.idx] + (d.head[c.idx] & ps.ring_mask[c.idx])]);
+        return rcv_ctx (c.idx, base + c.ts, d.rings[ps.ring_off[c.idx] + (d.head[c.idx] & ps.ring_mask[c.idx])], d.head[c.idx]);
       case PK_TXC:
         return txc_ctx (c.idx, base + c.ts);
       case PK_FLOW:
@@ -656,46 +676,21 @@ struct PSim
       }
   }
 
-  /* is the packet at the head of access link l one of flow f? */
-  PRB_HD bool
-  sent_by_flow (int l, int f) const
-  {
-    if (l < st.L) return false;
-    const PRec &r = d.rings[ps.ring_off[l] + (d.head[l] & ps.ring_mask[l])];
-    return (int) ((r.w0 >> 16) & 255) == (int) st.flow_src[f] && (int) ((r.w0 >> 24) & 255) == (int) st.flow_dst[f]
-           && (int) (r.w0 & 7) == PRB_DATA;
-  }
-
-  /* true when a runs before b (same timestamp, same node).
-   * 1. the event that was scheduled earlier has the smaller scheduler uid;
-   * 2. TransmitStart schedules its TransmitComplete before the peer's Receive (zero-delay access link);
-   * 3. scheduled at the same instant: the parents ran at the same instant, and so on back — the histories
-   *    (POrd) are compared generation by generation, down to the creation order of the setup events (ping
-   *    timers in overlay-index order before the sources, sim.cc:519-560,599-632) and the tunnel order inside
-   *    one ping round (data-packet-manager.cc:349-357);
-   * 3b. a source's packet reaches the node (access link) before the source's next packet is scheduled;
-   * 4. histories that do not tell (shed entries, a source among the ancestors) set PRB_ERR_TIE unless the
-   *    two events cannot influence each other (TransmitComplete of two different devices). */
+  /* true when a runs before b (same timestamp, same node): the event that was scheduled earlier has the smaller
+   * scheduler uid; scheduled at the same instant, the lineages decide (lineage_cmp).  A pair the walk cannot decide sets
+   * PRB_ERR_TIE unless the two events cannot influence each other (TransmitComplete of two different devices). */
   PRB_HDN bool
   tie_before (const PCand &a, const PCand &b)
   {
     PCtx ca = cand_ctx (a), cb = cand_ctx (b);
     if (ca.sched != cb.sched) return ca.sched < cb.sched;
-    if (a.kind == PK_TXC && b.kind == PK_RCV && a.idx == b.idx) return true;
-    if (a.kind == PK_RCV && b.kind == PK_TXC && a.idx == b.idx) return false;
-    /* a source hands its packet to the device (Send -> TransmitStart schedules the peer's Receive) before it
-     * schedules its next packet (poisson-application.cc:331,357): gaps as short as the access link's
-     * serialisation time do occur */
-    if (a.kind == PK_FLOW && b.kind == PK_RCV && sent_by_flow (b.idx, a.idx)) return false;
-    if (a.kind == PK_RCV && b.kind == PK_FLOW && sent_by_flow (a.idx, b.idx)) return true;
-    int r = ord_compare (ca.ord, cb.ord);
+    int r = lineage_cmp (ev_of (ca, base + a.ts), ev_of (cb, base + b.ts));
     if (r != 0) return r < 0;
     if (!(a.kind == PK_TXC && b.kind == PK_TXC))
       {
 #if defined(PRB_DEBUG_TIES) && !defined(__CUDA_ARCH__)
-        fprintf (stderr, "tie: ts=%lld sched=%lld a=(%d,%d) b=(%d,%d) ord=%016llx.%016llx / %016llx.%016llx\n", (long long) (base + a.ts),
-                 (long long) ca.sched, a.kind, a.idx, b.kind, b.idx, (unsigned long long) ca.ord.a, (unsigned long long) ca.ord.b,
-                 (unsigned long long) cb.ord.a, (unsigned long long) cb.ord.b);
+        fprintf (stderr, "tie: ts=%lld sched=%lld a=(%d,%d,%u) b=(%d,%d,%u)\n", (long long) (base + a.ts), (long long) ca.sched,
+                 a.kind, a.idx, ca.seq, b.kind, b.idx, cb.seq);
 #endif
         acc.errors |= PRB_ERR_TIE;
       }
@@ -852,12 +847,13 @@ struct PSim
     int l = c.idx;
     /* (A) */
     PRec r;
-    r.w0 = 0; r.uid = 0; r.aux = 0; r.ord.a = 0; r.ord.b = 0;
+    r.w0 = 0; r.uid = 0; r.aux = 0; r.s = 0; r.xw = 0;
+    uint16_t ri = 0;
     if (kind == PK_RCV || kind == PK_TXC)
       {
-        uint16_t i = kind == PK_RCV ? d.head[l] : d.mid[l];
-        r = d.rings[ps.ring_off[l] + (i & ps.ring_mask[l])];
-        if (kind == PK_RCV) d.head[l] = (uint16_t) (i + 1);
+        ri = kind == PK_RCV ? d.head[l] : d.mid[l];
+        r = d.rings[ps.ring_off[l] + (ri & ps.ring_mask[l])];
+        if (kind == PK_RCV) d.head[l] = (uint16_t) (ri + 1);
       }
     Pkt p;
     to_pkt (r, p);
@@ -868,7 +864,7 @@ struct PSim
     if (kind == PK_RCV)
       {
         /* PointToPointNetDevice::Receive (+ agent hook, ExecuteActions, IP forward, statistics) */
-        cur = rcv_ctx (l, now_abs, r);
+        cur = rcv_ctx (l, now_abs, r, ri);
         bool access = l >= st.L;
         int type = p_type (p);
         acc.ev_real++;
@@ -1031,7 +1027,6 @@ struct PSim
     /* (C) */
     for (int i = 0; i < ns; i++)
       {
-        uint32_t branch = P_NONE16;
         int li = i == 0 ? l0 : l1;
         Pkt q = i == 0 ? s0 : s1;
         if (kind == PK_PING)
@@ -1042,9 +1037,8 @@ struct PSim
             set_p_tunnel (q, i);
             q.uid = d.ping_index[m]; q.aux = (uint32_t) (now_abs / 1000000);
             li = st.route[x * st.N + nb];
-            branch = (uint32_t) i;
           }
-        dev_send (x, li, now, q, cur, branch, mode);
+        dev_send (x, li, now, q, cur, (uint32_t) i, mode);
       }
     if (kind == PK_PING)
       {

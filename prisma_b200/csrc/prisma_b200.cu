@@ -1009,8 +1009,7 @@ upload_ptables (prb_env *env)
   std::vector<char> buf;
   size_t o[8];
   place (buf, pm.in_links, o[0]); place (buf, pm.out_links, o[1]); place (buf, pm.ring_off, o[2]);
-  place (buf, pm.ring_mask, o[3]); place (buf, pm.flow_begin, o[4]); place (buf, pm.dcode_rcv, o[5]);
-  place (buf, pm.dcode_txc, o[6]);
+  place (buf, pm.ring_mask, o[3]); place (buf, pm.flow_begin, o[4]);
   CUDA_TRY (cudaMalloc (&env->d_ptables, buf.size ()));
   CUDA_TRY (cudaMemcpyAsync (env->d_ptables, buf.data (), buf.size (), cudaMemcpyHostToDevice, env->stream));
   CUDA_TRY (cudaMalloc (&env->d_pblob0, pm.ps.pblob_bytes));
@@ -1022,8 +1021,7 @@ upload_ptables (prb_env *env)
   char *b = env->d_ptables;
   s.in_links = (const int16_t *) (b + o[0]); s.out_links = (const int16_t *) (b + o[1]);
   s.ring_off = (const int32_t *) (b + o[2]); s.ring_mask = (const uint16_t *) (b + o[3]);
-  s.flow_begin = (const int32_t *) (b + o[4]); s.dcode_rcv = (const uint16_t *) (b + o[5]);
-  s.dcode_txc = (const uint16_t *) (b + o[6]);
+  s.flow_begin = (const int32_t *) (b + o[4]);
   s.tr_prev = nullptr; s.pol_off = nullptr;
   return PRB_OK;
 }
@@ -1038,6 +1036,8 @@ ensure_par_state (prb_env *env)
   cudaError_t e = cudaMalloc (&env->d_pblobs, (size_t) ps.pblob_bytes * st.E);
   if (e == cudaSuccess) e = cudaMalloc (&env->d_rings, sizeof (PRec) * (size_t) ps.ring_records * st.E);
   if (e != cudaSuccess) return fail (PRB_ENOMEM, std::string ("cudaMalloc (parallel engine state): ") + cudaGetErrorString (e));
+  /* no record has been written yet: every lineage field reads as "no transmission start" (P_XW_QUEUED) */
+  CUDA_TRY (cudaMemsetAsync (env->d_rings, 0xFF, sizeof (PRec) * (size_t) ps.ring_records * st.E, env->stream));
   int64_t work = (int64_t) ps.pblob_bytes / 16 * st.E;
   int blocks = (int) std::min<int64_t> ((work + 255) / 256, 148 * 16);
   k_reset_par<<<blocks, 256, 0, env->stream>>> (st, ps, env->d_pblobs, env->d_pblob0);

@@ -86,5 +86,28 @@ def test_random_network_both_cores_against_the_restatement(seed):
 
 
 def test_hand_overs_are_the_exception():
-    """Runs after the cases above: an undecided tie must stay rare, or the parallel core would not be one."""
-    assert len(HANDED_OVER) <= 2, HANDED_OVER
+    """Runs after the cases above: with the lineage walk none of the 12 cases is handed over."""
+    assert len(HANDED_OVER) == 0, HANDED_OVER
+
+
+@pytest.mark.parametrize("seed", [0, 3, 5, 7, 9, 11])
+def test_short_lineage_retention_flags_but_never_errs(seed, monkeypatch):
+    """The lineage of an event is read from consumed ring records until the ring wraps.  With (almost) no retention
+    (PRB_LINEAGE_RECORDS=8: the rings hold the live packets only) a walk soon meets an overwritten record: the engine may
+    then flag the environment (hand-over), it must never finish with a result that differs."""
+    monkeypatch.setenv("PRB_LINEAGE_RECORDS", "8")
+    cfg, env_id = random_case(seed)
+    arrays = cfg.load()
+    table = common.sp_table(arrays)
+    osim = common.oracle_run(cfg, arrays, oracle, policy="table", table=table, env_id=env_id)
+    try:
+        hp = host_sim.HostParSim(cfg.abi_params(arrays, env_id_base=env_id), team=16 if arrays.n_nodes <= 16 else 32)
+    except Exception as ex:
+        pytest.skip("parallel core refuses: %s" % ex)
+    hp.set_policy("table", table)
+    hp.run(log=False)
+    pc = hp.counters()
+    if pc["errors"] & (PRB_ERR_TIE | PRB_ERR_POOL):
+        return
+    common.assert_counters_equal(osim.counters(), pc)
+    assert np.array_equal(osim.queue_bytes(), hp.queue_bytes())
