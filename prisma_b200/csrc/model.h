@@ -567,6 +567,8 @@ build_pmodel (const prb_config &c, const HostModel &hm, PModel &pm)
   auto ring_bytes = [&] (int32_t sw, int32_t ac) { return (int64_t) sizeof (PRec) * ((int64_t) L * sw + (int64_t) (LA - L) * ac) * std::max<int64_t> (c.num_envs, 1); };
   while (lin > rc && ring_bytes (std::max (rc, lin), std::max (8, lin / 8)) > budget * (1ll << 20)) lin /= 2;
   const int32_t rc_sw = std::max (rc, lin), rc_ac = std::max (8, lin / 8);
+  ps.walk_max = P_WALK_MAX;
+  if (const char *e = getenv ("PRB_LINEAGE_WALK_MAX")) ps.walk_max = std::max (0, atoi (e));    /* tests: 0 = no walk, every such tie is handed over */
   pm.ring_off.assign (LA, 0);
   pm.ring_mask.assign (LA, 0);
   int32_t off = 0;

@@ -125,6 +125,7 @@ struct PStatic
   int32_t W;                 /* wire-ring slots per link (power of two) */
   int32_t DEG;               /* row length of in_links / out_links */
   int32_t ring_records;      /* PRec per environment */
+  int32_t walk_max;          /* generations a lineage walk may climb (P_WALK_MAX; PRB_LINEAGE_WALK_MAX for tests) */
   uint32_t la32;             /* la_ns as a 32-bit offset */
   int64_t la_ns;             /* smallest (tx + delay) of a switch<->switch link */
   int64_t max_chunk_ns;      /* longest stretch of simulated time one launch may cover (32-bit offsets) */
@@ -228,6 +229,106 @@ struct PCtx
   uint32_t seq;
 };
 constexpr int64_t P_SCHED_LAZY = INT64_MIN + 1;
+
+/* gap (nd >= 1) or start offset (nd == 0) of synthetic source f of environment env: Philox-4x32-10, DESIGN.md section 2 */
+PRB_HDN inline int64_t
+p_philox_gap (const Static &st, int env, int f, uint32_t nd)
+{
+  uint64_t eid = st.env_id_base + (uint64_t) env;
+  uint32_t fkey = (uint32_t) (st.flow_src[f] * st.N + st.flow_dst[f]);
+  uint32_t r[4];
+  philox4x32 ((uint32_t) eid, (uint32_t) (eid >> 32), fkey, nd, (uint32_t) st.seed, (uint32_t) (st.seed >> 32), r);
+  if (nd == 0) return 100000 + (int64_t) dmul_ (u01_53 (r[0], r[1]), 1e9);      /* start offset of the source */
+  double u = u01_53 (r[0], r[1]);
+  double delay = dmul_ (st.flow_mean_s[f], neglog (u));
+  return (int64_t) dmul_ (delay, 1e9);
+}
+
+/* ---- lineage (see PRec) ---- */
+/* The event that scheduled e.  Returns 1 and fills p (with its timestamp) and pos (the place of the Schedule call
+ * inside p's handler: Send number * 2, + 1 for the peer's Receive, which TransmitStart schedules after the
+ * TransmitComplete, point-to-point-net-device.cc:295-296; P_POS_LAST for what a source or a ping timer schedules after
+ * its Sends, poisson-application.cc:331,357); 2 when e was scheduled before Simulator::Run (p.idx = creation rank: ping
+ * timers in overlay-index order, then the sources, sim.cc:519-560,599-632); 0 when the record has been overwritten. */
+PRB_HD int
+p_parent_of (const Static &st, const PStatic &ps, const PRec *rings, int env, const PEv &e, PEv &p, int &pos)
+{
+  if (e.kind == PK_RCV || e.kind == PK_TXC)
+    {
+      const PRec &r = rings[ps.ring_off[e.idx] + (e.seq & ps.ring_mask[e.idx])];
+      const uint64_t xw = r.xw;
+      const int kind = (int) (xw >> 61);
+      if ((uint32_t) (xw & 0xFFFFu) != (e.seq & 0xFFFFu) || kind == PK_NONE || kind > PK_PING) return 0;
+      p.kind = kind; p.idx = (int32_t) ((xw >> 40) & 0xFFFFu); p.seq = (uint32_t) ((xw >> 16) & 0xFFFFFFu); p.t = r.s;
+      pos = (int) ((xw >> 56) & 31u) * 2 + (e.kind == PK_RCV ? 1 : 0);
+      return 1;
+    }
+  pos = P_POS_LAST;
+  if (e.kind == PK_FLOW)
+    {
+      const int f = e.idx;
+      if (st.inject_mode == PRB_INJECT_TRACE)
+        {
+          int32_t pv = ps.tr_prev[(int32_t) e.seq];
+          if (pv < 0)
+            {
+              p.kind = PK_NONE; p.idx = st.M + f; p.seq = 0; p.t = -1;
+              return 2;
+            }
+          p.kind = PK_FLOW; p.idx = f; p.seq = (uint32_t) pv; p.t = st.tr_t[pv];
+          return 1;
+        }
+      uint32_t nd = e.seq - 1;          /* ordinal of the gap that produced e.t */
+      if (nd <= 1)
+        {
+          p.kind = PK_NONE; p.idx = st.M + f; p.seq = 0; p.t = -1;
+          return 2;
+        }
+      p.kind = PK_FLOW; p.idx = f; p.seq = e.seq - 1; p.t = e.t - p_philox_gap (st, env, f, nd);
+      return 1;
+    }
+  /* ping timer */
+  if (e.seq == 0)
+    {
+      p.kind = PK_NONE; p.idx = e.idx; p.seq = 0; p.t = -1;
+      return 2;
+    }
+  p.kind = PK_PING; p.idx = e.idx; p.seq = e.seq - 1; p.t = e.t - st.ping_interval_ns;
+  return 1;
+}
+
+/* Scheduler order of two events with one timestamp: -1 a first, +1 b first, 0 undecided (a record on the way up has
+ * been overwritten, or the walk is longer than P_WALK_MAX generations). */
+PRB_NOINLINE int
+p_lineage_cmp (const Static &st, const PStatic &ps, const PRec *rings, int env, uint64_t ak, int64_t at, uint64_t bk, int64_t bt)
+{
+  /* the two events travel as scalars (kind << 48 | idx << 32 | seq, timestamp): register arguments, no stack frame */
+  PEv a, b;
+  a.kind = (int32_t) (ak >> 48); a.idx = (int32_t) ((ak >> 32) & 0xFFFFu); a.seq = (uint32_t) ak; a.t = at;
+  b.kind = (int32_t) (bk >> 48); b.idx = (int32_t) ((bk >> 32) & 0xFFFFu); b.seq = (uint32_t) bk; b.t = bt;
+  for (int depth = 0; depth < ps.walk_max; depth++)
+    {
+      if (a.kind == b.kind && a.idx == b.idx && a.seq == b.seq) return 0;       /* one event */
+      /* every ping timer fires at the same instants: two firings with one timestamp belong to one round and run in
+       * the order the timers were created */
+      if (a.kind == PK_PING && b.kind == PK_PING) return a.idx < b.idx ? -1 : 1;
+      PEv pa, pb;
+      int posa, posb;
+      const int ra = p_parent_of (st, ps, rings, env, a, pa, posa), rb = p_parent_of (st, ps, rings, env, b, pb, posb);
+      if (ra == 0 || rb == 0) return 0;
+      if (pa.t != pb.t) return pa.t < pb.t ? -1 : 1;
+      if (ra == 2 || rb == 2)
+        {
+          if (ra != rb) return ra == 2 ? -1 : 1;       /* cannot happen (setup time is -1); keep the order total */
+          return pa.idx < pb.idx ? -1 : (pa.idx > pb.idx ? 1 : 0);
+        }
+      if (pa.kind == pb.kind && pa.idx == pb.idx && pa.seq == pb.seq)
+        return posa < posb ? -1 : (posa > posb ? 1 : 0);
+      a = pa; b = pb;
+    }
+  return 0;
+}
+
 
 template <bool LOG, int CDEG = 0, int CW = 0>
 struct PSim
@@ -482,17 +583,10 @@ struct PSim
   }
 
   /* ---- sources ---- */
-  PRB_HDN int64_t
+  PRB_HD int64_t
   philox_gap (int f, uint32_t nd) const
   {
-    uint64_t eid = st.env_id_base + (uint64_t) env;
-    uint32_t fkey = (uint32_t) (st.flow_src[f] * st.N + st.flow_dst[f]);
-    uint32_t r[4];
-    philox4x32 ((uint32_t) eid, (uint32_t) (eid >> 32), fkey, nd, (uint32_t) st.seed, (uint32_t) (st.seed >> 32), r);
-    if (nd == 0) return 100000 + (int64_t) dmul_ (u01_53 (r[0], r[1]), 1e9);      /* start offset of the source */
-    double u = u01_53 (r[0], r[1]);
-    double delay = dmul_ (st.flow_mean_s[f], neglog (u));
-    return (int64_t) dmul_ (delay, 1e9);
+    return p_philox_gap (st, env, f, nd);
   }
 
   PRB_HD void
@@ -550,84 +644,12 @@ struct PSim
     return e;
   }
 
-  /* The event that scheduled e.  Returns 1 and fills p (with its timestamp) and pos (the place of the Schedule call
-   * inside p's handler: Send number * 2, + 1 for the peer's Receive, which TransmitStart schedules after the
-   * TransmitComplete, point-to-point-net-device.cc:295-296; P_POS_LAST for what a source or a ping timer schedules after
-   * its Sends, poisson-application.cc:331,357); 2 when e was scheduled before Simulator::Run (p.idx = creation rank: ping
-   * timers in overlay-index order, then the sources, sim.cc:519-560,599-632); 0 when the record has been overwritten. */
+  /* scheduler order of two events with one timestamp (p_lineage_cmp, out of line: rare) */
   PRB_HD int
-  parent_of (const PEv &e, PEv &p, int &pos) const
+  lineage_cmp (const PEv &a, const PEv &b) const
   {
-    if (e.kind == PK_RCV || e.kind == PK_TXC)
-      {
-        const PRec &r = d.rings[ps.ring_off[e.idx] + (e.seq & ps.ring_mask[e.idx])];
-        const uint64_t xw = r.xw;
-        const int kind = (int) (xw >> 61);
-        if ((uint32_t) (xw & 0xFFFFu) != (e.seq & 0xFFFFu) || kind == PK_NONE || kind > PK_PING) return 0;
-        p.kind = kind; p.idx = (int32_t) ((xw >> 40) & 0xFFFFu); p.seq = (uint32_t) ((xw >> 16) & 0xFFFFFFu); p.t = r.s;
-        pos = (int) ((xw >> 56) & 31u) * 2 + (e.kind == PK_RCV ? 1 : 0);
-        return 1;
-      }
-    pos = P_POS_LAST;
-    if (e.kind == PK_FLOW)
-      {
-        const int f = e.idx;
-        if (st.inject_mode == PRB_INJECT_TRACE)
-          {
-            int32_t pv = ps.tr_prev[(int32_t) e.seq];
-            if (pv < 0)
-              {
-                p.kind = PK_NONE; p.idx = st.M + f; p.seq = 0; p.t = -1;
-                return 2;
-              }
-            p.kind = PK_FLOW; p.idx = f; p.seq = (uint32_t) pv; p.t = st.tr_t[pv];
-            return 1;
-          }
-        uint32_t nd = e.seq - 1;          /* ordinal of the gap that produced e.t */
-        if (nd <= 1)
-          {
-            p.kind = PK_NONE; p.idx = st.M + f; p.seq = 0; p.t = -1;
-            return 2;
-          }
-        p.kind = PK_FLOW; p.idx = f; p.seq = e.seq - 1; p.t = e.t - philox_gap (f, nd);
-        return 1;
-      }
-    /* ping timer */
-    if (e.seq == 0)
-      {
-        p.kind = PK_NONE; p.idx = e.idx; p.seq = 0; p.t = -1;
-        return 2;
-      }
-    p.kind = PK_PING; p.idx = e.idx; p.seq = e.seq - 1; p.t = e.t - st.ping_interval_ns;
-    return 1;
-  }
-
-  /* Scheduler order of two events with one timestamp: -1 a first, +1 b first, 0 undecided (a record on the way up has
-   * been overwritten, or the walk is longer than P_WALK_MAX generations). */
-  PRB_HDN int
-  lineage_cmp (PEv a, PEv b) const
-  {
-    for (int depth = 0; depth < P_WALK_MAX; depth++)
-      {
-        if (a.kind == b.kind && a.idx == b.idx && a.seq == b.seq) return 0;       /* one event */
-        /* every ping timer fires at the same instants: two firings with one timestamp belong to one round and run in
-         * the order the timers were created */
-        if (a.kind == PK_PING && b.kind == PK_PING) return a.idx < b.idx ? -1 : 1;
-        PEv pa, pb;
-        int posa, posb;
-        const int ra = parent_of (a, pa, posa), rb = parent_of (b, pb, posb);
-        if (ra == 0 || rb == 0) return 0;
-        if (pa.t != pb.t) return pa.t < pb.t ? -1 : 1;
-        if (ra == 2 || rb == 2)
-          {
-            if (ra != rb) return ra == 2 ? -1 : 1;       /* cannot happen (setup time is -1); keep the order total */
-            return pa.idx < pb.idx ? -1 : (pa.idx > pb.idx ? 1 : 0);
-          }
-        if (pa.kind == pb.kind && pa.idx == pb.idx && pa.seq == pb.seq)
-          return posa < posb ? -1 : (posa > posb ? 1 : 0);
-        a = pa; b = pb;
-      }
-    return 0;
+    return p_lineage_cmp (st, ps, d.rings, env, ((uint64_t) (uint32_t) a.kind << 48) | ((uint64_t) ((uint32_t) a.idx & 0xFFFFu) << 32) | a.seq, a.t,
+                          ((uint64_t) (uint32_t) b.kind << 48) | ((uint64_t) ((uint32_t) b.idx & 0xFFFFu) << 32) | b.seq, b.t);
   }
 
   /* earliest injection among the flows of node x; equal times: the one scheduled first */

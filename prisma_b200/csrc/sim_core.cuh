@@ -33,9 +33,11 @@
 #if defined(__CUDACC__)
 #define PRB_HD __host__ __device__ __forceinline__
 #define PRB_HDN __host__ __device__
+#define PRB_NOINLINE __host__ __device__ __noinline__
 #else
 #define PRB_HD inline
 #define PRB_HDN
+#define PRB_NOINLINE
 #endif
 
 namespace prb {
