@@ -256,7 +256,8 @@ replay_push (const Static &st, const ReplayArgs &ra, int node, const int32_t *en
     {
       /* forwarder.py:494-505: a transit transition carries the gradient step of the node that computed its target
        * and raises the latest step seen for that action; :227-233: a lost packet is added with the latest one */
-      int32_t *lat = &ra.latest[(size_t) node * st.K + ent[3]];
+      const int act = ent[3] < 0 ? 0 : (ent[3] >= st.K ? st.K - 1 : ent[3]);    /* rows only ever hold valid actions */
+      int32_t *lat = &ra.latest[(size_t) node * st.K + act];
       int32_t g = from_node >= 0 ? ra.node_gstep[from_node] : *lat;
       if (from_node >= 0) atomicMax (lat, g);
       ra.row_gstep[(size_t) node * ra.cap + slot] = (float) g;
@@ -311,8 +312,15 @@ replay_record_one (const Static &st, const ReplayArgs &ra, int e, const prb_step
       else
         atomicAdd (ra.missed, 1ull);
     }
-  /* the decision taken now travels with the packet */
-  if (r->need_action)
+  /* the decision taken now travels with the packet — unless the action names no neighbour: the packet vanishes
+   * (data-packet-manager.cc:294-297), the reference never completes such a transition, and rows index per-action
+   * tables with it */
+  if (r->need_action && (action < 0 || action >= (int32_t) st.agent_k[r->overlay]))
+    {
+      atomicAdd (ra.missed, 1ull);
+      if (ent[0] == (int32_t) r->uid && ent[1] == (int32_t) (r->uid >> 32)) ent[2] = -1;
+    }
+  else if (r->need_action)
     {
       ent[0] = (int32_t) r->uid; ent[1] = (int32_t) (r->uid >> 32); ent[2] = r->overlay; ent[3] = action;
       for (int i = 0; i < ow; i++) ent[4 + i] = r->obs[i];
@@ -333,6 +341,7 @@ replay_priority (const ReplayArgs &ra, int node, unsigned long long idx, int ow,
 {
   const float *row = ra.rows + ((size_t) node * ra.cap + idx) * ra.R;
   int a = (int) row[ow];
+  a = a < 0 ? 0 : (a >= K ? K - 1 : a);
   float lat = (float) ra.latest[(size_t) node * K + a];
   float g = ra.row_gstep[(size_t) node * ra.cap + idx];
   return powf (g / (lat > 0.0f ? lat : 1.0f), ra.alpha);

@@ -413,35 +413,72 @@ class Ns3EnvGroup:
             return -1 if self._ended else int(self._rec["overlay"])
 
     def info_string(self, rec, c) -> str:
-        """PacketManager::getInfo (prisma/ns3/packet-manager.cc:119-176, fields 0-17) followed by the fields of the
-        packet's own manager — data: Packet Lost / Source / Destination / node (data-packet-manager.cc:229-248);
-        small signalling: PacketIdSignaled / Arrived at final dest (small-signaling-packet-manager.cc:109-119);
-        big signalling: NN Index / segment Index / NodeId Signaled (big-signaling-packet-manager.cc:110-122) —
-        in the positions Forwarder.treat_info reads them from (prisma/source/forwarder.py:197-289)."""
-        size = self.benv.cfg.packet_size + 28 if rec["ptype"] == 0 else 0
-        mo = self.benv.arrays.map_overlay
+        return format_info(rec, c, self.benv.arrays.map_overlay, self.benv.cfg.packet_size)
+
+
+def format_info(rec, c, map_overlay, packet_size) -> str:
+    """The reference's info string, key for key and separator for separator: PacketManager::getInfo
+    (prisma/ns3/packet-manager.cc:119-176, fields 0-17: note the irregular blanks around '=' and after ','), followed by
+    the fields of the packet's own manager — data: Packet Lost / Source / Destination / node
+    (data-packet-manager.cc:229-248); small signalling: PacketIdSignaled / Arrived at final dest
+    (small-signaling-packet-manager.cc:109-119); big signalling: NN Index / segment Index / NodeId Signaled
+    (big-signaling-packet-manager.cc:110-122).  Numbers are std::to_string's: "%f" for doubles and floats.
+    Forwarder.treat_info reads the fields by position (prisma/source/forwarder.py:197-289).
+    rec: one prb_step_rec (numpy record or mapping), c: the environment's prb_counters."""
+    ptype = int(rec["ptype"])
+    # m_packetSize is the size on the wire: payload + 30 (data; a source pads payloads below 200 bytes,
+    # poisson-application.cc:277-278), 512 + 30 for an NN segment.  Not reproduced for signalling records, and never
+    # read there by Forwarder.treat_info: field 0 (an uninitialised member in the reference), field 1 of small
+    # signalling (the sender's degree decides it) and field 3 (ns-3's global Packet uid).
+    if ptype == 0:
+        size = (max(packet_size, 200) if int(rec["is_new"]) and int(rec["prev_node"]) < 0 else packet_size) + 30
+    else:
+        size = 542 if ptype == 1 else 0
+    mo = map_overlay
+    uid = int(rec["uid"])
+    buffered_o = int(c["overlay_injected"]) - int(c["overlay_arrived"]) - int(c["overlay_lost"])
+    buffered_u = int(c["underlay_injected"]) - int(c["underlay_arrived"]) - int(c["underlay_lost"])
+    # field 0 is a double in the reference: Now().GetSeconds() - m_sourceTimeStamp, the tag's start time being whole
+    # seconds (poisson-application.cc:310); the record carries it as float32, from which the integer is recovered
+    now_s = int(rec["t_ns"]) / 1e9
+    start_s = round(now_s - float(rec["e2e_delay"]))
+    s = "End to End Delay=%f" % (now_s - start_s if ptype == 0 else float(rec["e2e_delay"]))
+    s += ", Packet Size=%d" % size
+    s += ", Current sim time =%f" % now_s
+    s += ", Pkt ID =%d" % (0 if ptype == 1 else uid)
+    s += ", packetType =%d" % ptype
+    s += ", Avg End to End Delay =%f" % float(c["avg_e2e"])
+    s += ", Avg Cost =%f" % float(c["avg_cost"])
+    s += ", Avg Underlay End to End Delay =%f" % float(c["avg_underlay_e2e"])
+    s += ", Avg Underlay Cost =%f" % float(c["avg_underlay_cost"])
+    s += ", Packets dropped =%d" % int(c["overlay_lost"])
+    s += ", Packets delivered =%d" % int(c["overlay_arrived"])
+    s += ", Packets injected =%d" % int(c["overlay_injected"])
+    s += ",Packets Buffered =%d" % buffered_o
+    s += ", Packets dropped Underlay =%d" % int(c["underlay_lost"])
+    s += ", Packets delivered Underlay=%d" % int(c["underlay_arrived"])
+    s += ", Packets injected Underlay=%d" % int(c["underlay_injected"])
+    s += ",Packets Buffered Underlay=%d" % buffered_u
+    s += ",Signaling overhead =%f" % float(c["signaling_overhead"])
+    if ptype == 1:
+        s += ", NN Index=%d, segment Index=%d, NodeId Signaled=%d" % (uid >> 32, uid & 0xFFFFFFFF, int(mo[int(rec["prev_node"])]))
+    elif ptype == 2:
+        s += ", PacketIdSignaled=%d, Arrived at final dest=%d" % (uid, 1)
+    else:
         lost = "".join("%d;" % int(u) for u in rec["lost_uid"][:min(int(rec["n_lost"]), 8)])
-        buffered_o = int(c["overlay_injected"] - c["overlay_arrived"] - c["overlay_lost"])
-        buffered_u = int(c["underlay_injected"] - c["underlay_arrived"] - c["underlay_lost"])
-        f = [("End to End Delay", "%f" % rec["e2e_delay"]), ("Packet Size", size),
-             ("Current sim time", "%f" % (rec["t_ns"] * 1e-9)), ("Pkt ID", int(rec["uid"])),
-             ("Pkt Type", int(rec["ptype"])), ("Avg End to End Delay", "%f" % c["avg_e2e"]),
-             ("Avg Cost", "%f" % c["avg_cost"]), ("Underlay Avg End to End Delay", "%f" % c["avg_underlay_e2e"]),
-             ("Underlay Avg Cost", "%f" % c["avg_underlay_cost"]), ("Overlay Pkts Dropped", int(c["overlay_lost"])),
-             ("Overlay Pkts Delivered", int(c["overlay_arrived"])), ("Overlay Pkts Injected", int(c["overlay_injected"])),
-             ("Overlay Pkts Buffered", buffered_o), ("Underlay Pkts Dropped", int(c["underlay_lost"])),
-             ("Underlay Pkts Delivered", int(c["underlay_arrived"])), ("Underlay Pkts Injected", int(c["underlay_injected"])),
-             ("Underlay Pkts Buffered", buffered_u), ("Signaling Overhead", "%f" % c["signaling_overhead"])]
-        if rec["ptype"] == 1:
-            f += [("NN Index", int(rec["uid"]) >> 32), ("segment Index", int(rec["uid"]) & 0xFFFFFFFF),
-                  ("NodeId Signaled", int(mo[int(rec["prev_node"])]))]
-            f[3] = ("Pkt ID", -1)
-        elif rec["ptype"] == 2:
-            f += [("PacketIdSignaled", int(rec["uid"])), ("Arrived at final dest", 1)]
-        else:
-            f += [("Packet Lost", lost), ("Source", int(mo[int(rec["src"])])), ("Destination", int(rec["obs"][0])),
-                  ("node", int(rec["overlay"]))]
-        return ",".join("%s=%s" % kv for kv in f)
+        s += ", Packet Lost=%s, Source=%d, Destination=%d, node=%d" % (lost, int(mo[int(rec["src"])]), int(rec["obs"][0]),
+                                                                      int(rec["overlay"]))
+    return s
+
+
+class _NoBridge:
+    """Stands where Ns3ZmqBridge (prisma/ns3_model/ns3env.py:33-375) stood: there is no socket to close."""
+
+    def send_close_command(self):
+        return True
+
+    def close(self):
+        return None
 
 
 class Ns3EnvCompat:
@@ -455,6 +492,7 @@ class Ns3EnvCompat:
         self.action_space = _Discrete(k)
         self.observation_space = _Box(0, 16260, (1 + k,), np.uint32)   # data-packet-manager.cc:139-141
         self.connected = True
+        self.ns3ZmqBridge = _NoBridge()       # Forwarder.run ends with env.ns3ZmqBridge.send_close_command() (forwarder.py:331)
 
     def _wait_mine(self, timeout=None):
         """Called with the group's condition held: blocks until the ready step is this node's."""

@@ -2,7 +2,8 @@
 prisma/main.py (prisma/source/argument_parser.py:33-98, same names and defaults) and runs the session on the
 device-side environment instead of ns-3 + ZMQ + one Python thread per node:
 
-* `--train=0`, or an agent without learning (`sp`, `opt`, `dqn_routing` loaded as a next-hop table): every
+* `--train=0`, or an agent without learning (`sp`, `dqn_routing` loaded as a next-hop table; `opt` is refused: it is a
+  caller-side Gym-mode hook, `prisma_b200.agents.OptAgent`): every
   environment of the batch runs `simTime` seconds inside `prb_run`; the summary of prisma/main.py:152-172 is
   printed and the `stats_writer_test` scalars are written (prisma/source/tb_logger.py:145-164).
 * `--train=1 --agent_type=dqn_buffer`: the Gym loop runs on the device (`prb_step_qnet`: Q-network forward,
@@ -100,6 +101,14 @@ def build_parser() -> argparse.ArgumentParser:
 def parse_arguments(argv=None) -> dict:
     """The `params` dict of prisma/source/argument_parser.py:100-164 (absolute paths, session name and log folders)."""
     params = vars(build_parser().parse_args(argv))
+    # combinations this driver has no device path for are refused here, with the way out, instead of failing in set_agent
+    if params["agent_type"] == "opt":
+        raise SystemExit("--agent_type opt: the optimal-solution agent is a per-(source, destination) probabilistic choice "
+                         "(utils.py:161-199) evaluated by the caller in Gym mode (prisma_b200.agents.OptAgent); this driver "
+                         "runs table and dqn_buffer agents only")
+    if params["agent_type"] == "dqn_routing" and not params["load_path"]:
+        raise SystemExit("--agent_type dqn_routing needs --load_path with a routing_table.txt (a destination-only network is "
+                         "served as a next-hop table); to train on the device use --agent_type dqn_buffer")
     for k in ("logs_parent_folder", "physical_adjacency_matrix_path", "overlay_adjacency_matrix_path", "map_overlay_path"):
         params[k] = os.path.abspath(params[k])
     if params["load_path"]:
@@ -144,7 +153,7 @@ def overlay_neighbor_indices(env):
 
 
 def run_fixed_agent(env, params, episode):
-    """sp / opt / a loaded dq_routing table: the agent hook is evaluated on the device inside prb_run."""
+    """sp / a loaded dq_routing table: the agent hook is evaluated on the device inside prb_run."""
     env.reset()
     table = None
     if params["agent_type"] == "dqn_routing" and params["load_path"]:

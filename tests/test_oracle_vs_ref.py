@@ -137,3 +137,46 @@ def test_time_arithmetic_kats():
         elif a[0] == "ns2s":
             got = struct.unpack("Q", struct.pack("d", oracle.ns_to_seconds(int(a[1]))))[0]
             assert got == int(a[2], 16), a
+
+
+def _skeleton(info):
+    """An info string with every value removed: the keys, the separators and the irregular blanks of the reference."""
+    import re
+    return re.sub(r"=[^,]*", "=", info)
+
+
+def test_info_string_is_byte_compatible_with_the_reference(tmp_path):
+    """format_info (prisma_b200/env.py) against the strings the reference's getInfo() produced in the same run
+    (packet-manager.cc:119-176, data-packet-manager.cc:229-248, small-/big-signaling-packet-manager.cc): keys,
+    separators and blanks byte for byte for every packet type; for data packets also every value that belongs to the
+    step (fields 0-4 and the manager's own fields).  The running averages (fields 5-17) are compared by the counter
+    tests; fields 0, 1 and 3 of signalling records hold an uninitialised member / ns-3's global Packet uid."""
+    from prisma_b200.env import format_info
+    cfg, arrays, summ, route, ev, dec, sim = run_case("abilene_train_nn_big_signaling", str(tmp_path))
+    od = sim.decisions()
+    zero = {k: 0 for k in ("overlay_injected", "overlay_arrived", "overlay_lost", "underlay_injected", "underlay_arrived",
+                           "underlay_lost", "avg_e2e", "avg_cost", "avg_underlay_e2e", "avg_underlay_cost",
+                           "signaling_overhead")}
+    seen = set()
+    n_data = 0
+    inj = ev[(ev["kind"] == 0) & (ev["type"] == 0)]
+    src_of = {int(u): int(s) for u, s in zip(inj["uid"], inj["src"])}      # the restatement's record has no source field
+    for r, o in zip(dec, od):
+        o = {k: o[k] for k in o.dtype.names}
+        o["src"] = src_of.get(int(o["uid"]), 0)
+        mine = format_info(o, zero, arrays.map_overlay, cfg.packet_size)
+        assert _skeleton(mine) == _skeleton(r["info"]), (mine, r["info"])
+        seen.add(int(o["ptype"]))
+        if o["ptype"] == 0:
+            a, b = mine.split(","), r["info"].split(",")
+            assert a[:5] == b[:5] and a[18:] == b[18:], (mine, r["info"])
+            n_data += 1
+        elif o["ptype"] == 1:
+            assert mine.split(",")[18:] == r["info"].split(",")[18:] and mine.split(",")[4] == r["info"].split(",")[4]
+    assert seen == {0, 1, 2} and n_data > 500
+
+
+def test_compat_view_has_the_bridge_forwarder_closes():
+    """Forwarder.run ends with self.env.ns3ZmqBridge.send_close_command() (forwarder.py:331)."""
+    from prisma_b200.env import _NoBridge
+    assert _NoBridge().send_close_command() is True
