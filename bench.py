@@ -221,6 +221,169 @@ def run_reference_arm(args, rank, world):
 
 
 # ------------------------------------------------------------------------------------------------
+# secondary legs: BASELINE.json configs[2], [3], [4] at this rank's share, and the learner's gradient exchange
+# ------------------------------------------------------------------------------------------------
+
+def _timed(torch, fn):
+    torch.cuda.synchronize()
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    a.record()
+    fn()
+    b.record()
+    torch.cuda.synchronize()
+    return a.elapsed_time(b) / 1000.0
+
+
+def _reduce(dist, torch, world, sums, maxes):
+    """Whole-job figures: counts are summed over the ranks, times are the slowest rank's."""
+    if world > 1:
+        s = torch.tensor(sums, dtype=torch.float64, device="cuda")
+        dist.all_reduce(s, op=dist.ReduceOp.SUM)
+        m = torch.tensor(maxes, dtype=torch.float64, device="cuda")
+        dist.all_reduce(m, op=dist.ReduceOp.MAX)
+        return [float(x) for x in s], [float(x) for x in m]
+    return list(sums), list(maxes)
+
+
+def leg_table_run(torch, dist, rank, local_rank, world, topo, envs, load_factor, lead_s, timed_s, peak, extra=None):
+    """prb_run with the shortest-path table on `envs` environments per GPU: `lead_s` untimed simulated seconds (queues
+    fill), then `timed_s` one-second steps timed on the device with the hand-over check inside the timed region."""
+    from prisma_b200.env import BatchedRoutingEnv, sp_table
+    cfg = workload_cfg(envs, lead_s + timed_s, topo=topo, load_factor=load_factor)
+    for k, v in (extra or {}).items():
+        setattr(cfg, k, v)
+    arrays = cfg.load()
+    env = BatchedRoutingEnv(cfg, device=local_rank, arrays=arrays, env_id_base=rank * envs)
+    env.set_policy("table", sp_table(arrays))
+    env.run(until_s=float(lead_s))
+    c0 = env.counters()
+
+    def go():
+        for t in range(int(timed_s)):
+            env.run(until_s=float(lead_s + t + 1))
+            env.handovers()
+    dt = _timed(torch, go)
+    c1 = env.counters()
+    env.check_errors(c1)
+    engine = env.engine
+    handed, replay_ms = env.handover_stats() if engine == "parallel" else (0, 0.0)
+    kdeg = max(len(x) for x in arrays.overlay_neighbors())
+    d = lambda k: float(c1[k].sum() - c0[k].sum())
+    lost = float(c1["overlay_lost"].sum()) / max(float(c1["overlay_injected"].sum()), 1.0)
+    (hops, steps, handed), (dt,) = _reduce(dist, torch, world, [d("packet_hops"), d("env_steps"), handed], [dt])
+    env.close()
+    b_hop = B_HOP_BASE + 4 * (1 + kdeg)
+    return {"topology": topo, "nodes": int(arrays.n_nodes), "envs_per_gpu": envs, "total_envs": envs * world,
+            "load_factor": load_factor, "engine": engine, "timed_window_sim_s": [lead_s, lead_s + timed_s],
+            "packet_hops_per_s": hops / dt, "env_steps_per_s": steps / dt, "overlay_loss": lost,
+            "envs_replayed_by_the_serial_engine": int(handed),
+            "roofline_frac": hops / dt * b_hop / 1e9 / (peak * world), "bytes_per_packet_hop": b_hop}
+
+
+def leg_device_agents(torch, dist, rank, local_rank, world, topo, envs, load_factor, calls, peak, extra=None):
+    """The Gym loop with dqn_buffer agents on the device (prb_step_qnet) and the replay rows written to the HBM rings."""
+    from prisma_b200 import qnet
+    from prisma_b200.env import BatchedRoutingEnv
+    cfg = workload_cfg(envs, 60.0, topo=topo, load_factor=load_factor)
+    cfg.agent_type = "dqn_buffer"
+    for k, v in (extra or {}).items():
+        setattr(cfg, k, v)
+    arrays = cfg.load()
+    env = BatchedRoutingEnv(cfg, device=local_rank, arrays=arrays, env_id_base=rank * envs)
+    deg = [len(n) for n in env.neighbors]
+    env.qnet_load(qnet.pack_weights(qnet.init_weights(len(deg), deg, max(deg), seed=1)))
+    env.replay_enable(rows_per_node=1 << 18)
+    env.step_qnet(calls // 2, eps=0.05, seed=rank)
+    c0 = env.counters()
+    dt = _timed(torch, lambda: env.step_qnet(calls, eps=0.05, seed=1000 + rank))
+    c1 = env.counters()
+    env.check_errors(c1)
+    d = lambda k: float(c1[k].sum() - c0[k].sum())
+    stored = float(env.replay_counts()[0].sum())
+    (steps, hops, stored), (dt,) = _reduce(dist, torch, world, [d("env_steps"), d("packet_hops"), stored], [dt])
+    env.close()
+    return {"topology": topo, "envs_per_gpu": envs, "total_envs": envs * world, "load_factor": load_factor,
+            "agent": "dqn_buffer on the device (Q-network forward + eps-greedy argmin per step), pingAsObs=%d" % cfg.pingAsObs,
+            "engine": "event-serial (k_advance, Gym mode)", "gym_calls": calls, "agent_steps_per_s": steps / dt,
+            "packet_hops_per_s": hops / dt, "replay_rows_stored": int(stored)}
+
+def leg_learner(torch, dist, rank, local_rank, world, envs, iters):
+    """Data-parallel DQN training as trainer.py:45-99 runs it, on this rank's shard: collect with the device-side agents
+    -> sample from the HBM replay rings -> one gradient step per node, the ranks' gradients exchanged as ONE bucket per
+    step (NCCL all-reduce; none on one GPU) -> new weights back to the device-side agents."""
+    from prisma_b200 import learner
+    from prisma_b200.env import BatchedRoutingEnv
+    cfg = workload_cfg(envs, 60.0, load_factor=1.1)
+    cfg.agent_type = "dqn_buffer"
+    arrays = cfg.load()
+    env = BatchedRoutingEnv(cfg, device=local_rank, arrays=arrays, env_id_base=rank * envs)
+    u2o = {int(u): i for i, u in enumerate(env.overlay_to_underlay)}
+    neigh = [[u2o[int(u)] for u in nb] for nb in env.neighbors]
+    L = learner.DQNLearner(neigh, lr=1e-3, seed=2, device="cuda:%d" % local_rank)      # same seed: same initial weights
+    env.qnet_load(L.weights())
+    env.replay_enable(rows_per_node=1 << 16)
+    ar_ms = []
+
+    def ar(t):
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        dist.all_reduce(t)
+        b.record()
+        ar_ms.append((a, b))
+    env.step_qnet(128, eps=0.2, seed=rank)
+    L.train_on_env(env, batch_size=512, seed=rank, world_size=world, all_reduce=ar if world > 1 else None)   # warm-up
+    torch.cuda.synchronize()
+    ar_ms.clear()
+    collect_s = train_s = 0.0
+    t_all = time.perf_counter()
+    for it in range(iters):
+        collect_s += _timed(torch, lambda: env.step_qnet(64, eps=0.2, seed=100 * rank + it))
+        t0 = time.perf_counter()
+        L.train_on_env(env, batch_size=512, seed=1000 * rank + it, world_size=world, all_reduce=ar if world > 1 else None)
+        torch.cuda.synchronize()
+        train_s += time.perf_counter() - t0
+    wall = time.perf_counter() - t_all
+    env.check_errors()
+    w = L.W.detach()
+    same = True
+    if world > 1:
+        ref = w.clone()
+        dist.broadcast(ref, 0)
+        flag = torch.tensor([1.0 if torch.equal(w, ref) else 0.0], device="cuda")
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+        same = bool(flag.item() == 1.0)
+    ar_mean = sum(a.elapsed_time(b) for a, b in ar_ms) / max(len(ar_ms), 1)
+    (_,), (wall, train_s, collect_s, ar_mean) = _reduce(dist, torch, world, [0.0], [wall, train_s, collect_s, ar_mean])
+    env.close()
+    return {"what": "collect 64 Gym steps per environment (device-side dqn_buffer agents) -> sample 512 rows per node from the "
+                    "HBM rings -> one Adam step per node (PyTorch autograd, library code) -> weights back to the device",
+            "envs_per_gpu": envs, "iterations": iters, "training_steps_per_s": iters / wall,
+            "train_step_ms": 1000.0 * train_s / iters, "collect_ms": 1000.0 * collect_s / iters,
+            "allreduce_bytes": int((w.numel() + L.m) * 4) if world > 1 else 0, "allreduce_ms": ar_mean if world > 1 else 0.0,
+            "allreduce_share_of_train_step": (ar_mean / (1000.0 * train_s / iters)) if world > 1 else 0.0,
+            "backend": "nccl" if world > 1 else "none (one GPU)", "weights_identical_across_ranks": same}
+
+
+def secondary_legs(args, torch, dist, rank, local_rank, world, peak):
+    """BASELINE.json configs[2], [3], [4] (this rank's share of each, 1-GPU sized at --gpus 1) and the learner."""
+    out = {}
+    # configs[3]: GEANT-scale 23-node underlay, load sweep, 64k envs over 8 GPUs = 8192 per GPU
+    out["c3_geant_load_sweep"] = [leg_table_run(torch, dist, rank, local_rank, world, "geant", args.c3_envs, lf, 30, 4, peak)
+                                  for lf in (0.5, 0.9, 1.5)]
+    # configs[2]: overlay + map_overlay with dynamic underlay traffic, dqn agents on the device, pingAsObs=1, 16k envs
+    out["c2_overlay_dqn_pingobs"] = leg_device_agents(torch, dist, rank, local_rank, world, "overlay_full_mesh_3n_abilene",
+                                                      args.c2_envs, 0.9, 256, peak, extra={"pingAsObs": 1})
+    # configs[4]: 100-node random underlay, 4-packet buffers (drop-heavy), control packets (train=1, NN signalling)
+    c5 = {"max_out_buffer_size": 2168, "train": 1, "signaling_type": "NN", "agent_type": "dqn_buffer"}
+    out["c5_synthetic100_drop_heavy"] = leg_table_run(torch, dist, rank, local_rank, world, "synthetic100", args.c5_envs, 1.3,
+                                                      2, 2, peak, extra=c5)
+    out["c5_synthetic100_drop_heavy"]["note"] = ("1M envs over 8 GPUs = 131072 per GPU; measured at %d per GPU (state: see "
+                                                 "DESIGN.md); table agent, control packets on" % args.c5_envs)
+    out["learner"] = leg_learner(torch, dist, rank, local_rank, world, 1024, args.learner_iters)
+    return out
+
+
+# ------------------------------------------------------------------------------------------------
 # this repo's arm
 # ------------------------------------------------------------------------------------------------
 
@@ -244,6 +407,11 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--gym-steps", type=int, default=512, dest="gym_steps",
                     help="iterations of the supplementary Gym-mode leg with device-side dqn_buffer agents (0 = skip)")
+    ap.add_argument("--no-secondary", action="store_true", help="skip the legs on BASELINE.json configs[2..4] and the learner")
+    ap.add_argument("--c3-envs", type=int, default=8192, dest="c3_envs")
+    ap.add_argument("--c2-envs", type=int, default=16384, dest="c2_envs")
+    ap.add_argument("--c5-envs", type=int, default=4096, dest="c5_envs")
+    ap.add_argument("--learner-iters", type=int, default=8, dest="learner_iters")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
@@ -385,14 +553,21 @@ def main():
                "what": "prb_step_qnet: every environment takes `calls` Gym steps; its warp evaluates the dqn_buffer Q-network "
                        "(forward + eps-greedy argmin) for each step inside k_advance; records and actions never leave the GPU"}
 
+    # ---- the other BASELINE.json configurations and the learner's gradient exchange (all ranks take part) ----
+    secondary = None
+    if not args.no_secondary:
+        env.close()
+        env = None
+        secondary = secondary_legs(args, torch, dist, rank, local_rank, world, measured_peak_gbs()[0])
+
     # ---- reductions over ranks ----
     if world > 1:
         t = torch.tensor([elapsed, e2e_wall], dtype=torch.float64, device="cuda")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         elapsed, e2e_wall = float(t[0]), float(t[1])
-        s = torch.tensor([d_hops, d_steps, d_events, e2e_hops, launches], dtype=torch.int64, device="cuda")
+        s = torch.tensor([d_hops, d_steps, d_events, e2e_hops, launches, handovers, e2e_handovers], dtype=torch.int64, device="cuda")
         dist.all_reduce(s, op=dist.ReduceOp.SUM)
-        d_hops, d_steps, d_events, e2e_hops, launches = (int(x) for x in s)
+        d_hops, d_steps, d_events, e2e_hops, launches, handovers, e2e_handovers = (int(x) for x in s)
 
     if rank == 0:
         peak, peak_src = measured_peak_gbs()
@@ -426,6 +601,8 @@ def main():
             line["engine"] = {"name": "event-serial (k_advance)"}
         if gym:
             line["gym_dqn_buffer"] = gym
+        if secondary:
+            line["configs"] = secondary
         if world == 1 and not args.no_cpu_baseline:
             cores = os.cpu_count() or 1
             hc = sc_ = dt = 0.0
@@ -439,7 +616,8 @@ def main():
                                               "workload, sp table agent in-process, %.1f s wall" % (cores, episodes,
                                                                                                    args.cpu_sim_time, dt)}
         print(json.dumps(line), flush=True)
-    env.close()
+    if env is not None:
+        env.close()
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
