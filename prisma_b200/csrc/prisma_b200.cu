@@ -1701,7 +1701,8 @@ prb_run (prb_env *env, int64_t until_ns)
   /* AUTO: only while an environment's state fits shared memory for the launch — beyond that (hundreds of flows
    * per node: the 100-node fixture holds 159 KB per environment) the event-serial engine is the faster one
    * (measured on B200, 4096 environments: 1.1e8 against 4.1e7 packet-hops/s) */
-  bool par_fits = (size_t) env->dps.pblob_bytes + 1024 <= (size_t) env->max_smem;
+  /* "fits": at least four environments resident per SM (one per block with ~150 KB of flow timers is one warp per SM) */
+  bool par_fits = 4 * ((size_t) env->dps.pblob_bytes + 1024) <= (size_t) env->smem_per_sm;
   bool want_par = env->engine_mode == PRB_ENGINE_PARALLEL
                   || (env->engine_mode == PRB_ENGINE_AUTO && env->pm.supported && par_fits && par_policy && !env->log_on);
   if (env->engine_active == PRB_ENGINE_SERIAL) want_par = false;
