@@ -229,6 +229,13 @@ int prb_step_host (prb_env *env, const int32_t *actions, prb_step_rec *out);
 int64_t prb_qnet_num_floats (prb_env *env);
 int prb_qnet_load (prb_env *env, const float *weights, int64_t n_floats);
 int prb_qnet_act (prb_env *env, const prb_step_rec *rec_dev, int32_t *actions_dev, float *q_out_dev, float eps, uint64_t seed);
+/* How the Q-networks are evaluated (DQN_AGENT.step, prisma/source/learner.py:142-159; the reference hands the batch to
+ * TensorFlow / cuBLAS).  FUSED (default): inside the simulator kernel, one warp per environment, fp32 (prb_step_qnet is one
+ * launch).  WARP: the same arithmetic as its own kernel (prb_qnet_act).  MMA: the pending decisions of all environments are
+ * bucketed by node and evaluated in tiles of 16 on the tensor cores (mma.sync TF32 with split operands, fp32 accumulate:
+ * Q-values within 2e-5 of the fp32 path); prb_step_qnet then issues three launches per step.  Also: PRB_QNET_MODE=mma|warp. */
+enum { PRB_QNET_FUSED = 0, PRB_QNET_WARP = 1, PRB_QNET_MMA = 2 };
+int prb_qnet_set_mode (prb_env *env, int mode);
 int prb_step_qnet (prb_env *env, int32_t n_steps, float eps, uint64_t seed, prb_step_rec *out_dev);
 
 /* ---- replay buffers in HBM (prisma/source/replay_buffer.py:12-86; producers forwarder.py:135-161,214-244,352-379) ----

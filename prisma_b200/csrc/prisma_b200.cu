@@ -335,6 +335,243 @@ k_replay_record (const __grid_constant__ Static st, const ReplayArgs ra, const p
   replay_record_one (st, ra, e, &rec[e], actions[e], ra.target_mode && ra.tmin ? ra.tmin[e] : INFINITY);
 }
 
+/* ------------------------------------------------------------------------------------------------
+ * Batched Q-network forward on the tensor cores (DQN_buffer_model, prisma/source/models.py:258-306, and
+ * DQN_AGENT.step, prisma/source/learner.py:142-159, for the pending decisions of ALL environments at once).
+ * k_qnet_bucket sorts the pending decisions by overlay node (one atomic per decision); k_qnet_mma gives every warp a
+ * tile of 16 decisions of ONE node and evaluates Dense64 -> Dense64 -> Dense(k) as mma.sync.m16n8k8 TF32 tiles with fp32
+ * accumulators.  Every product is taken three times on split operands (x = hi + lo, hi * hi + lo * hi + hi * lo: "3xTF32"),
+ * which brings the result back to fp32 accuracy (the reference's TensorFlow runs these layers in fp32 or TF32 depending on
+ * the GPU; the fused fp32 path of k_advance stays the numerical yardstick of the tests).  Why mma.sync and not
+ * tcgen05: one call is 70 MFLOP (4096 decisions x 17.7 kFLOP) in tiles of 16 x 64 x 64 — a tcgen05 tile is at least
+ * 64 rows of one node, TMEM allocation and descriptor set-up would outlast the arithmetic, and the kernel is bound by the
+ * launch and by the latency of the weight loads either way.  The destination branch (a row lookup) and the buffer branch
+ * (LayerNorm + Dense of k <= 16 inputs) are fp32 FMAs.  After the last layer one lane per decision takes the argmin /
+ * eps-greedy draw (same Philox stream as qnet_forward), writes the action and feeds the replay rings.
+ * ---------------------------------------------------------------------------------------------- */
+struct QBatchArgs
+{
+  int32_t *count;          /* [2][M + 1]: decisions per node of this call (parity: the other half is cleared for the next call) */
+  int32_t *perm;           /* [M][E]: environment indices per node */
+  int parity;
+};
+
+__global__ void
+k_qnet_bucket (const __grid_constant__ Static st, const ReplayArgs ra, const prb_step_rec *rec, int32_t *actions, QBatchArgs qb)
+{
+  const int e = blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= st.E) return;
+  const prb_step_rec *r = &rec[e];
+  if (!r->valid || !r->need_action)
+    {
+      actions[e] = 0;
+      /* a step without a decision (the packet arrived) still closes the previous node's transition */
+      if (ra.rows) replay_record_one (st, ra, e, r, 0, INFINITY);
+      return;
+    }
+  const int m = r->overlay;
+  const int pos = atomicAdd (&qb.count[qb.parity * (st.M + 1) + m], 1);
+  qb.perm[(size_t) m * st.E + pos] = e;
+}
+
+__device__ __forceinline__ uint32_t
+tf32_hi (float x)
+{
+  uint32_t r;
+  asm ("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(x));
+  return r;
+}
+
+__device__ __forceinline__ void
+mma_tf32 (float (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1)
+{
+  asm volatile ("mma.sync.aligned.m16n8k8.row.col.f32.tf32.tf32.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+                : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+
+/* c += a * b with a (16 x 8 of the activations) and b (8 x 8 of the weights) split into TF32 hi + lo parts */
+__device__ __forceinline__ void
+mma_3xtf32 (float (&c)[4], const float (&a)[4], float b0, float b1)
+{
+  uint32_t ah[4], al[4];
+#pragma unroll
+  for (int i = 0; i < 4; i++)
+    {
+      ah[i] = tf32_hi (a[i]);
+      al[i] = tf32_hi (a[i] - __uint_as_float (ah[i]));
+    }
+  const uint32_t bh0 = tf32_hi (b0), bh1 = tf32_hi (b1);
+  const uint32_t bl0 = tf32_hi (b0 - __uint_as_float (bh0)), bl1 = tf32_hi (b1 - __uint_as_float (bh1));
+  mma_tf32 (c, al, bh0, bh1);
+  mma_tf32 (c, ah, bl0, bl1);
+  mma_tf32 (c, ah, bh0, bh1);
+}
+
+constexpr int QM_WARPS = 2;          /* warps (tiles of 16 decisions) per block */
+constexpr int QM_LD = QH2 + 4;       /* row pitch of the activation tile in shared memory (floats): conflict-free fragment reads */
+
+/* one Dense(64 -> 64) + elu on a 16-row tile: activations in act (shared, [16][QM_LD]), result written back in place */
+__device__ __forceinline__ void
+qm_dense64 (float *act, const float *__restrict__ w, const float *__restrict__ b, int g, int t)
+{
+  float c[8][4];
+#pragma unroll
+  for (int nt = 0; nt < 8; nt++)
+    {
+      const float b0 = b[nt * 8 + 2 * t], b1 = b[nt * 8 + 2 * t + 1];
+      c[nt][0] = b0; c[nt][1] = b1; c[nt][2] = b0; c[nt][3] = b1;
+    }
+#pragma unroll
+  for (int kk = 0; kk < 8; kk++)
+    {
+      float a[4];
+      a[0] = act[g * QM_LD + kk * 8 + t];
+      a[1] = act[(g + 8) * QM_LD + kk * 8 + t];
+      a[2] = act[g * QM_LD + kk * 8 + t + 4];
+      a[3] = act[(g + 8) * QM_LD + kk * 8 + t + 4];
+#pragma unroll
+      for (int nt = 0; nt < 8; nt++)
+        mma_3xtf32 (c[nt], a, __ldg (&w[(size_t) (kk * 8 + t) * QH2 + nt * 8 + g]), __ldg (&w[(size_t) (kk * 8 + t + 4) * QH2 + nt * 8 + g]));
+    }
+  __syncwarp ();
+#pragma unroll
+  for (int nt = 0; nt < 8; nt++)
+    {
+      act[g * QM_LD + nt * 8 + 2 * t] = elu_ (c[nt][0]);
+      act[g * QM_LD + nt * 8 + 2 * t + 1] = elu_ (c[nt][1]);
+      act[(g + 8) * QM_LD + nt * 8 + 2 * t] = elu_ (c[nt][2]);
+      act[(g + 8) * QM_LD + nt * 8 + 2 * t + 1] = elu_ (c[nt][3]);
+    }
+  __syncwarp ();
+}
+
+__global__ void __launch_bounds__ (QM_WARPS * 32)
+k_qnet_mma (const __grid_constant__ Static st, const ReplayArgs ra, const float *__restrict__ wts, const prb_step_rec *rec,
+            int32_t *actions, float *q_out, float eps, uint64_t seed, uint64_t step, float *tmin_out, QBatchArgs qb)
+{
+  __shared__ __align__ (16) float s_act[QM_WARPS][16 * QM_LD];
+  __shared__ float s_q[QM_WARPS][16 * PRB_MAX_K];
+  __shared__ int s_env[QM_WARPS][16];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int g = lane >> 2, t = lane & 3;
+  const int M = st.M, K = st.K;
+  const int32_t *count = qb.count + qb.parity * (M + 1);
+  /* the other half of the counters is the next call's: clear it */
+  if (blockIdx.x == 0 && threadIdx.x <= M) qb.count[(qb.parity ^ 1) * (M + 1) + threadIdx.x] = 0;
+  /* which node, which 16 decisions of it */
+  int tile = blockIdx.x * QM_WARPS + warp, m = 0, n_m = 0;
+  for (; m < M; m++)
+    {
+      n_m = count[m];
+      const int tiles = (n_m + 15) >> 4;
+      if (tile < tiles) break;
+      tile -= tiles;
+    }
+  if (m >= M) return;
+  const int row0 = tile * 16;
+  const int k = st.agent_k[m];
+  const float *W = wts + (size_t) m * qnet_floats_per_node (M, K);
+  const float *w_dst = W, *b_dst = w_dst + (size_t) M * QH1, *w_buf = b_dst + QH1, *b_buf = w_buf + (size_t) K * QH1;
+  const float *w1 = b_buf + QH1, *b1 = w1 + 2 * QH1 * QH2, *w2 = b1 + QH2, *b2 = w2 + QH2 * QH2, *w3 = b2 + QH2, *b3 = w3 + (size_t) QH2 * K;
+  float *act = s_act[warp];
+  if (lane < 16) s_env[warp][lane] = row0 + lane < n_m ? qb.perm[(size_t) m * st.E + row0 + lane] : -1;
+  __syncwarp ();
+  /* input branches, fp32: lane j owns unit j of both; the k queue values are normalised by every lane alike */
+  for (int r = 0; r < 16; r++)
+    {
+      const int e = s_env[warp][r];
+      float hd = 0.0f, hb = 0.0f;
+      if (e >= 0)
+        {
+          const prb_step_rec *rc = &rec[e];
+          int dst = rc->obs[0];
+          dst = dst < 0 ? 0 : (dst >= M ? M - 1 : dst);
+          hd = elu_ (w_dst[(size_t) dst * QH1 + lane] + b_dst[lane]);
+          float sum = 0.0f;
+          for (int i = 0; i < k; i++) sum += (float) (uint32_t) rc->obs[1 + i];
+          const float mean = sum / (float) k;
+          float var = 0.0f;
+          for (int i = 0; i < k; i++)
+            {
+              const float dv = (float) (uint32_t) rc->obs[1 + i] - mean;
+              var += dv * dv;
+            }
+          const float rs = rsqrtf (var / (float) k + 1e-3f);
+          float a = b_buf[lane];
+          for (int i = 0; i < k; i++) a = fmaf (((float) (uint32_t) rc->obs[1 + i] - mean) * rs, w_buf[(size_t) i * QH1 + lane], a);
+          hb = elu_ (a);
+        }
+      act[r * QM_LD + lane] = hd;
+      act[r * QM_LD + QH1 + lane] = hb;
+    }
+  __syncwarp ();
+  qm_dense64 (act, w1, b1, g, t);
+  qm_dense64 (act, w2, b2, g, t);
+  /* Dense(k): columns >= k are padding */
+  for (int nt = 0; nt * 8 < K; nt++)
+    {
+      float c[4];
+      const int n0 = nt * 8 + 2 * t, n1 = n0 + 1;
+      c[0] = c[2] = n0 < k ? b3[n0] : 0.0f;
+      c[1] = c[3] = n1 < k ? b3[n1] : 0.0f;
+      const int nb = nt * 8 + g;
+#pragma unroll
+      for (int kk = 0; kk < 8; kk++)
+        {
+          float a[4];
+          a[0] = act[g * QM_LD + kk * 8 + t];
+          a[1] = act[(g + 8) * QM_LD + kk * 8 + t];
+          a[2] = act[g * QM_LD + kk * 8 + t + 4];
+          a[3] = act[(g + 8) * QM_LD + kk * 8 + t + 4];
+          mma_3xtf32 (c, a, nb < k ? __ldg (&w3[(size_t) (kk * 8 + t) * K + nb]) : 0.0f,
+                      nb < k ? __ldg (&w3[(size_t) (kk * 8 + t + 4) * K + nb]) : 0.0f);
+        }
+      if (n0 < K)
+        {
+          s_q[warp][g * PRB_MAX_K + n0] = n0 < k ? elu_ (c[0]) : 0.0f;
+          s_q[warp][(g + 8) * PRB_MAX_K + n0] = n0 < k ? elu_ (c[2]) : 0.0f;
+        }
+      if (n1 < K)
+        {
+          s_q[warp][g * PRB_MAX_K + n1] = n1 < k ? elu_ (c[1]) : 0.0f;
+          s_q[warp][(g + 8) * PRB_MAX_K + n1] = n1 < k ? elu_ (c[3]) : 0.0f;
+        }
+    }
+  __syncwarp ();
+  /* one lane per decision: argmin (first index on equal values, tf.argmin), eps-greedy, replay bookkeeping */
+  if (lane < 16 && s_env[warp][lane] >= 0)
+    {
+      const int e = s_env[warp][lane];
+      const prb_step_rec *rc = &rec[e];
+      const float *q = &s_q[warp][lane * PRB_MAX_K];
+      float bq = INFINITY, tq = INFINITY;
+      int action = 0;
+      for (int i = 0; i < k; i++)
+        {
+          if (q[i] < bq)
+            {
+              bq = q[i]; action = i;
+            }
+          if ((int) st.agent_nbr[(size_t) m * K + i] != rc->prev_node) tq = fminf (tq, q[i]);
+        }
+      if (q_out)
+        for (int i = 0; i < K; i++) q_out[(size_t) e * K + i] = q[i];
+      if (eps > 0.0f)
+        {
+          const uint64_t eid = st.env_id_base + (uint64_t) e;
+          uint32_t rr[4];
+          philox4x32 ((uint32_t) eid, (uint32_t) (eid >> 32), (uint32_t) step, (uint32_t) (step >> 32), (uint32_t) seed,
+                      (uint32_t) (seed >> 32) ^ 0x51DEu, rr);
+          const float u = (float) (rr[0] >> 8) * (1.0f / 16777216.0f);
+          if (u < eps) action = (int) (rr[1] % (uint32_t) k);
+        }
+      actions[e] = action;
+      if (tmin_out) tmin_out[e] = tq;
+      if (ra.rows) replay_record_one (st, ra, e, rc, action, ra.target_mode ? tq : INFINITY);
+    }
+}
+
 /* priority of row idx of a node: (gradient step of the row / latest step seen for its action) ^ alpha */
 __device__ __forceinline__ float
 replay_priority (const ReplayArgs &ra, int node, unsigned long long idx, int ow, int K)
@@ -963,6 +1200,9 @@ struct prb_env
   float *d_qw = nullptr;
   uint64_t q_step = 0;
   bool qnet_unfused = false;   /* PRB_QNET_UNFUSED=1: prb_step_qnet as a sequence of launches (A/B tests) */
+  int qnet_mode = PRB_QNET_FUSED;  /* prb_qnet_set_mode */
+  int32_t *d_qcount = nullptr, *d_qperm = nullptr;
+  int q_parity = 0;
   /* replay buffers */
   ReplayArgs rp = {};
   uint64_t rp_call = 0;
@@ -1244,6 +1484,7 @@ prb_destroy (prb_env *env)
   cudaFree (env->d_scratch);
   cudaFree (env->d_ptables); cudaFree (env->d_pblob0); cudaFree (env->d_pblobs); cudaFree (env->d_rings);
   cudaFree (env->d_tr_prev); cudaFree (env->d_round_stats); cudaFree (env->d_qw); cudaFree (env->d_tied_list); cudaFree (env->d_tied_flags); cudaFree (env->d_pol_replay);
+  cudaFree (env->d_qcount); cudaFree (env->d_qperm);
   if (env->rp_ev0) { cudaEventDestroy (env->rp_ev0); cudaEventDestroy (env->rp_ev1); }
   cudaFree (env->rp.rows); cudaFree (env->rp.cursor); cudaFree (env->rp.pending); cudaFree (env->rp.tmin);
   cudaFree (env->rp.row_gstep); cudaFree (env->rp.latest); cudaFree (env->rp.psum);
@@ -1271,6 +1512,8 @@ prb_create (const prb_config *cfg, int device, void *cuda_stream, prb_env **out)
   env->stream = (cudaStream_t) cuda_stream;
   env->G = cfg->lanes_per_env > 0 ? cfg->lanes_per_env : 32;
   env->qnet_unfused = getenv ("PRB_QNET_UNFUSED") != nullptr;
+  if (const char *qm = getenv ("PRB_QNET_MODE"))
+    env->qnet_mode = !strcmp (qm, "mma") ? PRB_QNET_MMA : (!strcmp (qm, "warp") ? PRB_QNET_WARP : PRB_QNET_FUSED);
   if (env->G != 32 && env->G != 16 && env->G != 8)
     {
       delete env;
@@ -1776,6 +2019,42 @@ prb_qnet_load (prb_env *env, const float *weights, int64_t n_floats)
   return PRB_OK;
 }
 
+/* the pending decisions of all environments, bucketed by node and evaluated on the tensor cores (k_qnet_mma);
+ * ra.rows != null: the replay bookkeeping of every record happens here too */
+static int
+qnet_act_batched (prb_env *env, const prb_step_rec *rec_dev, int32_t *actions_dev, float *q_out_dev, float eps, uint64_t seed,
+                  const ReplayArgs &ra)
+{
+  const Static &st = env->dst;
+  if (!env->d_qcount)
+    {
+      CUDA_TRY (cudaMalloc (&env->d_qcount, sizeof (int32_t) * 2 * (size_t) (st.M + 1)));
+      CUDA_TRY (cudaMalloc (&env->d_qperm, sizeof (int32_t) * (size_t) st.M * (size_t) st.E));
+      CUDA_TRY (cudaMemsetAsync (env->d_qcount, 0, sizeof (int32_t) * 2 * (size_t) (st.M + 1), env->stream));
+      env->q_parity = 0;
+    }
+  QBatchArgs qb;
+  qb.count = env->d_qcount; qb.perm = env->d_qperm; qb.parity = env->q_parity;
+  env->q_parity ^= 1;
+  k_qnet_bucket<<<(st.E + 127) / 128, 128, 0, env->stream>>> (st, ra, rec_dev, actions_dev, qb);
+  CUDA_TRY (cudaGetLastError ());
+  const int tiles = st.E / 16 + st.M + 1;
+  k_qnet_mma<<<(tiles + QM_WARPS - 1) / QM_WARPS, QM_WARPS * 32, 0, env->stream>>> (st, ra, env->d_qw, rec_dev, actions_dev, q_out_dev, eps, seed,
+                                                                                    env->q_step++, env->rp.target_mode ? env->rp.tmin : nullptr, qb);
+  CUDA_TRY (cudaGetLastError ());
+  env->launches += 2;
+  return PRB_OK;
+}
+
+int
+prb_qnet_set_mode (prb_env *env, int mode)
+{
+  if (!env) return fail (PRB_EINVAL, "null handle");
+  if (mode < PRB_QNET_FUSED || mode > PRB_QNET_MMA) return fail (PRB_EINVAL, "unknown Q-network mode");
+  env->qnet_mode = mode;
+  return PRB_OK;
+}
+
 int
 prb_qnet_act (prb_env *env, const prb_step_rec *rec_dev, int32_t *actions_dev, float *q_out_dev, float eps, uint64_t seed)
 {
@@ -1783,6 +2062,7 @@ prb_qnet_act (prb_env *env, const prb_step_rec *rec_dev, int32_t *actions_dev, f
   if (!env->d_qw) return fail (PRB_ESTATE, "no Q-network loaded (prb_qnet_load)");
   CUDA_TRY (cudaSetDevice (env->device));
   const Static &st = env->dst;
+  if (env->qnet_mode == PRB_QNET_MMA) return qnet_act_batched (env, rec_dev, actions_dev, q_out_dev, eps, seed, ReplayArgs ());
   k_qnet_act<<<(st.E + 3) / 4, 128, 0, env->stream>>> (st, env->d_qw, rec_dev, actions_dev, q_out_dev, eps, seed, env->q_step++,
                                                        env->rp.target_mode ? env->rp.tmin : nullptr);
   CUDA_TRY (cudaGetLastError ());
@@ -1970,7 +2250,19 @@ prb_step_qnet (prb_env *env, int32_t n_steps, float eps, uint64_t seed, prb_step
   if (!env || !out_dev || n_steps < 1) return fail (PRB_EINVAL, "bad argument");
   if (!env->d_qw) return fail (PRB_ESTATE, "no Q-network loaded (prb_qnet_load)");
   int rc = PRB_OK;
-  if (env->G == 32 && !env->qnet_unfused)
+  if (env->qnet_mode == PRB_QNET_MMA)
+    {
+      /* two launches + the simulator's per step: decisions of all environments bucketed by node, Q-networks on the
+       * tensor cores, replay bookkeeping in the same kernel */
+      CUDA_TRY (cudaSetDevice (env->device));
+      for (int i = 0; i < n_steps && rc == PRB_OK; i++)
+        {
+          rc = qnet_act_batched (env, out_dev, env->d_actions, nullptr, eps, seed, env->rp);
+          if (rc == PRB_OK) rc = prb_step (env, env->d_actions, out_dev);
+        }
+      return rc;
+    }
+  if (env->G == 32 && !env->qnet_unfused && env->qnet_mode == PRB_QNET_FUSED)
     {
       /* one launch: every warp answers the steps of its environment itself (k_advance, gym mode) */
       CUDA_TRY (cudaSetDevice (env->device));

@@ -214,6 +214,11 @@ class BatchedRoutingEnv:
         w = np.ascontiguousarray(weights, dtype=np.float32).ravel()
         _abi.check(self.lib.prb_qnet_load(self.h, w.ctypes.data_as(C.c_void_p), w.size))
 
+    def qnet_set_mode(self, mode: str = "fused"):
+        """'fused': Q-networks inside the simulator kernel (one warp per environment, fp32); 'warp': the same as its own
+        kernel; 'mma': decisions of all environments bucketed by node, tiles of 16 on the tensor cores."""
+        _abi.check(self.lib.prb_qnet_set_mode(self.h, {"fused": 0, "warp": 1, "mma": 2}[mode]))
+
     def qnet_act(self, eps: float = 0.0, seed: int = 0, actions=None, q_out=None):
         """argmin-Q actions (eps-greedy) for the records of the last `step`; returns the int32 [E] cuda tensor."""
         torch = self._torch
