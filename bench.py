@@ -364,6 +364,33 @@ def leg_learner(torch, dist, rank, local_rank, world, envs, iters):
             "backend": "nccl" if world > 1 else "none (one GPU)", "weights_identical_across_ranks": same}
 
 
+def leg_qnet_forward(torch, local_rank, envs):
+    """The Q-network forward of all pending decisions as its own call (prb_qnet_act): one warp per environment in fp32
+    (k_qnet_act) against the node-bucketed tensor-core kernel (k_qnet_bucket + k_qnet_mma, mma.sync TF32 split operands)."""
+    from prisma_b200 import qnet
+    from prisma_b200.env import BatchedRoutingEnv
+    cfg = workload_cfg(envs, 60.0)
+    cfg.agent_type = "dqn_buffer"
+    arrays = cfg.load()
+    env = BatchedRoutingEnv(cfg, device=local_rank, arrays=arrays)
+    deg = [len(n) for n in env.neighbors]
+    env.qnet_load(qnet.pack_weights(qnet.init_weights(len(deg), deg, max(deg), seed=1)))
+    env.step_qnet(64, eps=0.05, seed=1)
+    rec = env.last.numpy()
+    pending = int(((rec["valid"] != 0) & (rec["need_action"] != 0)).sum())
+    out = {"envs": envs, "pending_decisions": pending, "flop_per_decision": 17700}
+    for mode in ("warp", "mma"):
+        env.qnet_set_mode(mode)
+        env.qnet_act()
+
+        def go():
+            for _ in range(50):
+                env.qnet_act()
+        out["%s_us_per_call" % mode] = 1e6 * _timed(torch, go) / 50
+    env.close()
+    return out
+
+
 def secondary_legs(args, torch, dist, rank, local_rank, world, peak):
     """BASELINE.json configs[2], [3], [4] (this rank's share of each, 1-GPU sized at --gpus 1) and the learner."""
     out = {}
@@ -379,6 +406,8 @@ def secondary_legs(args, torch, dist, rank, local_rank, world, peak):
                                                       2, 2, peak, extra=c5)
     out["c5_synthetic100_drop_heavy"]["note"] = ("1M envs over 8 GPUs = 131072 per GPU; measured at %d per GPU (state: see "
                                                  "DESIGN.md); table agent, control packets on" % args.c5_envs)
+    if rank == 0:
+        out["qnet_forward"] = leg_qnet_forward(torch, local_rank, 65536)
     out["learner"] = leg_learner(torch, dist, rank, local_rank, world, 1024, args.learner_iters)
     return out
 
