@@ -1,7 +1,7 @@
 #!/bin/bash
 # usage: ab.sh libA.so libB.so ...: bench each library 2x (alternating), print hops/s
 for rep in 1 2; do for lib in "$@"; do
-  PRB_LIB=$PWD/$lib timeout 300 python bench.py --steps 5 --warmup 3 --no-cpu-baseline --gym-steps 0 > gpurun_out/ab_tmp.log 2>&1
+  PRB_LIB=$PWD/$lib timeout 300 python bench.py --steps 5 --warmup 3 --no-cpu-baseline --gym-steps 0 --no-secondary > gpurun_out/ab_tmp.log 2>&1
   python - <<PY
 import json
 try:

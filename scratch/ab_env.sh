@@ -1,7 +1,7 @@
 #!/bin/bash
 # usage: ab_env.sh VAR "v1 v2 ...": bench with VAR=v for each value, twice
 for rep in 1 2; do for v in $2; do
-  env $1=$v timeout 300 python bench.py --steps 5 --warmup 3 --no-cpu-baseline --gym-steps 0 > gpurun_out/ab_tmp.log 2>&1
+  env $1=$v timeout 300 python bench.py --steps 5 --warmup 3 --no-cpu-baseline --gym-steps 0 --no-secondary > gpurun_out/ab_tmp.log 2>&1
   python - <<PY
 import json
 try:
