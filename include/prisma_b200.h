@@ -273,6 +273,29 @@ int prb_replay_read (prb_env *env, int32_t node, float *rows_host, int64_t max_r
 int prb_replay_sample (prb_env *env, int32_t node, int32_t batch, uint64_t seed, float *obs_dev, int32_t *action_dev,
                        float *reward_dev, float *next_obs_dev, float *done_dev);
 
+/* ---- the DQN learner's gradient step on the device (dqn_buffer agents) ----
+ * Replaces DQN_AGENT.train / get_neighbor_target_value (prisma/source/learner.py:162-189,231-255) and Trainer.step
+ * (prisma/source/trainer.py:45-99): TD targets through the neighbours' target networks (or the stored targets with `target`
+ * signalling, trainer.py:52-55), Huber loss, Adam with Keras' defaults, one optimiser state per node.  The online weights are
+ * the ones prb_qnet_load installed: training updates them in place, so the device-side agents act on the new weights at once.
+ * prb_replay_sample_all: ReplayBuffer.sample for every node at once into [M][batch][...] device arrays (active_dev[m] = 1 when
+ *   node m holds at least min_rows transitions, trainer.py:41; weights_dev may be NULL).
+ * prb_learner_grad: gradients of every active node into bucket_dev [M * P floats][M activity flags] — ONE buffer, the unit of the
+ *   data-parallel exchange (all-reduce it over the ranks, e.g. NCCL, then prb_learner_apply with world_size);
+ *   td_mse_host [M] (may be NULL): mean squared TD error per node.
+ * prb_learner_apply: Adam on the nodes whose activity count is positive.  prb_learner_sync_targets: update_target /
+ *   sync_neighbor_target_q_network (learner.py:190-199,256-270).  prb_learner_read: 0 weights, 1 target weights, 2 exp_avg,
+ *   3 exp_avg_sq ([M * P] floats), 4 steps ([M]). */
+int prb_replay_sample_all (prb_env *env, int32_t batch, uint64_t seed, int64_t min_rows, float *obs_dev, int32_t *action_dev,
+                           float *reward_dev, float *next_obs_dev, float *done_dev, float *weights_dev, float *active_dev);
+int prb_learner_init (prb_env *env, float lr, float gamma, float beta1, float beta2, float adam_eps, int target_mode);
+int prb_learner_sync_targets (prb_env *env);
+int prb_learner_grad (prb_env *env, int32_t batch, const float *obs_dev, const int32_t *action_dev, const float *reward_dev,
+                      const float *next_obs_dev, const float *done_dev, const float *weights_dev, const float *active_dev,
+                      float *bucket_dev, float *td_mse_host);
+int prb_learner_apply (prb_env *env, const float *bucket_dev, int32_t world_size);
+int prb_learner_read (prb_env *env, int32_t which, float *out_host, int64_t n_floats);
+
 int prb_counters_host (prb_env *env, prb_counters *out /* [E] */);
 int prb_counters_dev (prb_env *env, prb_counters *out_dev /* [E] device */);
 int prb_queue_bytes (prb_env *env, int32_t e, int32_t *out /* [L] */);

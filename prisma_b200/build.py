@@ -14,7 +14,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OUT = os.path.join(HERE, "libprisma_b200.so")
 SOURCES = [os.path.join(CSRC, "prisma_b200.cu")]
-DEPS = SOURCES + [os.path.join(CSRC, "sim_core.cuh"), os.path.join(CSRC, "par_core.cuh"), os.path.join(CSRC, "model.h"),
+DEPS = SOURCES + [os.path.join(CSRC, "sim_core.cuh"), os.path.join(CSRC, "par_core.cuh"), os.path.join(CSRC, "learner_core.cuh"), os.path.join(CSRC, "model.h"),
                   os.path.join(HERE, "..", "include", "prisma_b200.h")]
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-O3", "-std=c++17", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-fmad=false",

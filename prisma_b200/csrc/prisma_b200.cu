@@ -572,6 +572,8 @@ k_qnet_mma (const __grid_constant__ Static st, const ReplayArgs ra, const float 
     }
 }
 
+#include "learner_core.cuh"
+
 /* priority of row idx of a node: (gradient step of the row / latest step seen for its action) ^ alpha */
 __device__ __forceinline__ float
 replay_priority (const ReplayArgs &ra, int node, unsigned long long idx, int ow, int K)
@@ -1203,6 +1205,10 @@ struct prb_env
   int qnet_mode = PRB_QNET_FUSED;  /* prb_qnet_set_mode */
   int32_t *d_qcount = nullptr, *d_qperm = nullptr;
   int q_parity = 0;
+  /* learner on the device (prb_learner_*): the online weights ARE d_qw */
+  float *d_lw_target = nullptr, *d_lexp = nullptr, *d_lexp_sq = nullptr, *d_lsteps = nullptr, *d_ltd = nullptr;
+  float l_lr = 1e-3f, l_gamma = 1.0f, l_b1 = 0.9f, l_b2 = 0.999f, l_eps = 1e-7f;
+  int l_target_mode = 0;
   /* replay buffers */
   ReplayArgs rp = {};
   uint64_t rp_call = 0;
@@ -1485,6 +1491,7 @@ prb_destroy (prb_env *env)
   cudaFree (env->d_ptables); cudaFree (env->d_pblob0); cudaFree (env->d_pblobs); cudaFree (env->d_rings);
   cudaFree (env->d_tr_prev); cudaFree (env->d_round_stats); cudaFree (env->d_qw); cudaFree (env->d_tied_list); cudaFree (env->d_tied_flags); cudaFree (env->d_pol_replay);
   cudaFree (env->d_qcount); cudaFree (env->d_qperm);
+  cudaFree (env->d_lw_target); cudaFree (env->d_lexp); cudaFree (env->d_lexp_sq); cudaFree (env->d_lsteps); cudaFree (env->d_ltd);
   if (env->rp_ev0) { cudaEventDestroy (env->rp_ev0); cudaEventDestroy (env->rp_ev1); }
   cudaFree (env->rp.rows); cudaFree (env->rp.cursor); cudaFree (env->rp.pending); cudaFree (env->rp.tmin);
   cudaFree (env->rp.row_gstep); cudaFree (env->rp.latest); cudaFree (env->rp.psum);
@@ -2225,6 +2232,147 @@ prb_replay_sample_weighted (prb_env *env, int32_t node, int32_t batch, uint64_t 
                                                                   reward_dev, next_obs_dev, done_dev, weights_dev, env->dst.K);
   CUDA_TRY (cudaGetLastError ());
   env->launches++;
+  return PRB_OK;
+}
+
+/* ---- learner on the device ---- */
+int
+prb_replay_sample_all (prb_env *env, int32_t batch, uint64_t seed, int64_t min_rows, float *obs_dev, int32_t *action_dev, float *reward_dev,
+                       float *next_obs_dev, float *done_dev, float *weights_dev, float *active_dev)
+{
+  if (!env || !obs_dev || !action_dev || !reward_dev || !next_obs_dev || !done_dev || !active_dev || batch < 1)
+    return fail (PRB_EINVAL, "bad argument");
+  if (!env->rp.rows) return fail (PRB_ESTATE, "replay buffers not enabled (prb_replay_enable)");
+  CUDA_TRY (cudaSetDevice (env->device));
+  const Static &st = env->dst;
+  const int ow = 1 + st.K;
+  std::vector<unsigned long long> cur ((size_t) st.M);
+  CUDA_TRY (cudaMemcpyAsync (cur.data (), env->rp.cursor, sizeof (unsigned long long) * st.M, cudaMemcpyDeviceToHost, env->stream));
+  CUDA_TRY (cudaStreamSynchronize (env->stream));
+  std::vector<float> act ((size_t) st.M, 0.0f);
+  for (int m = 0; m < st.M; m++)
+    {
+      const int64_t have = (int64_t) std::min<unsigned long long> (cur[(size_t) m], (unsigned long long) env->rp.cap);
+      if (have < std::max<int64_t> (min_rows, 1)) continue;
+      act[(size_t) m] = 1.0f;
+      const size_t o = (size_t) m * batch;
+      float *wts = weights_dev ? weights_dev + o : nullptr;
+      if (env->rp.row_gstep && wts)
+        {
+          CUDA_TRY (cudaMemsetAsync (env->rp.psum, 0, sizeof (double), env->stream));
+          k_replay_priority_sum<<<64, 256, 0, env->stream>>> (env->rp, m, ow, st.K);
+          env->launches++;
+        }
+      k_replay_sample<<<(batch + 127) / 128, 128, 0, env->stream>>> (env->rp, m, batch, ow, seed, env->rp_call, obs_dev + o * ow, action_dev + o,
+                                                                      reward_dev + o, next_obs_dev + o * ow, done_dev + o, wts, st.K);
+      CUDA_TRY (cudaGetLastError ());
+      env->launches++;
+    }
+  env->rp_call++;
+  CUDA_TRY (cudaMemcpyAsync (active_dev, act.data (), sizeof (float) * st.M, cudaMemcpyHostToDevice, env->stream));
+  CUDA_TRY (cudaStreamSynchronize (env->stream));        /* `act` leaves scope */
+  return PRB_OK;
+}
+
+int
+prb_learner_init (prb_env *env, float lr, float gamma, float beta1, float beta2, float adam_eps, int target_mode)
+{
+  if (!env) return fail (PRB_EINVAL, "null handle");
+  if (!env->d_qw) return fail (PRB_ESTATE, "no Q-network loaded (prb_qnet_load): the learner trains the loaded weights in place");
+  CUDA_TRY (cudaSetDevice (env->device));
+  const Static &st = env->dst;
+  const size_t n = (size_t) st.M * (size_t) qnet_floats_per_node (st.M, st.K);
+  if (!env->d_lw_target)
+    {
+      CUDA_TRY (cudaMalloc (&env->d_lw_target, sizeof (float) * n));
+      CUDA_TRY (cudaMalloc (&env->d_lexp, sizeof (float) * n));
+      CUDA_TRY (cudaMalloc (&env->d_lexp_sq, sizeof (float) * n));
+      CUDA_TRY (cudaMalloc (&env->d_lsteps, sizeof (float) * st.M));
+      CUDA_TRY (cudaMalloc (&env->d_ltd, sizeof (float) * st.M));
+    }
+  CUDA_TRY (cudaMemcpyAsync (env->d_lw_target, env->d_qw, sizeof (float) * n, cudaMemcpyDeviceToDevice, env->stream));
+  CUDA_TRY (cudaMemsetAsync (env->d_lexp, 0, sizeof (float) * n, env->stream));
+  CUDA_TRY (cudaMemsetAsync (env->d_lexp_sq, 0, sizeof (float) * n, env->stream));
+  CUDA_TRY (cudaMemsetAsync (env->d_lsteps, 0, sizeof (float) * st.M, env->stream));
+  env->l_lr = lr; env->l_gamma = gamma; env->l_b1 = beta1; env->l_b2 = beta2; env->l_eps = adam_eps; env->l_target_mode = target_mode ? 1 : 0;
+  return PRB_OK;
+}
+
+int
+prb_learner_sync_targets (prb_env *env)
+{
+  if (!env || !env->d_lw_target) return fail (PRB_ESTATE, "no learner (prb_learner_init)");
+  CUDA_TRY (cudaSetDevice (env->device));
+  const size_t n = (size_t) env->dst.M * (size_t) qnet_floats_per_node (env->dst.M, env->dst.K);
+  CUDA_TRY (cudaMemcpyAsync (env->d_lw_target, env->d_qw, sizeof (float) * n, cudaMemcpyDeviceToDevice, env->stream));
+  return PRB_OK;
+}
+
+int
+prb_learner_grad (prb_env *env, int32_t batch, const float *obs_dev, const int32_t *action_dev, const float *reward_dev,
+                  const float *next_obs_dev, const float *done_dev, const float *weights_dev, const float *active_dev, float *bucket_dev,
+                  float *td_mse_host)
+{
+  if (!env || !obs_dev || !action_dev || !reward_dev || !next_obs_dev || !done_dev || !active_dev || !bucket_dev || batch < 1)
+    return fail (PRB_EINVAL, "bad argument");
+  if (!env->d_lw_target) return fail (PRB_ESTATE, "no learner (prb_learner_init)");
+  CUDA_TRY (cudaSetDevice (env->device));
+  const Static &st = env->dst;
+  const int P = (int) qnet_floats_per_node (st.M, st.K);
+  const size_t smem = sizeof (float) * (size_t) P;
+  if (smem > (size_t) env->max_smem) return fail (PRB_EINVAL, "one node's parameters do not fit shared memory");
+  CUDA_TRY (cudaMemsetAsync (bucket_dev, 0, sizeof (float) * (size_t) st.M * P, env->stream));
+  CUDA_TRY (cudaMemcpyAsync (bucket_dev + (size_t) st.M * P, active_dev, sizeof (float) * st.M, cudaMemcpyDeviceToDevice, env->stream));
+  CUDA_TRY (cudaMemsetAsync (env->d_ltd, 0, sizeof (float) * st.M, env->stream));
+  LearnArgs a;
+  a.W = env->d_qw; a.Wt = env->d_lw_target; a.obs = obs_dev; a.nxt = next_obs_dev; a.act = action_dev; a.rew = reward_dev; a.done = done_dev;
+  a.wts = weights_dev; a.active = active_dev; a.grad = bucket_dev; a.td_sq = env->d_ltd; a.B = batch; a.target_mode = env->l_target_mode;
+  a.gamma = env->l_gamma;
+  CUDA_TRY (cudaFuncSetAttribute (k_learn_grad, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
+  const int chunks = (batch + LEARN_ROWS - 1) / LEARN_ROWS;
+  k_learn_grad<<<st.M * chunks, 32, smem, env->stream>>> (st, a);
+  CUDA_TRY (cudaGetLastError ());
+  env->launches++;
+  if (td_mse_host)
+    {
+      CUDA_TRY (cudaMemcpyAsync (td_mse_host, env->d_ltd, sizeof (float) * st.M, cudaMemcpyDeviceToHost, env->stream));
+      CUDA_TRY (cudaStreamSynchronize (env->stream));
+      for (int m = 0; m < st.M; m++) td_mse_host[m] /= (float) batch;
+    }
+  return PRB_OK;
+}
+
+int
+prb_learner_apply (prb_env *env, const float *bucket_dev, int32_t world_size)
+{
+  if (!env || !bucket_dev || world_size < 1) return fail (PRB_EINVAL, "bad argument");
+  if (!env->d_lw_target) return fail (PRB_ESTATE, "no learner (prb_learner_init)");
+  CUDA_TRY (cudaSetDevice (env->device));
+  const Static &st = env->dst;
+  const int P = (int) qnet_floats_per_node (st.M, st.K);
+  dim3 grid ((P + 255) / 256, st.M);
+  k_learn_adam<<<grid, 256, 0, env->stream>>> (env->d_qw, env->d_lexp, env->d_lexp_sq, env->d_lsteps, bucket_dev, st.M, P, 1.0f / (float) world_size,
+                                               env->l_lr, env->l_b1, env->l_b2, env->l_eps);
+  CUDA_TRY (cudaGetLastError ());
+  k_learn_bump<<<(st.M + 31) / 32, 32, 0, env->stream>>> (env->d_lsteps, bucket_dev, st.M, P);
+  CUDA_TRY (cudaGetLastError ());
+  env->launches += 2;
+  return PRB_OK;
+}
+
+int
+prb_learner_read (prb_env *env, int32_t which, float *out_host, int64_t n_floats)
+{
+  if (!env || !out_host) return fail (PRB_EINVAL, "null argument");
+  if (!env->d_lw_target) return fail (PRB_ESTATE, "no learner (prb_learner_init)");
+  CUDA_TRY (cudaSetDevice (env->device));
+  const Static &st = env->dst;
+  const int64_t n = (int64_t) st.M * qnet_floats_per_node (st.M, st.K);
+  const float *src = which == 0 ? env->d_qw : (which == 1 ? env->d_lw_target : (which == 2 ? env->d_lexp : (which == 3 ? env->d_lexp_sq : env->d_lsteps)));
+  const int64_t have = which == 4 ? st.M : n;
+  if (which < 0 || which > 4 || n_floats != have) return fail (PRB_EINVAL, "which is 0..4 (weights, target, exp_avg, exp_avg_sq, steps) with its float count");
+  CUDA_TRY (cudaMemcpyAsync (out_host, src, sizeof (float) * (size_t) have, cudaMemcpyDeviceToHost, env->stream));
+  CUDA_TRY (cudaStreamSynchronize (env->stream));
   return PRB_OK;
 }
 

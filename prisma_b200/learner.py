@@ -174,3 +174,83 @@ class DQNLearner:
         if getattr(env, "_replay_prioritized", False):
             env.replay_set_gradient_steps(self.steps.to(torch.int32).cpu().numpy())     # the targets computed from now on
         return out
+
+
+class DeviceLearner:
+    """The same learner with the gradient step on the device (prb_learner_*, prisma_b200/csrc/learner_core.cuh): sampling
+    from the HBM replay rings, TD targets through the neighbours' target networks, forward, hand-written backward and Adam
+    are CUDA kernels of the library; the only thing that leaves it is the ONE gradient bucket [M * P + M] floats that a
+    data-parallel job all-reduces between `grad` and `apply`.  The online weights are the ones the device-side agents act
+    on (prb_qnet_load), updated in place.  No autograd, no per-node Python loop."""
+
+    def __init__(self, env, lr: float = 1e-3, gamma: float = 1.0, betas=(0.9, 0.999), adam_eps: float = 1e-7,
+                 signaling_type: str = "ideal", weights: Optional[np.ndarray] = None):
+        import ctypes as C
+        from . import _abi
+        if signaling_type not in ("ideal", "NN", "target"):
+            raise ValueError("signaling_type must be ideal, NN or target")
+        self._C, self._abi = C, _abi
+        self.env = env
+        self.m = len(env.neighbors)
+        self.k_max = max(len(n) for n in env.neighbors)
+        self.p = qnet.floats_per_node(self.m, self.k_max)
+        if weights is not None:
+            env.qnet_load(weights)
+        _abi.check(env.lib.prb_learner_init(env.h, lr, gamma, betas[0], betas[1], adam_eps, 1 if signaling_type == "target" else 0))
+        self._buf = {}
+
+    def _buffers(self, batch):
+        if batch not in self._buf:
+            dev, ow = self.env._out.device, 1 + self.k_max
+            f = lambda *s: torch.zeros(s, dtype=torch.float32, device=dev)
+            self._buf[batch] = dict(obs=f(self.m, batch, ow), nxt=f(self.m, batch, ow), act=torch.zeros((self.m, batch), dtype=torch.int32, device=dev),
+                                    rew=f(self.m, batch), done=f(self.m, batch), wts=f(self.m, batch), active=f(self.m),
+                                    bucket=f(self.m * self.p + self.m))
+        return self._buf[batch]
+
+    def read(self, which: int = 0) -> np.ndarray:
+        n = self.m if which == 4 else self.m * self.p
+        out = np.zeros(n, dtype=np.float32)
+        self._abi.check(self.env.lib.prb_learner_read(self.env.h, which, out.ctypes.data_as(self._C.c_void_p), n))
+        return out
+
+    def weights(self) -> np.ndarray:
+        return self.read(0)
+
+    def sync_targets(self):
+        self._abi.check(self.env.lib.prb_learner_sync_targets(self.env.h))
+
+    def grad(self, batch, obs, act, rew, nxt, done, active, wts=None, want_td=True):
+        """Gradient bucket (a device tensor [M * P + M]) of the batches given as [M, B, ...] device tensors."""
+        C = self._C
+        b = self._buffers(batch)
+        td = np.zeros(self.m, dtype=np.float32)
+        ptr = lambda t: C.c_void_p(t.data_ptr()) if t is not None else None
+        self._abi.check(self.env.lib.prb_learner_grad(self.env.h, batch, ptr(obs), ptr(act), ptr(rew), ptr(nxt), ptr(done), ptr(wts), ptr(active),
+                                                      ptr(b["bucket"]), td.ctypes.data_as(C.c_void_p) if want_td else None))
+        return b["bucket"], td
+
+    def apply(self, bucket, world_size: int = 1):
+        self._abi.check(self.env.lib.prb_learner_apply(self.env.h, self._C.c_void_p(bucket.data_ptr()), int(world_size)))
+
+    def train_on_env(self, env=None, batch_size: int = 512, seed: int = 0, min_rows: Optional[int] = None, world_size: int = 1,
+                     all_reduce=None, want_td=True):
+        """One training step from the replay rings (Trainer.step): sample, gradients, all-reduce of the one bucket over the
+        ranks, Adam.  Returns the mean squared TD error per node (None for nodes without a batch)."""
+        C = self._C
+        b = self._buffers(batch_size)
+        prio = getattr(self.env, "_replay_prioritized", False)
+        ptr = lambda t: C.c_void_p(t.data_ptr())
+        self._abi.check(self.env.lib.prb_replay_sample_all(self.env.h, batch_size, seed, batch_size if min_rows is None else min_rows, ptr(b["obs"]),
+                                                           ptr(b["act"]), ptr(b["rew"]), ptr(b["nxt"]), ptr(b["done"]),
+                                                           ptr(b["wts"]) if prio else None, ptr(b["active"])))
+        bucket, td = self.grad(batch_size, b["obs"], b["act"], b["rew"], b["nxt"], b["done"], b["active"], b["wts"] if prio else None, want_td)
+        if all_reduce is not None and world_size > 1:
+            all_reduce(bucket)
+        self.apply(bucket, world_size)
+        if prio:
+            self.env.replay_set_gradient_steps(self.read(4).astype(np.int32))
+        if not want_td:
+            return None
+        act = b["active"].cpu().numpy()
+        return [float(td[i]) if act[i] > 0 else None for i in range(self.m)]

@@ -1,0 +1,117 @@
+"""The learner's gradient step on the device (prb_learner_*, prisma_b200/csrc/learner_core.cuh) against the PyTorch autograd
+statement of the same step (prisma_b200/learner.py:DQNLearner, itself held to numpy / torch.optim.Adam in tests/test_learner.py):
+identical batches drawn from the HBM replay rings, gradients of every parameter of every node, TD errors, and the weights after
+several Adam steps.  Tolerance: 2e-5 of the largest gradient entry (fp32, different summation order); weights 1e-5 absolute.
+The reference's TensorFlow numerics are unpinned."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+from tests import common
+
+pytestmark = pytest.mark.gpu
+
+
+def setup(signaling_type="ideal", num_envs=256):
+    import torch
+    from prisma_b200 import learner
+    from prisma_b200.env import BatchedRoutingEnv
+    cfg = common.env_config("abilene", num_envs=num_envs, simTime=5.0, load_factor=1.3, pingAsObs=0, activateUnderlayTraffic=1)
+    arrays = cfg.load()
+    env = BatchedRoutingEnv(cfg, arrays=arrays)
+    u2o = {int(u): i for i, u in enumerate(env.overlay_to_underlay)}
+    neigh = [[u2o[int(u)] for u in nb] for nb in env.neighbors]
+    L = learner.DQNLearner(neigh, lr=1e-3, gamma=0.9, seed=4, device="cuda", signaling_type=signaling_type)
+    env.qnet_load(L.weights())
+    env.replay_enable(rows_per_node=1 << 15)
+    if signaling_type == "target":
+        env.replay_set_target_mode(True, gamma=0.9)
+    env.step_qnet(300, eps=0.3, seed=1)
+    D = learner.DeviceLearner(env, lr=1e-3, gamma=0.9, signaling_type=signaling_type)
+    # a target network that differs from the online one
+    with torch.no_grad():
+        L.W += 0.01 * torch.randn_like(L.W)
+    env.qnet_load(L.weights())
+    return env, L, D
+
+
+@pytest.mark.parametrize("signaling_type", ["ideal", "target"])
+def test_device_gradients_and_adam_match_autograd(signaling_type):
+    import torch
+    env, L, D = setup(signaling_type)
+    B = 256
+    for it in range(3):
+        b = D._buffers(B)
+        p = lambda t: C.c_void_p(t.data_ptr())
+        from prisma_b200 import _abi
+        _abi.check(env.lib.prb_replay_sample_all(env.h, B, 10 + it, B, p(b["obs"]), p(b["act"]), p(b["rew"]), p(b["nxt"]), p(b["done"]), None,
+                                                 p(b["active"])))
+        assert float(b["active"].sum()) == L.m
+        assert (b["rew"] != 0).any() and (b["done"] > 0).any()
+        bucket, td = D.grad(B, b["obs"], b["act"], b["rew"], b["nxt"], b["done"], b["active"])
+        got = bucket[:L.m * D.p].view(L.m, D.p).clone()
+        # the same batches through autograd
+        batches = [(b["obs"][i], b["act"][i], b["rew"][i], b["nxt"][i], b["done"][i]) for i in range(L.m)]
+        if L.W.grad is not None:
+            L.W.grad.zero_()
+        total = None
+        ref_td = []
+        for i, bt in enumerate(batches):
+            l, tdv = L.loss(i, *bt)
+            total = l if total is None else total + l
+            ref_td.append(float((tdv * tdv).mean()))
+        total.backward()
+        ref = L.W.grad.detach()
+        scale = float(ref.abs().max())
+        assert scale > 1e-4
+        assert float((got - ref).abs().max()) <= 2e-5 * max(scale, 1.0), (float((got - ref).abs().max()), scale)
+        assert np.allclose(td, ref_td, rtol=1e-4, atol=1e-7)
+        # one Adam step on both
+        L.step(batches)
+        D.apply(bucket, 1)
+        assert np.abs(D.weights() - L.weights()).max() < 1e-5
+        assert np.array_equal(D.read(4), np.full(L.m, it + 1, dtype=np.float32))
+        if it == 1:
+            L.sync_targets()
+            D.sync_targets()
+            assert np.array_equal(D.read(1), D.read(0))
+    env.close()
+
+
+def test_device_learner_trains_and_the_agents_act_on_the_new_weights():
+    """Collect -> train on the device -> collect: the weights the agents act on are the trained ones, inactive nodes keep their
+    state, and the TD error of a fixed batch falls."""
+    import torch
+    env, L, D = setup("ideal", num_envs=128)
+    w0 = D.weights().copy()
+    first = last = None
+    for it in range(30):
+        mse = D.train_on_env(batch_size=128, seed=5)         # the same rows every time: the fit must improve
+        vals = [m for m in mse if m is not None]
+        assert len(vals) == L.m and np.isfinite(vals).all()
+        first = first if first is not None else float(np.mean(vals))
+        last = float(np.mean(vals))
+    assert last < first
+    w1 = D.weights()
+    assert np.abs(w1 - w0).max() > 1e-4
+    # the Q-values the device-side agents compute are those of the trained weights
+    q = torch.zeros((env.num_envs, L.k_max), dtype=torch.float32, device="cuda")
+    env.step_qnet(5, eps=0.0, seed=9)
+    rec = env.last.numpy()
+    env.qnet_act(q_out=q)
+    torch.cuda.synchronize()
+    with torch.no_grad():
+        L.W.copy_(torch.from_numpy(w1).view(L.m, -1).cuda())
+    need = np.nonzero((rec["valid"] != 0) & (rec["need_action"] != 0))[0][:32]
+    assert len(need) > 5
+    for e in need:
+        node = int(rec["overlay"][e])
+        obs = torch.from_numpy(rec["obs"][e][:1 + L.k_max].astype(np.float32)).cuda().view(1, -1)
+        ref = L.q_values(node, obs).detach().cpu().numpy()[0]
+        assert np.abs(q[e, :L.degrees[node]].cpu().numpy() - ref).max() < 1e-4
+    # a node without enough rows is left alone
+    mse = D.train_on_env(batch_size=128, seed=6, min_rows=1 << 30)
+    assert all(m is None for m in mse) and np.array_equal(D.weights(), w1)
+    env.check_errors()
+    env.close()
