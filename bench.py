@@ -309,8 +309,9 @@ def leg_device_agents(torch, dist, rank, local_rank, world, topo, envs, load_fac
 
 def leg_learner(torch, dist, rank, local_rank, world, envs, iters):
     """Data-parallel DQN training as trainer.py:45-99 runs it, on this rank's shard: collect with the device-side agents
-    -> sample from the HBM replay rings -> one gradient step per node, the ranks' gradients exchanged as ONE bucket per
-    step (NCCL all-reduce; none on one GPU) -> new weights back to the device-side agents."""
+    -> sample from the HBM replay rings -> TD targets, forward, backward and Adam as kernels of the library
+    (prb_learner_*), the ranks' gradients exchanged as ONE bucket per step (NCCL all-reduce; none on one GPU); the agents
+    act on the updated weights at once.  The PyTorch-autograd learner of round 1 is timed next to it on the same rings."""
     from prisma_b200 import learner
     from prisma_b200.env import BatchedRoutingEnv
     cfg = workload_cfg(envs, 60.0, load_factor=1.1)
@@ -322,6 +323,7 @@ def leg_learner(torch, dist, rank, local_rank, world, envs, iters):
     L = learner.DQNLearner(neigh, lr=1e-3, seed=2, device="cuda:%d" % local_rank)      # same seed: same initial weights
     env.qnet_load(L.weights())
     env.replay_enable(rows_per_node=1 << 16)
+    D = learner.DeviceLearner(env, lr=1e-3)
     ar_ms = []
 
     def ar(t):
@@ -330,8 +332,9 @@ def leg_learner(torch, dist, rank, local_rank, world, envs, iters):
         dist.all_reduce(t)
         b.record()
         ar_ms.append((a, b))
+    use_ar = ar if world > 1 else None
     env.step_qnet(128, eps=0.2, seed=rank)
-    L.train_on_env(env, batch_size=512, seed=rank, world_size=world, all_reduce=ar if world > 1 else None)   # warm-up
+    D.train_on_env(batch_size=512, seed=rank, world_size=world, all_reduce=use_ar, want_td=False)   # warm-up
     torch.cuda.synchronize()
     ar_ms.clear()
     collect_s = train_s = 0.0
@@ -339,12 +342,12 @@ def leg_learner(torch, dist, rank, local_rank, world, envs, iters):
     for it in range(iters):
         collect_s += _timed(torch, lambda: env.step_qnet(64, eps=0.2, seed=100 * rank + it))
         t0 = time.perf_counter()
-        L.train_on_env(env, batch_size=512, seed=1000 * rank + it, world_size=world, all_reduce=ar if world > 1 else None)
+        D.train_on_env(batch_size=512, seed=1000 * rank + it, world_size=world, all_reduce=use_ar, want_td=False)
         torch.cuda.synchronize()
         train_s += time.perf_counter() - t0
     wall = time.perf_counter() - t_all
     env.check_errors()
-    w = L.W.detach()
+    w = torch.from_numpy(D.weights()).cuda()
     same = True
     if world > 1:
         ref = w.clone()
@@ -353,13 +356,23 @@ def leg_learner(torch, dist, rank, local_rank, world, envs, iters):
         dist.all_reduce(flag, op=dist.ReduceOp.MIN)
         same = bool(flag.item() == 1.0)
     ar_mean = sum(a.elapsed_time(b) for a, b in ar_ms) / max(len(ar_ms), 1)
+    # the autograd learner on the same rings (one rank's step, no exchange): what the device step replaces
+    L.train_on_env(env, batch_size=512, seed=1)
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for it in range(3):
+        L.train_on_env(env, batch_size=512, seed=2 + it)
+    torch.cuda.synchronize()
+    autograd_ms = 1000.0 * (time.perf_counter() - t0) / 3
     (_,), (wall, train_s, collect_s, ar_mean) = _reduce(dist, torch, world, [0.0], [wall, train_s, collect_s, ar_mean])
     env.close()
     return {"what": "collect 64 Gym steps per environment (device-side dqn_buffer agents) -> sample 512 rows per node from the "
-                    "HBM rings -> one Adam step per node (PyTorch autograd, library code) -> weights back to the device",
+                    "HBM rings -> TD targets, forward, backward, Adam on the device (k_learn_grad, k_learn_adam) -> the agents act "
+                    "on the new weights",
             "envs_per_gpu": envs, "iterations": iters, "training_steps_per_s": iters / wall,
             "train_step_ms": 1000.0 * train_s / iters, "collect_ms": 1000.0 * collect_s / iters,
-            "allreduce_bytes": int((w.numel() + L.m) * 4) if world > 1 else 0, "allreduce_ms": ar_mean if world > 1 else 0.0,
+            "pytorch_autograd_train_step_ms": autograd_ms,
+            "allreduce_bytes": int((D.m * D.p + D.m) * 4) if world > 1 else 0, "allreduce_ms": ar_mean if world > 1 else 0.0,
             "allreduce_share_of_train_step": (ar_mean / (1000.0 * train_s / iters)) if world > 1 else 0.0,
             "backend": "nccl" if world > 1 else "none (one GPU)", "weights_identical_across_ranks": same}
 
@@ -440,7 +453,7 @@ def main():
     ap.add_argument("--c3-envs", type=int, default=8192, dest="c3_envs")
     ap.add_argument("--c2-envs", type=int, default=16384, dest="c2_envs")
     ap.add_argument("--c5-envs", type=int, default=4096, dest="c5_envs")
-    ap.add_argument("--learner-iters", type=int, default=8, dest="learner_iters")
+    ap.add_argument("--learner-iters", type=int, default=32, dest="learner_iters")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))

@@ -248,15 +248,24 @@ def main(argv=None) -> dict:
                   "with `%s` the weights stay 1" % params["signaling_type"], file=sys.stderr)
         from . import learner as learner_mod, qnet
         nbrs = overlay_neighbor_indices(env)
-        learner = learner_mod.DQNLearner(nbrs, lr=params["lr"], gamma=params["gamma"], seed=params["seed"],
-                                         device="cuda:%d" % params["device"], signaling_type=params["signaling_type"])
-        if params["load_path"]:
-            nets = metrics.load_model(params["load_path"])
-            import torch
-            w = torch.from_numpy(qnet.pack_weights(nets)).view(learner.m, -1).to(learner.W.device)
-            with torch.no_grad():
-                learner.W.copy_(w)
-            learner.sync_targets()
+        if os.environ.get("PRB_LEARNER", "device") == "torch":
+            # round 1's learner: PyTorch autograd above the environment (kept for A/B runs)
+            learner = learner_mod.DQNLearner(nbrs, lr=params["lr"], gamma=params["gamma"], seed=params["seed"],
+                                             device="cuda:%d" % params["device"], signaling_type=params["signaling_type"])
+            if params["load_path"]:
+                nets = metrics.load_model(params["load_path"])
+                import torch
+                w = torch.from_numpy(qnet.pack_weights(nets)).view(learner.m, -1).to(learner.W.device)
+                with torch.no_grad():
+                    learner.W.copy_(w)
+                learner.sync_targets()
+        else:
+            # the gradient step on the device (prb_learner_*): no autograd, no per-node Python loop
+            degrees = [len(n) for n in nbrs]
+            nets = metrics.load_model(params["load_path"]) if params["load_path"] else \
+                qnet.init_weights(len(nbrs), degrees, max(degrees), seed=params["seed"])
+            learner = learner_mod.DeviceLearner(env, lr=params["lr"], gamma=params["gamma"], signaling_type=params["signaling_type"],
+                                                weights=qnet.pack_weights(nets))
         if params["train"]:
             env.replay_enable(rows_per_node=int(params["replay_buffer_max_size"]))
             if params["signaling_type"] == "target":
