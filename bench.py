@@ -355,7 +355,8 @@ def leg_learner(torch, dist, rank, local_rank, world, envs, iters):
         flag = torch.tensor([1.0 if torch.equal(w, ref) else 0.0], device="cuda")
         dist.all_reduce(flag, op=dist.ReduceOp.MIN)
         same = bool(flag.item() == 1.0)
-    ar_mean = sum(a.elapsed_time(b) for a, b in ar_ms) / max(len(ar_ms), 1)
+    ar_all = [a.elapsed_time(b) for a, b in ar_ms] or [0.0]
+    ar_mean, ar_min = sum(ar_all) / len(ar_all), min(ar_all)     # the mean holds the wait for the slowest rank to arrive
     # the autograd learner on the same rings (one rank's step, no exchange): what the device step replaces
     L.train_on_env(env, batch_size=512, seed=1)
     torch.cuda.synchronize()
@@ -364,7 +365,7 @@ def leg_learner(torch, dist, rank, local_rank, world, envs, iters):
         L.train_on_env(env, batch_size=512, seed=2 + it)
     torch.cuda.synchronize()
     autograd_ms = 1000.0 * (time.perf_counter() - t0) / 3
-    (_,), (wall, train_s, collect_s, ar_mean) = _reduce(dist, torch, world, [0.0], [wall, train_s, collect_s, ar_mean])
+    (_,), (wall, train_s, collect_s, ar_mean, ar_min) = _reduce(dist, torch, world, [0.0], [wall, train_s, collect_s, ar_mean, ar_min])
     env.close()
     return {"what": "collect 64 Gym steps per environment (device-side dqn_buffer agents) -> sample 512 rows per node from the "
                     "HBM rings -> TD targets, forward, backward, Adam on the device (k_learn_grad, k_learn_adam) -> the agents act "
@@ -373,7 +374,9 @@ def leg_learner(torch, dist, rank, local_rank, world, envs, iters):
             "train_step_ms": 1000.0 * train_s / iters, "collect_ms": 1000.0 * collect_s / iters,
             "pytorch_autograd_train_step_ms": autograd_ms,
             "allreduce_bytes": int((D.m * D.p + D.m) * 4) if world > 1 else 0, "allreduce_ms": ar_mean if world > 1 else 0.0,
+            "allreduce_ms_min": ar_min if world > 1 else 0.0,
             "allreduce_share_of_train_step": (ar_mean / (1000.0 * train_s / iters)) if world > 1 else 0.0,
+            "allreduce_share_of_iteration": (ar_mean / (1000.0 * wall / iters)) if world > 1 else 0.0,
             "backend": "nccl" if world > 1 else "none (one GPU)", "weights_identical_across_ranks": same}
 
 

@@ -25,6 +25,9 @@ neigh = [[u2o[int(u)] for u in nb] for nb in env.neighbors]
 L = learner.DQNLearner(neigh, lr=1e-3, seed=2, device="cuda:%d" % local)       # same seed: same initial weights
 env.qnet_load(L.weights())
 env.replay_enable(rows_per_node=1 << 15)
+DEVICE = os.environ.get("PRB_LEARNER", "device") != "torch"
+if DEVICE:                              # the gradient step as kernels of the library (prb_learner_*); PRB_LEARNER=torch: autograd
+    L = learner.DeviceLearner(env, lr=1e-3)
 t_ar = 0.0
 for it in range(10):
     env.step_qnet(150, eps=0.2, seed=100 * rank + it)            # different traffic (env ids) and exploration per rank
@@ -32,11 +35,12 @@ for it in range(10):
     def ar(t):
         a.record(); dist.all_reduce(t); b.record()
     mse = L.train_on_env(env, batch_size=256, seed=1000 * rank + it, world_size=world, all_reduce=ar)
+    assert any(x is not None for x in mse)
     torch.cuda.synchronize()
     t_ar += a.elapsed_time(b)
     if it % 4 == 3:
         L.sync_targets()
-w = L.W.detach()
+w = torch.from_numpy(L.weights()).cuda() if DEVICE else L.W.detach()
 ref = w.clone()
 dist.broadcast(ref, 0)
 same = torch.equal(w, ref)
@@ -44,8 +48,8 @@ flags = torch.tensor([1.0 if same else 0.0, float(env.counters()["packet_hops"].
 dist.all_reduce(flags)
 env.check_errors()
 if rank == 0:
-    print("ranks %d identical_weights %s total_packet_hops %d bucket_floats %d mean_all_reduce_ms %.3f" % (
-        world, flags[0].item() == world, int(flags[1].item()), w.numel() + L.m, t_ar / 10), flush=True)
+    print("learner %s ranks %d identical_weights %s total_packet_hops %d bucket_floats %d mean_all_reduce_ms %.3f" % (
+        "device" if DEVICE else "torch", world, flags[0].item() == world, int(flags[1].item()), w.numel() + L.m, t_ar / 10), flush=True)
 assert same
 env.close()
 dist.destroy_process_group()
