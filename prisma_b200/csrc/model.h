@@ -396,6 +396,11 @@ build_model (const prb_config &c, HostModel &hm)
   st.off_sent_mask = o; o += 8 * M * K;
   st.off_t_key = o; o += 4 * st.NKP;
   st.off_t_seq = o; o += 4 * st.S;
+  st.FG = (std::max (F, 1) + 31) / 32;
+  o = align_up (o, 8);
+  st.off_fg_ts = o; o += 8 * st.FG;
+  st.off_fg_seq = o; o += 4 * st.FG;
+  st.off_fg_slot = o; o += 4 * st.FG;
   st.off_q_bytes = o; o += 4 * LA;
   st.off_f_pos = o; o += 4 * std::max (F, 1);
   st.off_ping_index = o; o += 4 * M;
@@ -416,6 +421,10 @@ build_model (const prb_config &c, HostModel &hm)
   Dyn d;
   bind_state (st, hm.blob0.data (), d);
   for (int s = 0; s < st.S; s++) d.t_ts[s] = T_IDLE;
+  for (int g = 0; g < st.FG; g++)
+    {
+      d.fg_ts[g] = T_IDLE; d.fg_seq[g] = 0xFFFFFFFFu; d.fg_slot[g] = -1;
+    }
   for (int s = 0; s < st.NKP; s++) d.t_key[s] = KEY_IDLE;
   for (int l = 0; l < LA; l++) d.q_head[l] = d.q_tail[l] = d.w_head[l] = d.w_tail[l] = NIL;
   for (int m = 0; m < M; m++) d.last_dst[m] = -1;

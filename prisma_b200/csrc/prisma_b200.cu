@@ -660,6 +660,41 @@ group_min (unsigned gmask, const uint32_t *t_seq, uint32_t key, int slot, uint32
   mslot = __shfl_sync (gmask, slot, __ffs (b) - 1);
 }
 
+/* the earliest timer of flow group g, found by the G lanes of the environment together (sim_core.cuh: scan_flow_groups) */
+template <int G>
+__device__ __forceinline__ void
+fg_rescan_coop (const Static &st, const Dyn &d, int g, int gl, unsigned gmask)
+{
+  int64_t bt = T_IDLE; uint32_t bq = 0xFFFFFFFFu; int bs = -1;
+  const int s0 = st.NK + 32 * g, s1 = s0 + 32 < st.S ? s0 + 32 : st.S;
+  for (int s = s0 + gl; s < s1; s += G)
+    {
+      int64_t t = d.t_ts[s];
+      if (t == T_IDLE || t > bt) continue;
+      uint32_t q = d.t_seq[s];
+      if (t < bt || q < bq)
+        {
+          bt = t; bq = q; bs = s;
+        }
+    }
+#pragma unroll
+  for (int o = G / 2; o > 0; o >>= 1)
+    {
+      const int64_t ot = __shfl_xor_sync (gmask, bt, o);
+      const uint32_t oq = __shfl_xor_sync (gmask, bq, o);
+      const int os = __shfl_xor_sync (gmask, bs, o);
+      if (ot < bt || (ot == bt && oq < bq))
+        {
+          bt = ot; bq = oq; bs = os;
+        }
+    }
+  if (gl == 0)
+    {
+      d.fg_ts[g] = bt; d.fg_seq[g] = bq; d.fg_slot[g] = bs;
+    }
+  __syncwarp (gmask);
+}
+
 /* Advance every environment: run mode until `until_ns`, gym mode until the next valid Notify().
  * SMEM: the env blob lives in shared memory during the launch. */
 template <int G, bool LOG, bool GYM, bool SMEM>
@@ -722,6 +757,7 @@ k_advance (const __grid_constant__ Static st, const LaunchArgs a)
           own_action = act;
         }
     }
+  int fresh = 0;
   if (active && gl == 0)
     {
       if (GYM) rec->valid = 0;
@@ -729,17 +765,28 @@ k_advance (const __grid_constant__ Static st, const LaunchArgs a)
         active = false;
       else
         {
-          if (!sc->started) sim.start ();
+          if (!sc->started)
+            {
+              sim.start ();
+              fresh = 1;
+            }
           if (sc->pending) active_resume = 1;
         }
     }
   active = __shfl_sync (gmask, active ? 1 : 0, leader) != 0;
   active_resume = __shfl_sync (gmask, active_resume, leader);
+  fresh = __shfl_sync (gmask, fresh, leader);
   __syncwarp (gmask);
 
-  /* flows are scanned lazily: a lane rescans its flow slots only after one of them fired */
+  /* flow timers sit under a two-level minimum (sim_core.cuh: scan_flow_groups): the groups are built once per episode,
+   * a lane keeps the earliest of its groups in registers and looks again only after a source of one of them fired */
+  if (fresh)
+    {
+      for (int g = gl; g < st.FG; g += G) fg_rescan_serial (st, d, g);
+      __syncwarp (gmask);
+    }
   int64_t fts = T_IDLE; uint32_t fseq = 0xFFFFFFFFu; int fslot = -1;
-  if (active) scan_flows (st, d, gl, G, fts, fseq, fslot);
+  if (active) scan_flow_groups (st, d, gl, G, fts, fseq, fslot);
 
   while (__any_sync (gmask, active))
     {
@@ -783,7 +830,12 @@ k_advance (const __grid_constant__ Static st, const LaunchArgs a)
       if (gl == 0) go = step_or_stop (st, sim, mslot, until, action, status) ? 1 : 0;
       __syncwarp (gmask);
       go = __shfl_sync (gmask, go, leader);
-      if (mslot == fslot && mslot >= 0) scan_flows (st, d, gl, G, fts, fseq, fslot);
+      if (mslot >= st.NK)
+        {
+          const int fg = (mslot - st.NK) >> 5;
+          fg_rescan_coop<G> (st, d, fg, gl, gmask);
+          if (gl == fg % G) scan_flow_groups (st, d, gl, G, fts, fseq, fslot);
+        }
       if (!go) active = false;
       if (GYM && G == 32 && a.qw)
         {

@@ -131,6 +131,8 @@ struct Static
   const int32_t *tr_next;              /* next injection of the same flow or -1 */
   const int32_t *flow_first;           /* [F] first trace index or -1 */
   /* state blob layout (byte offsets inside one env's blob) */
+  int32_t FG;                          /* groups of 32 flow timers (flow-group minima, scan_flow_groups) */
+  int32_t off_fg_ts, off_fg_seq, off_fg_slot;
   int32_t off_scal, off_t_ts, off_sent_mask, off_t_key, off_t_seq, off_q_bytes, off_f_pos, off_ping_index, off_win,
       off_lost, off_n_lost, off_q_pkts, off_q_head, off_q_tail, off_w_head, off_w_tail, off_last_dst, off_n_win,
       off_sent_old;
@@ -164,6 +166,9 @@ struct Dyn
   int64_t *t_ts;
   uint32_t *t_seq;
   uint32_t *t_key;
+  int64_t *fg_ts;      /* [FG] earliest timer of flow group g (slots NK + 32 g ..), its scheduler uid and its slot */
+  uint32_t *fg_seq;
+  int32_t *fg_slot;
   uint64_t *sent_mask;
   uint32_t *q_bytes, *f_pos, *ping_index, *lost, *n_lost;
   float *win;
@@ -180,6 +185,9 @@ bind_state (const Static &st, char *blob, Dyn &d)
 {
   d.sc = (Scal *) (blob + st.off_scal);
   d.t_ts = (int64_t *) (blob + st.off_t_ts);
+  d.fg_ts = (int64_t *) (blob + st.off_fg_ts);
+  d.fg_seq = (uint32_t *) (blob + st.off_fg_seq);
+  d.fg_slot = (int32_t *) (blob + st.off_fg_slot);
   d.sent_mask = (uint64_t *) (blob + st.off_sent_mask);
   d.t_seq = (uint32_t *) (blob + st.off_t_seq);
   d.t_key = (uint32_t *) (blob + st.off_t_key);
@@ -1342,19 +1350,41 @@ scan_keys (const Static &st, const Dyn &d, int gl, int G, uint32_t &bk, int &bsl
     }
 }
 
-/* one lane's share of the flow timers (exact 64-bit): slots NK+gl, NK+gl+G, ... */
+/* Flow timers (exact 64-bit, one per source: up to N * (N - 1) of them) are kept under a two-level minimum: groups of 32
+ * consecutive slots with their earliest timer in fg_ts / fg_seq / fg_slot, and every lane's share of the GROUP minima in
+ * its registers.  A source that fires costs one rescan of its group (32 slots, shared by the lanes) and one pass of a lane
+ * over its groups, instead of a pass of one lane over its share of ALL flows (310 slots at 100 nodes). */
 PRB_HD void
-scan_flows (const Static &st, const Dyn &d, int gl, int G, int64_t &fts, uint32_t &fseq, int &fslot)
+fg_rescan_serial (const Static &st, const Dyn &d, int g)
 {
-  fts = T_IDLE; fseq = 0xFFFFFFFFu; fslot = -1;
-  for (int s = st.NK + gl; s < st.S; s += G)
+  int64_t bt = T_IDLE; uint32_t bq = 0xFFFFFFFFu; int bs = -1;
+  const int s0 = st.NK + 32 * g, s1 = s0 + 32 < st.S ? s0 + 32 : st.S;
+  for (int s = s0; s < s1; s++)
     {
       int64_t t = d.t_ts[s];
-      if (t == T_IDLE || t > fts) continue;
+      if (t == T_IDLE || t > bt) continue;
       uint32_t q = d.t_seq[s];
+      if (t < bt || q < bq)
+        {
+          bt = t; bq = q; bs = s;
+        }
+    }
+  d.fg_ts[g] = bt; d.fg_seq[g] = bq; d.fg_slot[g] = bs;
+}
+
+/* one lane's share of the group minima: groups gl, gl+G, ... */
+PRB_HD void
+scan_flow_groups (const Static &st, const Dyn &d, int gl, int G, int64_t &fts, uint32_t &fseq, int &fslot)
+{
+  fts = T_IDLE; fseq = 0xFFFFFFFFu; fslot = -1;
+  for (int g = gl; g < st.FG; g += G)
+    {
+      int64_t t = d.fg_ts[g];
+      if (t == T_IDLE || t > fts) continue;
+      uint32_t q = d.fg_seq[g];
       if (t < fts || q < fseq)
         {
-          fts = t; fseq = q; fslot = s;
+          fts = t; fseq = q; fslot = d.fg_slot[g];
         }
     }
 }
@@ -1470,11 +1500,14 @@ run_env_serial (const Static &st, Dyn &d, int env, int64_t until_ns, int32_t act
   Sim<LOG, GYM> sim (st, d, env, rec);
   if (GYM) rec->valid = 0;
   if (sc->finished) return;
-  if (!sc->started) sim.start ();
+  const bool fresh = !sc->started;
+  if (fresh) sim.start ();
   bool resume_first = sc->pending != 0;
   const int64_t stop = st.sim_time_ns;
   int64_t fts; uint32_t fseq; int fslot;
-  scan_flows (st, d, 0, 1, fts, fseq, fslot);
+  if (fresh)
+    for (int g = 0; g < st.FG; g++) fg_rescan_serial (st, d, g);
+  scan_flow_groups (st, d, 0, 1, fts, fseq, fslot);
   for (;;)
     {
       uint32_t bk = KEY_IDLE;
@@ -1502,7 +1535,11 @@ run_env_serial (const Static &st, Dyn &d, int env, int64_t until_ns, int32_t act
       int status;
       bool fired_flow = bslot >= st.NK;
       if (!step_or_stop (st, sim, bslot, until_ns, 0, status)) break;
-      if (fired_flow) scan_flows (st, d, 0, 1, fts, fseq, fslot);
+      if (fired_flow)
+        {
+          fg_rescan_serial (st, d, (bslot - st.NK) >> 5);
+          scan_flow_groups (st, d, 0, 1, fts, fseq, fslot);
+        }
     }
   if (!sc->pending && until_ns < stop && sc->now < until_ns && !sc->finished) sc->now = until_ns;
   sc->c.end_ns = sc->now;
