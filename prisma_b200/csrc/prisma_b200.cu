@@ -697,7 +697,7 @@ fg_rescan_coop (const Static &st, const Dyn &d, int g, int gl, unsigned gmask)
 
 /* Advance every environment: run mode until `until_ns`, gym mode until the next valid Notify().
  * SMEM: the env blob lives in shared memory during the launch. */
-template <int G, bool LOG, bool GYM, bool SMEM>
+template <int G, bool LOG, bool GYM, bool SMEM, bool FLOW2 = false>
 __global__ void __launch_bounds__ (128, LOG ? 4 : 7)
 k_advance (const __grid_constant__ Static st, const LaunchArgs a)
 {
@@ -780,13 +780,20 @@ k_advance (const __grid_constant__ Static st, const LaunchArgs a)
 
   /* flow timers sit under a two-level minimum (sim_core.cuh: scan_flow_groups): the groups are built once per episode,
    * a lane keeps the earliest of its groups in registers and looks again only after a source of one of them fired */
-  if (fresh)
+  constexpr bool two_level = FLOW2;        /* host: flows_two_level (st); a build of its own keeps the small-topology loop as it was */
+  if (fresh && two_level)
     {
       for (int g = gl; g < st.FG; g += G) fg_rescan_serial (st, d, g);
       __syncwarp (gmask);
     }
   int64_t fts = T_IDLE; uint32_t fseq = 0xFFFFFFFFu; int fslot = -1;
-  if (active) scan_flow_groups (st, d, gl, G, fts, fseq, fslot);
+  if (active)
+    {
+      if (two_level)
+        scan_flow_groups (st, d, gl, G, fts, fseq, fslot);
+      else
+        scan_flows (st, d, gl, G, fts, fseq, fslot);
+    }
 
   while (__any_sync (gmask, active))
     {
@@ -830,12 +837,14 @@ k_advance (const __grid_constant__ Static st, const LaunchArgs a)
       if (gl == 0) go = step_or_stop (st, sim, mslot, until, action, status) ? 1 : 0;
       __syncwarp (gmask);
       go = __shfl_sync (gmask, go, leader);
-      if (mslot >= st.NK)
+      if (two_level && mslot >= st.NK)
         {
           const int fg = (mslot - st.NK) >> 5;
           fg_rescan_coop<G> (st, d, fg, gl, gmask);
           if (gl == fg % G) scan_flow_groups (st, d, gl, G, fts, fseq, fslot);
         }
+      else if (mslot == fslot && mslot >= 0)
+        scan_flows (st, d, gl, G, fts, fseq, fslot);
       if (!go) active = false;
       if (GYM && G == 32 && a.qw)
         {
@@ -1466,12 +1475,17 @@ launch_advance_g (prb_env *env, const LaunchArgs &a)
   bool use_smem = (!GYM || (a.qw && a.steps >= 8)) && smem + sizeof (prb_step_rec) * envs_per_block + 1024 <= (size_t) env->max_smem;
   if (use_smem)
     {
-      auto k = k_advance<G, LOG, GYM, true>;
+      auto k = flows_two_level (st) ? k_advance<G, LOG, GYM, true, true> : k_advance<G, LOG, GYM, true, false>;
       CUDA_TRY (cudaFuncSetAttribute (k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem));
       k<<<blocks, threads, smem, env->stream>>> (st, a);
     }
   else
-    k_advance<G, LOG, GYM, false><<<blocks, threads, 0, env->stream>>> (st, a);
+    {
+      if (flows_two_level (st))
+        k_advance<G, LOG, GYM, false, true><<<blocks, threads, 0, env->stream>>> (st, a);
+      else
+        k_advance<G, LOG, GYM, false, false><<<blocks, threads, 0, env->stream>>> (st, a);
+    }
   CUDA_TRY (cudaGetLastError ());
   env->launches++;
   return PRB_OK;

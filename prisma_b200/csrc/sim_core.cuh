@@ -1372,6 +1372,30 @@ fg_rescan_serial (const Static &st, const Dyn &d, int g)
   d.fg_ts[g] = bt; d.fg_seq[g] = bq; d.fg_slot[g] = bs;
 }
 
+/* Few flows (Abilene: 110): a lane's share of ALL flow timers is a handful of slots and the plain scan is cheaper. */
+PRB_HD bool
+flows_two_level (const Static &st)
+{
+  return st.F > 256;
+}
+
+/* one lane's share of the flow timers (exact 64-bit): slots NK+gl, NK+gl+G, ... */
+PRB_HD void
+scan_flows (const Static &st, const Dyn &d, int gl, int G, int64_t &fts, uint32_t &fseq, int &fslot)
+{
+  fts = T_IDLE; fseq = 0xFFFFFFFFu; fslot = -1;
+  for (int s = st.NK + gl; s < st.S; s += G)
+    {
+      int64_t t = d.t_ts[s];
+      if (t == T_IDLE || t > fts) continue;
+      uint32_t q = d.t_seq[s];
+      if (t < fts || q < fseq)
+        {
+          fts = t; fseq = q; fslot = s;
+        }
+    }
+}
+
 /* one lane's share of the group minima: groups gl, gl+G, ... */
 PRB_HD void
 scan_flow_groups (const Static &st, const Dyn &d, int gl, int G, int64_t &fts, uint32_t &fseq, int &fslot)
@@ -1505,9 +1529,13 @@ run_env_serial (const Static &st, Dyn &d, int env, int64_t until_ns, int32_t act
   bool resume_first = sc->pending != 0;
   const int64_t stop = st.sim_time_ns;
   int64_t fts; uint32_t fseq; int fslot;
-  if (fresh)
+  const bool two_level = flows_two_level (st);
+  if (fresh && two_level)
     for (int g = 0; g < st.FG; g++) fg_rescan_serial (st, d, g);
-  scan_flow_groups (st, d, 0, 1, fts, fseq, fslot);
+  if (two_level)
+    scan_flow_groups (st, d, 0, 1, fts, fseq, fslot);
+  else
+    scan_flows (st, d, 0, 1, fts, fseq, fslot);
   for (;;)
     {
       uint32_t bk = KEY_IDLE;
@@ -1535,11 +1563,13 @@ run_env_serial (const Static &st, Dyn &d, int env, int64_t until_ns, int32_t act
       int status;
       bool fired_flow = bslot >= st.NK;
       if (!step_or_stop (st, sim, bslot, until_ns, 0, status)) break;
-      if (fired_flow)
+      if (fired_flow && two_level)
         {
           fg_rescan_serial (st, d, (bslot - st.NK) >> 5);
           scan_flow_groups (st, d, 0, 1, fts, fseq, fslot);
         }
+      else if (fired_flow)
+        scan_flows (st, d, 0, 1, fts, fseq, fslot);
     }
   if (!sc->pending && until_ns < stop && sc->now < until_ns && !sc->finished) sc->now = until_ns;
   sc->c.end_ns = sc->now;

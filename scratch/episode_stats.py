@@ -24,6 +24,7 @@ for t in range(1, T + 1):
     a = time.perf_counter()
     env.run(until_s=float(t))
     n = env.handovers() if env.engine == "parallel" else 0
+    env.sync()
     per.append((time.perf_counter() - a, n))
 wall = time.perf_counter() - t0
 c = env.counters()
