@@ -106,9 +106,9 @@ def parse_arguments(argv=None) -> dict:
         raise SystemExit("--agent_type opt: the optimal-solution agent is a per-(source, destination) probabilistic choice "
                          "(utils.py:161-199) evaluated by the caller in Gym mode (prisma_b200.agents.OptAgent); this driver "
                          "runs table and dqn_buffer agents only")
-    if params["agent_type"] == "dqn_routing" and not params["load_path"]:
-        raise SystemExit("--agent_type dqn_routing needs --load_path with a routing_table.txt (a destination-only network is "
-                         "served as a next-hop table); to train on the device use --agent_type dqn_buffer")
+    if params["agent_type"] == "dqn_routing" and not params["load_path"] and not params["train"]:
+        raise SystemExit("--agent_type dqn_routing --train 0 needs --load_path (a routing_table.txt: a frozen destination-only "
+                         "network is a next-hop table); with --train 1 it is trained on the device")
     for k in ("logs_parent_folder", "physical_adjacency_matrix_path", "overlay_adjacency_matrix_path", "map_overlay_path"):
         params[k] = os.path.abspath(params[k])
     if params["load_path"]:
@@ -145,6 +145,12 @@ def summary_text(episode: int, s: metrics.SessionStats, iterations: int, transit
         "    Global Cost = %s," % s.sim_global_cost,
         "    Hops = %s," % ratio(s.total_hops, s.sim_delivered_packets),
         "    OverheadRatio = %s" % s.sim_signaling_overhead])
+
+
+def qnet_variants():
+    """Agent types whose Q-network the device kernels serve (prisma_b200/qnet.py: VARIANTS)."""
+    from . import qnet
+    return tuple(qnet.VARIANTS)
 
 
 def overlay_neighbor_indices(env):
@@ -236,13 +242,14 @@ def main(argv=None) -> dict:
     with open(os.path.join(params["logs_folder"], "params.json"), "w") as f:
         json.dump({k: v for k, v in params.items() if isinstance(v, (int, float, str, type(None)))}, f, indent=1)
     writer = metrics.StatsWriter(params["logs_parent_folder"], params["session_name"])
-    learning = params["agent_type"].startswith("dqn_buffer")
+    # Q-network agents run (and learn) on the device; a dqn_routing agent that only replays a loaded table does not need one
+    learning = params["agent_type"].startswith("dqn_buffer") or (params["agent_type"] == "dqn_routing" and bool(params["train"]))
     learner = None
     state = {"iterations": 0, "calls": 0, "grad_steps": 0, "snapshots": 0, "base_time": 0.0}
     if learning:
-        if params["agent_type"] != "dqn_buffer":
-            raise SystemExit("device-side agents exist for dqn_buffer; %s is served through prb_step with the "
-                             "caller's own network" % params["agent_type"])
+        if params["agent_type"] not in qnet_variants():
+            raise SystemExit("device-side agents exist for %s; %s is served through prb_step with the caller's own network"
+                             % (", ".join(qnet_variants()), params["agent_type"]))
         if params["prioritizedReplayBuffer"] and params["train"] and params["signaling_type"] != "target":
             print("note: the reference feeds its prioritized buffer from `target` signalling only (forwarder.py:494-505); "
                   "with `%s` the weights stay 1" % params["signaling_type"], file=sys.stderr)
@@ -263,7 +270,7 @@ def main(argv=None) -> dict:
             # the gradient step on the device (prb_learner_*): no autograd, no per-node Python loop
             degrees = [len(n) for n in nbrs]
             nets = metrics.load_model(params["load_path"]) if params["load_path"] else \
-                qnet.init_weights(len(nbrs), degrees, max(degrees), seed=params["seed"])
+                qnet.init_weights(len(nbrs), degrees, max(degrees), seed=params["seed"], variant=params["agent_type"])
             learner = learner_mod.DeviceLearner(env, lr=params["lr"], gamma=params["gamma"], signaling_type=params["signaling_type"],
                                                 weights=qnet.pack_weights(nets))
         if params["train"]:

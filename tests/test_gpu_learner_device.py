@@ -115,3 +115,56 @@ def test_device_learner_trains_and_the_agents_act_on_the_new_weights():
     assert all(m is None for m in mse) and np.array_equal(D.weights(), w1)
     env.check_errors()
     env.close()
+
+
+@pytest.mark.parametrize("variant", ["dqn_buffer_lite", "dqn_routing"])
+def test_narrower_variants_act_and_learn_on_the_device(variant):
+    """DQN_buffer_lite_model / DQN_routing_model as zero-padded dqn_buffer layouts (prisma_b200/qnet.py): the device-side agents
+    compute the narrow network's Q-values, and after training on the device the padding is still exactly zero."""
+    import torch
+    import torch.nn.functional as F
+    from prisma_b200 import learner, qnet
+    from prisma_b200.env import BatchedRoutingEnv
+    cfg = common.env_config("abilene", num_envs=128, simTime=5.0, load_factor=1.3, pingAsObs=0, activateUnderlayTraffic=1)
+    arrays = cfg.load()
+    env = BatchedRoutingEnv(cfg, arrays=arrays)
+    degrees = [len(n) for n in env.neighbors]
+    m, k_max = len(degrees), max(degrees)
+    nets = qnet.init_weights(m, degrees, k_max, seed=5, variant=variant)
+    mask = qnet.padding_mask(m, degrees, k_max, variant)
+    env.replay_enable(rows_per_node=1 << 14)
+    D = learner.DeviceLearner(env, lr=1e-3, weights=qnet.pack_weights(nets))
+    env.step_qnet(200, eps=0.3, seed=1)
+    for it in range(5):
+        mse = D.train_on_env(batch_size=128, seed=it)
+        assert all(x is not None and np.isfinite(x) for x in mse)
+    w = D.weights()
+    assert np.abs(w[~mask]).max() == 0.0                       # padding untouched by Adam
+    assert np.abs(w - qnet.pack_weights(nets))[mask].max() > 1e-5
+    # Q-values of the device-side agents == the narrow network evaluated by PyTorch on the trained weights
+    q = torch.zeros((env.num_envs, k_max), dtype=torch.float32, device="cuda")
+    env.qnet_act(q_out=q)
+    torch.cuda.synchronize()
+    rec = env.last.numpy()
+    need = np.nonzero((rec["valid"] != 0) & (rec["need_action"] != 0))[0][:24]
+    assert len(need) > 5
+    P = qnet.floats_per_node(m, k_max)
+    for e in need:
+        i = int(rec["overlay"][e])
+        k = degrees[i]
+        flat, o, net = w[i * P:(i + 1) * P], 0, {}
+        for name, shp in qnet.shapes(m, k_max).items():
+            n = int(np.prod(shp))
+            net[name] = flat[o:o + n].reshape(shp)
+            o += n
+        nv = {n_: torch.from_numpy(np.ascontiguousarray(v)) for n_, v in qnet.narrow_view(net, k, variant).items()}
+        x = torch.from_numpy(rec["obs"][e][:1 + k_max].astype(np.float32)).view(1, -1)
+        parts = [F.elu(nv["w_dst"][x[:, 0].long()] + nv["b_dst"])]
+        if "w_buf" in nv:
+            parts.append(F.elu(F.layer_norm(x[:, 1:1 + k], (k,), eps=1e-3) @ nv["w_buf"] + nv["b_buf"]))
+        h = F.elu(torch.cat(parts, dim=1) @ nv["w1"] + nv["b1"])
+        h = F.elu(h @ nv["w2"] + nv["b2"])
+        ref = F.elu(h @ nv["w3"] + nv["b3"]).numpy()[0]
+        assert np.abs(q[e, :k].cpu().numpy() - ref).max() < 1e-4
+    env.check_errors()
+    env.close()

@@ -182,3 +182,39 @@ def test_target_signalling_uses_the_stored_targets():
     assert torch.allclose(td, q[torch.arange(2), act] - rew)
     with pytest.raises(ValueError):
         learner.DQNLearner([[1], [0]], signaling_type="digital_twin")
+
+
+@pytest.mark.parametrize("variant", ["dqn_buffer_lite", "dqn_routing"])
+def test_narrower_model_variants_are_the_padded_network(variant):
+    """DQN_buffer_lite_model (16/16 -> 32 -> 32, models.py:184-227) and DQN_routing_model (dst only: 32 -> 64 -> 64,
+    models.py:360-392) laid out with zeros in the unused rows and columns of the dqn_buffer layout: the padded forward equals
+    the narrow network's own forward, and the padding receives exactly zero gradient, so it stays zero through training."""
+    import torch.nn.functional as F
+    from prisma_b200 import qnet
+    m, degrees = 5, [2, 3, 1, 3, 2]
+    k_max = max(degrees)
+    nets = qnet.init_weights(m, degrees, k_max, seed=3, variant=variant)
+    flat = torch.from_numpy(qnet.pack_weights(nets)).view(m, -1).clone().requires_grad_(True)
+    mask = torch.from_numpy(qnet.padding_mask(m, degrees, k_max, variant)).view(m, -1)
+    assert float(flat.detach()[~mask].abs().max()) == 0.0 and float(flat.detach()[mask].abs().min()) >= 0.0
+    rng = np.random.default_rng(0)
+    total = 0.0
+    for i in range(m):
+        k = degrees[i]
+        obs = np.zeros((40, 1 + k_max), dtype=np.float32)
+        obs[:, 0] = rng.integers(0, m, 40)
+        obs[:, 1:1 + k] = rng.integers(0, 16000, (40, k))
+        x = torch.from_numpy(obs)
+        q = learner.forward(flat[i], x, m, k, k_max)
+        w = {n: torch.from_numpy(np.ascontiguousarray(v)) for n, v in qnet.narrow_view(nets[i], k, variant).items()}
+        parts = [F.elu(w["w_dst"][x[:, 0].long()] + w["b_dst"])]
+        if "w_buf" in w:
+            parts.append(F.elu(F.layer_norm(x[:, 1:1 + k], (k,), eps=1e-3) @ w["w_buf"] + w["b_buf"]))
+        h = F.elu(torch.cat(parts, dim=1) @ w["w1"] + w["b1"])
+        h = F.elu(h @ w["w2"] + w["b2"])
+        ref = F.elu(h @ w["w3"] + w["b3"])
+        assert float((q.detach() - ref).abs().max()) < 1e-5
+        total = total + (q * q).sum()
+    total.backward()
+    assert float(flat.grad[~mask].abs().max()) == 0.0
+    assert float(flat.grad[mask].abs().max()) > 0.0
