@@ -990,7 +990,7 @@ k_run_par (const __grid_constant__ Static st, const __grid_constant__ PStatic ps
       }
   };
 
-  bool stats_pending = false;                  /* team-uniform: some ring may hold a record */
+  bool stats_pending = false, stats_tight = false;      /* team-uniform: some ring holds a record / is more than half full */
   while (!finished)
     {
       /* phase 1: earliest pending event of my nodes */
@@ -1017,10 +1017,11 @@ k_run_par (const __grid_constant__ Static st, const __grid_constant__ PStatic ps
           break;
         }
 #ifndef PRB_FOLD_EVERY
-#define PRB_FOLD_EVERY 4
+#define PRB_FOLD_EVERY 16
 #endif
-      /* the rings hold 8 records and an event pushes at most 2; at the end of the run everything that is left */
-      if ((stats_pending && rounds % PRB_FOLD_EVERY == 0) || !more) fold (more ? gmin : P_FAR32);
+      /* the rings hold 8 records and an event pushes at most 2: folded every 16th round, at once when some ring is more than
+       * half full (a node with less than two free records waits, see safe), and at the end of the run everything that is left */
+      if ((stats_pending && (stats_tight || rounds % PRB_FOLD_EVERY == 0)) || !more) fold (more ? gmin : P_FAR32);
       if (!more) break;
       /* phase 2: the earliest of my events that nothing can precede any more */
       PCand my;
@@ -1043,9 +1044,15 @@ k_run_par (const __grid_constant__ Static st, const __grid_constant__ PStatic ps
         }
       if (myx >= 0) sim.execute (myx, my);
       __syncwarp (tmask);
-      bool left = false;
-      for (int x = gl; x < N; x += T) left = left || d.s_head[x] != d.s_tail[x];
-      stats_pending = __any_sync (tmask, left);
+      unsigned left = 0;
+      for (int x = gl; x < N; x += T)
+        {
+          const unsigned n = (uint8_t) (d.s_tail[x] - d.s_head[x]);
+          left |= (n != 0 ? 1u : 0u) | (n > (unsigned) P_SR / 2 ? 2u : 0u);
+        }
+      left = __reduce_or_sync (tmask, left);
+      stats_pending = (left & 1u) != 0;
+      stats_tight = (left & 2u) != 0;
       rounds++;
       executed += __popc (go);
     }
