@@ -60,7 +60,10 @@
 
 namespace prb {
 
-constexpr int P_SR = 8;                  /* statistics-ring records per node */
+#ifndef PRB_P_SR
+#define PRB_P_SR 8
+#endif
+constexpr int P_SR = PRB_P_SR;                  /* statistics-ring records per node */
 constexpr int64_t P_FAR = INT64_MAX;
 constexpr uint32_t P_FAR32 = 0xFFFFFFFFu;   /* no event: times inside a run are 32-bit offsets from PScal::base */
 constexpr uint32_t P_NONE16 = 0xFFFFu;

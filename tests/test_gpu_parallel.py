@@ -316,3 +316,28 @@ def test_handover_replays_every_stretch_with_the_table_it_ran_with(monkeypatch):
         for k in common.COUNTER_INTS:
             assert np.array_equal(a[k], b[k]), k
         assert np.array_equal(qa, qb)
+
+
+@pytest.mark.parametrize("topo,lf,envs", [("abilene", 0.9, 4096), ("geant", 1.5, 2048)])
+def test_full_length_episodes_need_no_handover(topo, lf, envs):
+    """A whole 60-second episode (the reference's simTime, argument_parser.py:35-37) of the headline configuration
+    (BASELINE.json configs[1]: 4096 Abilene environments at load 0.9) and of GEANT at load 1.5 on the node-parallel engine:
+    no environment is handed over to the serial engine (round 1: 2.4 % of Abilene's environments by t = 60 s), packets are
+    conserved, and the saturated second half of the episode really drops packets."""
+    cfg = common.env_config(topo, num_envs=envs, simTime=60.0, load_factor=lf, pingAsObs=0, activateUnderlayTraffic=1,
+                            agent_type="dqn_routing", seed=100)
+    arrays = cfg.load()
+    env = make_env(cfg, arrays=arrays)
+    env.set_policy("table", common.sp_table(arrays))
+    for t in range(10, 61, 10):
+        env.run(until_s=float(t))
+        assert env.handovers() == 0, t
+    assert env.engine == "parallel"
+    n, ms = env.handover_stats()
+    assert n == 0 and ms == 0.0
+    c = env.counters()
+    env.check_errors(c)
+    inflight = c["overlay_injected"] - c["overlay_arrived"] - c["overlay_lost"]
+    assert (inflight >= 0).all() and (inflight < 2000).all()
+    assert int(c["overlay_lost"].sum()) > 0 and (c["end_ns"] == 60_000_000_000).all()
+    env.close()
