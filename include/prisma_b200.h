@@ -236,6 +236,10 @@ int prb_qnet_act (prb_env *env, const prb_step_rec *rec_dev, int32_t *actions_de
  * Q-values within 2e-5 of the fp32 path); prb_step_qnet then issues three launches per step.  Also: PRB_QNET_MODE=mma|warp. */
 enum { PRB_QNET_FUSED = 0, PRB_QNET_WARP = 1, PRB_QNET_MMA = 2 };
 int prb_qnet_set_mode (prb_env *env, int mode);
+/* Depth of the loaded Q-networks after the concatenation of the two input branches: 2 (DQN_buffer_model, DQN_buffer_lite_model,
+ * DQN_routing_model; default) or 1 (DQN_buffer_lighter_model and its _2 / _3 siblings, prisma/source/models.py:39-181: the output layer
+ * reads the first hidden layer; W_2 / b_2 of the layout are ignored).  Narrower layers are zero-padded layouts (prisma_b200/qnet.py). */
+int prb_qnet_set_arch (prb_env *env, int hidden_layers);
 int prb_step_qnet (prb_env *env, int32_t n_steps, float eps, uint64_t seed, prb_step_rec *out_dev);
 
 /* ---- replay buffers in HBM (prisma/source/replay_buffer.py:12-86; producers forwarder.py:135-161,214-244,352-379) ----

@@ -186,6 +186,7 @@ def lib():
         "prb_handover_stats": (C.c_int, [vp, C.POINTER(i64), C.POINTER(C.c_double)]),
         "prb_queue_bytes_noalloc": (C.c_int, [vp, i32, C.POINTER(i32), i32]),
         "prb_qnet_set_mode": (C.c_int, [vp, C.c_int]),
+        "prb_qnet_set_arch": (C.c_int, [vp, C.c_int]),
         "prb_replay_sample_all": (C.c_int, [vp, i32, u64, i64, vp, vp, vp, vp, vp, vp, vp]),
         "prb_learner_init": (C.c_int, [vp, C.c_float, C.c_float, C.c_float, C.c_float, C.c_float, C.c_int]),
         "prb_learner_sync_targets": (C.c_int, [vp]),
@@ -206,7 +207,7 @@ EXPORTS = ["prb_last_error", "prb_version", "prb_seconds_to_ns", "prb_ns_to_seco
            "prb_build_links", "prb_global_routes", "prb_create", "prb_destroy", "prb_reset", "prb_num_links",
            "prb_state_bytes", "prb_set_inject_trace", "prb_set_inject_trace_typed", "prb_set_policy", "prb_enable_log", "prb_read_events",
            "prb_read_steps", "prb_run", "prb_step", "prb_step_host", "prb_counters_host", "prb_counters_dev",
-           "prb_queue_bytes", "prb_sync", "prb_launch_count", "prb_set_engine", "prb_engine", "prb_round_stats", "prb_handovers", "prb_handover_stats", "prb_queue_bytes_noalloc", "prb_qnet_set_mode", "prb_replay_sample_all", "prb_learner_init", "prb_learner_sync_targets",
+           "prb_queue_bytes", "prb_sync", "prb_launch_count", "prb_set_engine", "prb_engine", "prb_round_stats", "prb_handovers", "prb_handover_stats", "prb_queue_bytes_noalloc", "prb_qnet_set_mode", "prb_qnet_set_arch", "prb_replay_sample_all", "prb_learner_init", "prb_learner_sync_targets",
            "prb_learner_grad", "prb_learner_apply", "prb_learner_read",
            "prb_qnet_num_floats", "prb_qnet_load", "prb_qnet_act", "prb_step_qnet",
            "prb_replay_enable", "prb_replay_set_target_mode", "prb_replay_record", "prb_replay_counts", "prb_replay_read", "prb_replay_sample",

@@ -47,7 +47,7 @@ struct QRow
 
 /* forward of one observation by a warp, same operation order as qnet_forward; o = [dst, q_1 .. q_k, 0 ...] as floats */
 __device__ __forceinline__ void
-q_forward_row (const QPtr &p, int M, int K, int k, const float *o, int lane, QRow &r)
+q_forward_row (const QPtr &p, int M, int K, int k, const float *o, int lane, QRow &r, int hidden)
 {
   int dst = (int) o[0];
   dst = dst < 0 ? 0 : (dst >= M ? M - 1 : dst);
@@ -73,15 +73,22 @@ q_forward_row (const QPtr &p, int M, int K, int k, const float *o, int lane, QRo
       a1 = fmaf (c, p.w1[(size_t) i * QH2 + lane + 32], a1);
     }
   r.h1a = elu_ (a0); r.h1b = elu_ (a1);
-  a0 = p.b2[lane]; a1 = p.b2[lane + 32];
-#pragma unroll 8
-  for (int i = 0; i < 64; i++)
+  if (hidden > 1)
     {
-      const float c = __shfl_sync (0xFFFFFFFFu, i < 32 ? r.h1a : r.h1b, i & 31);
-      a0 = fmaf (c, p.w2[(size_t) i * QH2 + lane], a0);
-      a1 = fmaf (c, p.w2[(size_t) i * QH2 + lane + 32], a1);
+      a0 = p.b2[lane]; a1 = p.b2[lane + 32];
+#pragma unroll 8
+      for (int i = 0; i < 64; i++)
+        {
+          const float c = __shfl_sync (0xFFFFFFFFu, i < 32 ? r.h1a : r.h1b, i & 31);
+          a0 = fmaf (c, p.w2[(size_t) i * QH2 + lane], a0);
+          a1 = fmaf (c, p.w2[(size_t) i * QH2 + lane + 32], a1);
+        }
+      r.h2a = elu_ (a0); r.h2b = elu_ (a1);
     }
-  r.h2a = elu_ (a0); r.h2b = elu_ (a1);
+  else
+    {
+      r.h2a = r.h1a; r.h2b = r.h1b;        /* one hidden layer: the output layer reads it directly */
+    }
   float q = lane < k ? p.b3[lane] : 0.0f;
 #pragma unroll 8
   for (int i = 0; i < 64; i++)
@@ -135,14 +142,14 @@ k_learn_grad (const __grid_constant__ Static st, const LearnArgs a)
           const int j = st.map_overlay[j_under];
           const int kj = st.agent_k[j];
           QRow t;
-          q_forward_row (q_ptrs (a.Wt + (size_t) j * P, M, K), M, K, kj, a.nxt + ri * ow, lane, t);
+          q_forward_row (q_ptrs (a.Wt + (size_t) j * P, M, K), M, K, kj, a.nxt + ri * ow, lane, t, st.q_hidden);
           float tq = (lane < kj && (int) st.agent_nbr[(size_t) j * K + lane] != me_under) ? t.q : INFINITY;
           for (int s = 16; s > 0; s >>= 1) tq = fminf (tq, __shfl_xor_sync (0xFFFFFFFFu, tq, s));
           if (tq < INFINITY) target = a.rew[ri] + a.gamma * (1.0f - a.done[ri]) * tq;
         }
       /* ---- forward, loss ---- */
       QRow r;
-      q_forward_row (w, M, K, k, a.obs + ri * ow, lane, r);
+      q_forward_row (w, M, K, k, a.obs + ri * ow, lane, r, st.q_hidden);
       const float q_sel = __shfl_sync (0xFFFFFFFFu, r.q, act);
       const float td = q_sel - target;
       td_sq += td * td;
@@ -156,18 +163,22 @@ k_learn_grad (const __grid_constant__ Static st, const LearnArgs a)
       const float dz2a = w.w3[(size_t) lane * K + act] * d3 * elu_prime (r.h2a);
       const float dz2b = w.w3[(size_t) (lane + 32) * K + act] * d3 * elu_prime (r.h2b);
       float s0 = 0.0f, s1 = 0.0f;
-#pragma unroll 4
-      for (int u = 0; u < 64; u++)
+      float dz1a = dz2a, dz1b = dz2b;                /* one hidden layer: h2 IS h1, the derivative above is already dz1 */
+      if (st.q_hidden > 1)
         {
-          const float h = __shfl_sync (0xFFFFFFFFu, u < 32 ? r.h1a : r.h1b, u & 31);     /* input unit u of layer 2 */
-          g_w2[u * QH2 + lane] += h * dz2a;
-          g_w2[u * QH2 + lane + 32] += h * dz2b;
-          const float dz = __shfl_sync (0xFFFFFFFFu, u < 32 ? dz2a : dz2b, u & 31);      /* output unit u of layer 2 */
-          s0 = fmaf (w.w2[(size_t) lane * QH2 + u], dz, s0);
-          s1 = fmaf (w.w2[(size_t) (lane + 32) * QH2 + u], dz, s1);
+#pragma unroll 4
+          for (int u = 0; u < 64; u++)
+            {
+              const float h = __shfl_sync (0xFFFFFFFFu, u < 32 ? r.h1a : r.h1b, u & 31);     /* input unit u of layer 2 */
+              g_w2[u * QH2 + lane] += h * dz2a;
+              g_w2[u * QH2 + lane + 32] += h * dz2b;
+              const float dz = __shfl_sync (0xFFFFFFFFu, u < 32 ? dz2a : dz2b, u & 31);      /* output unit u of layer 2 */
+              s0 = fmaf (w.w2[(size_t) lane * QH2 + u], dz, s0);
+              s1 = fmaf (w.w2[(size_t) (lane + 32) * QH2 + u], dz, s1);
+            }
+          g_b2[lane] += dz2a; g_b2[lane + 32] += dz2b;
+          dz1a = s0 * elu_prime (r.h1a); dz1b = s1 * elu_prime (r.h1b);
         }
-      g_b2[lane] += dz2a; g_b2[lane + 32] += dz2b;
-      const float dz1a = s0 * elu_prime (r.h1a), dz1b = s1 * elu_prime (r.h1b);
       s0 = 0.0f; s1 = 0.0f;
 #pragma unroll 4
       for (int u = 0; u < 64; u++)

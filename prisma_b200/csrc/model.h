@@ -355,6 +355,7 @@ build_model (const prb_config &c, HostModel &hm)
   hm.flow_first.assign (std::max (F, 1), -1);
   if (c.opt_rejected) hm.opt_rejected.assign (c.opt_rejected, c.opt_rejected + (size_t) N * N);
 
+  st.q_hidden = 2; st.q_pad_ = 0;
   st.E = c.num_envs; st.N = N; st.M = M; st.L = L; st.LA = LA; st.F = F; st.K = K;
   st.S = 2 * LA + M + F;
   st.NK = 2 * LA + M;

@@ -130,22 +130,25 @@ qnet_forward (const Static &st, const float *w, const prb_step_rec *r, int lane,
       a1 = fmaf (c, w1[(size_t) (QH1 + i) * QH2 + lane + 32], a1);
     }
   float h0 = elu_ (a0), h1 = elu_ (a1);
-  a0 = b2[lane]; a1 = b2[lane + 32];
-#pragma unroll QNET_UNROLL
-  for (int i = 0; i < 32; i++)
+  if (st.q_hidden > 1)         /* the one-hidden-layer models (lighter*) go from here straight to the output layer */
     {
-      float c = __shfl_sync (0xFFFFFFFFu, h0, i);
-      a0 = fmaf (c, w2[(size_t) i * QH2 + lane], a0);
-      a1 = fmaf (c, w2[(size_t) i * QH2 + lane + 32], a1);
-    }
+      a0 = b2[lane]; a1 = b2[lane + 32];
 #pragma unroll QNET_UNROLL
-  for (int i = 0; i < 32; i++)
-    {
-      float c = __shfl_sync (0xFFFFFFFFu, h1, i);
-      a0 = fmaf (c, w2[(size_t) (32 + i) * QH2 + lane], a0);
-      a1 = fmaf (c, w2[(size_t) (32 + i) * QH2 + lane + 32], a1);
+      for (int i = 0; i < 32; i++)
+        {
+          float c = __shfl_sync (0xFFFFFFFFu, h0, i);
+          a0 = fmaf (c, w2[(size_t) i * QH2 + lane], a0);
+          a1 = fmaf (c, w2[(size_t) i * QH2 + lane + 32], a1);
+        }
+#pragma unroll QNET_UNROLL
+      for (int i = 0; i < 32; i++)
+        {
+          float c = __shfl_sync (0xFFFFFFFFu, h1, i);
+          a0 = fmaf (c, w2[(size_t) (32 + i) * QH2 + lane], a0);
+          a1 = fmaf (c, w2[(size_t) (32 + i) * QH2 + lane + 32], a1);
+        }
+      h0 = elu_ (a0); h1 = elu_ (a1);
     }
-  h0 = elu_ (a0); h1 = elu_ (a1);
   /* Dense(k): lane j < k owns q_j */
   float q = lane < k ? b3[lane] : 0.0f;
 #pragma unroll QNET_UNROLL
@@ -507,7 +510,7 @@ k_qnet_mma (const __grid_constant__ Static st, const ReplayArgs ra, const float 
     }
   __syncwarp ();
   qm_dense64 (act, w1, b1, g, t);
-  qm_dense64 (act, w2, b2, g, t);
+  if (st.q_hidden > 1) qm_dense64 (act, w2, b2, g, t);
   /* Dense(k): columns >= k are padding */
   for (int nt = 0; nt * 8 < K; nt++)
     {
@@ -2123,6 +2126,15 @@ qnet_act_batched (prb_env *env, const prb_step_rec *rec_dev, int32_t *actions_de
                                                                                     env->q_step++, env->rp.target_mode ? env->rp.tmin : nullptr, qb);
   CUDA_TRY (cudaGetLastError ());
   env->launches += 2;
+  return PRB_OK;
+}
+
+int
+prb_qnet_set_arch (prb_env *env, int hidden_layers)
+{
+  if (!env) return fail (PRB_EINVAL, "null handle");
+  if (hidden_layers != 1 && hidden_layers != 2) return fail (PRB_EINVAL, "the Q-networks have 1 or 2 hidden layers after the concatenation");
+  env->dst.q_hidden = hidden_layers;
   return PRB_OK;
 }
 

@@ -107,6 +107,7 @@ struct Static
   int32_t ping_as_obs, train, opt_agent, inject_mode, policy, mode;
   float loss_penalty;
   uint64_t seed, env_id_base, policy_seed;
+  int32_t q_hidden, q_pad_;            /* hidden layers after the concatenation of the Q-networks: 2, or 1 (prb_qnet_set_arch) */
   uint64_t inv1e9_hi, inv1e9_lo;       /* int64x64_t::Invert (1e9), computed on the host */
   int64_t pol_n, tr_n;
   int64_t ev_cap, st_cap;

@@ -214,6 +214,10 @@ class BatchedRoutingEnv:
         w = np.ascontiguousarray(weights, dtype=np.float32).ravel()
         _abi.check(self.lib.prb_qnet_load(self.h, w.ctypes.data_as(C.c_void_p), w.size))
 
+    def qnet_set_arch(self, hidden_layers: int = 2):
+        """Hidden layers after the concatenation: 2 (dqn_buffer, dqn_buffer_lite, dqn_routing) or 1 (dqn_buffer_lighter*)."""
+        _abi.check(self.lib.prb_qnet_set_arch(self.h, int(hidden_layers)))
+
     def qnet_set_mode(self, mode: str = "fused"):
         """'fused': Q-networks inside the simulator kernel (one warp per environment, fp32); 'warp': the same as its own
         kernel; 'mma': decisions of all environments bucketed by node, tiles of 16 on the tensor cores."""

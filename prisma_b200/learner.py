@@ -38,7 +38,7 @@ def _views(flat: torch.Tensor, m: int, k_max: int):
     return out
 
 
-def forward(flat: torch.Tensor, obs: torch.Tensor, m: int, k: int, k_max: int) -> torch.Tensor:
+def forward(flat: torch.Tensor, obs: torch.Tensor, m: int, k: int, k_max: int, hidden: int = 2) -> torch.Tensor:
     """Q-values [B, k] of the node whose parameters are `flat` for observations [B, 1 + k_max]
     (prisma/source/models.py:257-301)."""
     w = _views(flat, m, k_max)
@@ -48,7 +48,8 @@ def forward(flat: torch.Tensor, obs: torch.Tensor, m: int, k: int, k_max: int) -
     ln = F.layer_norm(buf, (k,), eps=1e-3)
     hb = F.elu(ln @ w["w_buf"][:k] + w["b_buf"])
     h = F.elu(torch.cat([hd, hb], dim=1) @ w["w1"] + w["b1"])
-    h = F.elu(h @ w["w2"] + w["b2"])
+    if hidden > 1:
+        h = F.elu(h @ w["w2"] + w["b2"])
     return F.elu(h @ w["w3"][:, :k] + w["b3"][:k])
 
 
@@ -58,7 +59,8 @@ def huber(x: torch.Tensor, delta: float = 1.0) -> torch.Tensor:
 
 class DQNLearner:
     def __init__(self, neighbors: Sequence[Sequence[int]], lr: float = 1e-3, gamma: float = 1.0, seed: int = 0,
-                 device: str = "cpu", betas=(0.9, 0.999), adam_eps: float = 1e-7, signaling_type: str = "ideal"):
+                 device: str = "cpu", betas=(0.9, 0.999), adam_eps: float = 1e-7, signaling_type: str = "ideal",
+                 variant: str = "dqn_buffer"):
         """neighbors[i] = overlay neighbours of node i in action order (BatchedRoutingEnv.neighbors mapped to overlay
         indices).  Adam defaults are Keras' (learner.py:103: tf.keras.optimizers.Adam (lr))."""
         if signaling_type not in ("ideal", "NN", "target"):
@@ -69,7 +71,8 @@ class DQNLearner:
         self.degrees = [len(n) for n in self.neighbors]
         self.k_max = max(self.degrees)
         self.gamma, self.lr, self.betas, self.adam_eps = float(gamma), float(lr), betas, float(adam_eps)
-        nets = qnet.init_weights(self.m, self.degrees, self.k_max, seed=seed)
+        self.hidden = qnet.hidden_layers(variant)
+        nets = qnet.init_weights(self.m, self.degrees, self.k_max, seed=seed, variant=variant)
         w = torch.from_numpy(qnet.pack_weights(nets)).view(self.m, -1)
         self.W = w.to(device).requires_grad_(True)
         self.W_target = self.W.detach().clone()
@@ -89,7 +92,7 @@ class DQNLearner:
         self.W_target.copy_(self.W.detach())
 
     def q_values(self, node: int, obs: torch.Tensor) -> torch.Tensor:
-        return forward(self.W[node], obs, self.m, self.degrees[node], self.k_max)
+        return forward(self.W[node], obs, self.m, self.degrees[node], self.k_max, self.hidden)
 
     # ---- one gradient step of every node that has a batch ----
     def targets(self, node: int, act, rew, nxt, done) -> torch.Tensor:
@@ -103,7 +106,7 @@ class DQNLearner:
                 idx = self.filtered[node][a]
                 if len(sel) == 0 or not idx:
                     continue
-                q = forward(self.W_target[j], nxt[sel], self.m, self.degrees[j], self.k_max)[:, idx]
+                q = forward(self.W_target[j], nxt[sel], self.m, self.degrees[j], self.k_max, self.hidden)[:, idx]
                 t[sel] = rew[sel].float() + self.gamma * (1.0 - done[sel].float()) * q.min(dim=1).values
         return t
 
@@ -184,7 +187,7 @@ class DeviceLearner:
     on (prb_qnet_load), updated in place.  No autograd, no per-node Python loop."""
 
     def __init__(self, env, lr: float = 1e-3, gamma: float = 1.0, betas=(0.9, 0.999), adam_eps: float = 1e-7,
-                 signaling_type: str = "ideal", weights: Optional[np.ndarray] = None):
+                 signaling_type: str = "ideal", weights: Optional[np.ndarray] = None, variant: str = "dqn_buffer"):
         import ctypes as C
         from . import _abi
         if signaling_type not in ("ideal", "NN", "target"):
@@ -196,6 +199,7 @@ class DeviceLearner:
         self.p = qnet.floats_per_node(self.m, self.k_max)
         if weights is not None:
             env.qnet_load(weights)
+        env.qnet_set_arch(qnet.hidden_layers(variant))
         _abi.check(env.lib.prb_learner_init(env.h, lr, gamma, betas[0], betas[1], adam_eps, 1 if signaling_type == "target" else 0))
         self._buf = {}
 

@@ -272,7 +272,7 @@ def main(argv=None) -> dict:
             nets = metrics.load_model(params["load_path"]) if params["load_path"] else \
                 qnet.init_weights(len(nbrs), degrees, max(degrees), seed=params["seed"], variant=params["agent_type"])
             learner = learner_mod.DeviceLearner(env, lr=params["lr"], gamma=params["gamma"], signaling_type=params["signaling_type"],
-                                                weights=qnet.pack_weights(nets))
+                                                weights=qnet.pack_weights(nets), variant=params["agent_type"])
         if params["train"]:
             env.replay_enable(rows_per_node=int(params["replay_buffer_max_size"]))
             if params["signaling_type"] == "target":

@@ -33,7 +33,14 @@ def he_uniform(rng, fan_in: int, shape) -> np.ndarray:
 # zeros in the unused rows and columns: elu (0) = 0, so a padded unit outputs nothing, feeds nothing and receives a zero
 # gradient — the device kernels (acting and learning) serve these variants exactly, without a code path of their own.
 # The one-hidden-layer variants (lighter, lighter_2, lighter_3) and the `ff` model cannot be embedded (elu is no identity).
-VARIANTS = {"dqn_buffer": (32, 32, 64, 64), "dqn_buffer_lite": (16, 16, 32, 32), "dqn_routing": (32, 0, 64, 64)}
+# u2 == 0: ONE hidden layer after the concatenation (DQN_buffer_lighter_model :39-84, _2 :87-132, _3 :135-181): the output
+# layer reads the first hidden layer and W_2 / b_2 of the layout stay zero (prb_qnet_set_arch (1)).
+VARIANTS = {"dqn_buffer": (32, 32, 64, 64), "dqn_buffer_lite": (16, 16, 32, 32), "dqn_routing": (32, 0, 64, 64),
+            "dqn_buffer_lighter": (16, 16, 32, 0), "dqn_buffer_lighter_2": (8, 8, 16, 0), "dqn_buffer_lighter_3": (4, 4, 8, 0)}
+
+
+def hidden_layers(variant: str) -> int:
+    return 2 if VARIANTS[variant][3] else 1
 
 
 def init_weights(m: int, degrees: List[int], k_max: int, seed: int = 0, variant: str = "dqn_buffer") -> List[Dict[str, np.ndarray]]:
@@ -56,9 +63,11 @@ def init_weights(m: int, degrees: List[int], k_max: int, seed: int = 0, variant:
         net["w1"][:ud, :u1] = w1[:ud]
         net["w1"][H1:H1 + ub, :u1] = w1[ud:]
         net["b1"][:u1] = he_uniform(rng, u1, (u1,))
-        net["w2"][:u1, :u2] = he_uniform(rng, u1, (u1, u2))
-        net["b2"][:u2] = he_uniform(rng, u2, (u2,))
-        net["w3"][:u2, :k] = he_uniform(rng, u2, (u2, k))
+        if u2:
+            net["w2"][:u1, :u2] = he_uniform(rng, u1, (u1, u2))
+            net["b2"][:u2] = he_uniform(rng, u2, (u2,))
+        last = u2 or u1
+        net["w3"][:last, :k] = he_uniform(rng, last, (last, k))
         net["b3"][:k] = he_uniform(rng, k, (k,))
         nets.append(net)
     return nets
@@ -69,7 +78,10 @@ def narrow_view(net: Dict[str, np.ndarray], k: int, variant: str) -> Dict[str, n
     ud, ub, u1, u2 = VARIANTS[variant]
     out = {"w_dst": net["w_dst"][:, :ud], "b_dst": net["b_dst"][:ud],
            "w1": np.concatenate([net["w1"][:ud, :u1], net["w1"][H1:H1 + ub, :u1]]), "b1": net["b1"][:u1],
-           "w2": net["w2"][:u1, :u2], "b2": net["b2"][:u2], "w3": net["w3"][:u2, :k], "b3": net["b3"][:k]}
+           "w3": net["w3"][:(u2 or u1), :k], "b3": net["b3"][:k]}
+    if u2:
+        out["w2"] = net["w2"][:u1, :u2]
+        out["b2"] = net["b2"][:u2]
     if ub:
         out["w_buf"] = net["w_buf"][:k, :ub]
         out["b_buf"] = net["b_buf"][:ub]
@@ -88,7 +100,7 @@ def padding_mask(m: int, degrees: List[int], k_max: int, variant: str) -> np.nda
         net["w_buf"][:k, :ub] = True; net["b_buf"][:ub] = True
         net["w1"][:ud, :u1] = True; net["w1"][H1:H1 + ub, :u1] = True; net["b1"][:u1] = True
         net["w2"][:u1, :u2] = True; net["b2"][:u2] = True
-        net["w3"][:u2, :k] = True; net["b3"][:k] = True
+        net["w3"][:(u2 or u1), :k] = True; net["b3"][:k] = True
         parts += [net[name].ravel() for name in LAYERS]
     return np.concatenate(parts)
 

@@ -13,7 +13,7 @@ from tests import common
 pytestmark = pytest.mark.gpu
 
 
-def setup(signaling_type="ideal", num_envs=256):
+def setup(signaling_type="ideal", num_envs=256, variant="dqn_buffer"):
     import torch
     from prisma_b200 import learner
     from prisma_b200.env import BatchedRoutingEnv
@@ -22,13 +22,13 @@ def setup(signaling_type="ideal", num_envs=256):
     env = BatchedRoutingEnv(cfg, arrays=arrays)
     u2o = {int(u): i for i, u in enumerate(env.overlay_to_underlay)}
     neigh = [[u2o[int(u)] for u in nb] for nb in env.neighbors]
-    L = learner.DQNLearner(neigh, lr=1e-3, gamma=0.9, seed=4, device="cuda", signaling_type=signaling_type)
+    L = learner.DQNLearner(neigh, lr=1e-3, gamma=0.9, seed=4, device="cuda", signaling_type=signaling_type, variant=variant)
     env.qnet_load(L.weights())
     env.replay_enable(rows_per_node=1 << 15)
     if signaling_type == "target":
         env.replay_set_target_mode(True, gamma=0.9)
     env.step_qnet(300, eps=0.3, seed=1)
-    D = learner.DeviceLearner(env, lr=1e-3, gamma=0.9, signaling_type=signaling_type)
+    D = learner.DeviceLearner(env, lr=1e-3, gamma=0.9, signaling_type=signaling_type, variant=variant)
     # a target network that differs from the online one
     with torch.no_grad():
         L.W += 0.01 * torch.randn_like(L.W)
@@ -36,10 +36,10 @@ def setup(signaling_type="ideal", num_envs=256):
     return env, L, D
 
 
-@pytest.mark.parametrize("signaling_type", ["ideal", "target"])
-def test_device_gradients_and_adam_match_autograd(signaling_type):
+@pytest.mark.parametrize("signaling_type,variant", [("ideal", "dqn_buffer"), ("target", "dqn_buffer"), ("ideal", "dqn_buffer_lighter")])
+def test_device_gradients_and_adam_match_autograd(signaling_type, variant):
     import torch
-    env, L, D = setup(signaling_type)
+    env, L, D = setup(signaling_type, variant=variant)
     B = 256
     for it in range(3):
         b = D._buffers(B)
@@ -117,7 +117,7 @@ def test_device_learner_trains_and_the_agents_act_on_the_new_weights():
     env.close()
 
 
-@pytest.mark.parametrize("variant", ["dqn_buffer_lite", "dqn_routing"])
+@pytest.mark.parametrize("variant", ["dqn_buffer_lite", "dqn_routing", "dqn_buffer_lighter", "dqn_buffer_lighter_3"])
 def test_narrower_variants_act_and_learn_on_the_device(variant):
     """DQN_buffer_lite_model / DQN_routing_model as zero-padded dqn_buffer layouts (prisma_b200/qnet.py): the device-side agents
     compute the narrow network's Q-values, and after training on the device the padding is still exactly zero."""
@@ -133,7 +133,7 @@ def test_narrower_variants_act_and_learn_on_the_device(variant):
     nets = qnet.init_weights(m, degrees, k_max, seed=5, variant=variant)
     mask = qnet.padding_mask(m, degrees, k_max, variant)
     env.replay_enable(rows_per_node=1 << 14)
-    D = learner.DeviceLearner(env, lr=1e-3, weights=qnet.pack_weights(nets))
+    D = learner.DeviceLearner(env, lr=1e-3, weights=qnet.pack_weights(nets), variant=variant)
     env.step_qnet(200, eps=0.3, seed=1)
     for it in range(5):
         mse = D.train_on_env(batch_size=128, seed=it)
@@ -163,7 +163,8 @@ def test_narrower_variants_act_and_learn_on_the_device(variant):
         if "w_buf" in nv:
             parts.append(F.elu(F.layer_norm(x[:, 1:1 + k], (k,), eps=1e-3) @ nv["w_buf"] + nv["b_buf"]))
         h = F.elu(torch.cat(parts, dim=1) @ nv["w1"] + nv["b1"])
-        h = F.elu(h @ nv["w2"] + nv["b2"])
+        if "w2" in nv:
+            h = F.elu(h @ nv["w2"] + nv["b2"])
         ref = F.elu(h @ nv["w3"] + nv["b3"]).numpy()[0]
         assert np.abs(q[e, :k].cpu().numpy() - ref).max() < 1e-4
     env.check_errors()

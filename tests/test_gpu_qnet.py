@@ -190,3 +190,42 @@ def test_batched_tensor_core_loop_keeps_the_books_like_the_warp_path():
     for a, b in zip(out["fused"], out["mma"]):
         assert abs(a - b) <= 0.02 * a, out
     assert out["mma"][2] == 512 * 300 or out["mma"][2] > 0
+
+
+def test_one_hidden_layer_models_on_every_forward_path():
+    """DQN_buffer_lighter_model (one hidden layer, models.py:39-84) as a zero-padded layout with prb_qnet_set_arch (1): the
+    fused / warp kernel and the tensor-core kernel give the Q-values of the narrow network (PyTorch fp32)."""
+    import torch
+    import torch.nn.functional as F
+    from prisma_b200 import qnet
+    from prisma_b200.env import BatchedRoutingEnv
+    cfg = common.env_config("abilene", num_envs=256, simTime=1.0, load_factor=1.5, pingAsObs=0, activateUnderlayTraffic=1)
+    arrays = cfg.load()
+    env = BatchedRoutingEnv(cfg, arrays=arrays)
+    degrees = [len(n) for n in env.neighbors]
+    m, k_max = len(degrees), max(degrees)
+    nets = qnet.init_weights(m, degrees, k_max, seed=9, variant="dqn_buffer_lighter")
+    env.qnet_load(qnet.pack_weights(nets))
+    env.qnet_set_arch(1)
+    env.step_qnet(40, eps=0.1, seed=2)                  # fused path with the switch
+    rec = env.last.numpy()
+    need = np.nonzero((rec["valid"] != 0) & (rec["need_action"] != 0))[0]
+    assert len(need) > 50
+    q = torch.zeros((env.num_envs, k_max), dtype=torch.float32, device="cuda")
+    for mode, tol in (("warp", 1e-5), ("mma", 2e-5)):
+        env.qnet_set_mode(mode)
+        env.qnet_act(q_out=q)
+        torch.cuda.synchronize()
+        got = q.cpu().numpy()
+        for e in need[:48]:
+            i = int(rec["overlay"][e])
+            k = degrees[i]
+            nv = {n_: torch.from_numpy(np.ascontiguousarray(v)) for n_, v in qnet.narrow_view(nets[i], k, "dqn_buffer_lighter").items()}
+            x = torch.from_numpy(rec["obs"][e][:1 + k_max].astype(np.float32)).view(1, -1)
+            hd = F.elu(nv["w_dst"][x[:, 0].long()] + nv["b_dst"])
+            hb = F.elu(F.layer_norm(x[:, 1:1 + k], (k,), eps=1e-3) @ nv["w_buf"] + nv["b_buf"])
+            h = F.elu(torch.cat([hd, hb], dim=1) @ nv["w1"] + nv["b1"])
+            ref = F.elu(h @ nv["w3"] + nv["b3"]).numpy()[0]
+            assert np.abs(got[e, :k] - ref).max() < tol, (mode, np.abs(got[e, :k] - ref).max())
+    env.check_errors()
+    env.close()

@@ -184,7 +184,7 @@ def test_target_signalling_uses_the_stored_targets():
         learner.DQNLearner([[1], [0]], signaling_type="digital_twin")
 
 
-@pytest.mark.parametrize("variant", ["dqn_buffer_lite", "dqn_routing"])
+@pytest.mark.parametrize("variant", ["dqn_buffer_lite", "dqn_routing", "dqn_buffer_lighter", "dqn_buffer_lighter_3"])
 def test_narrower_model_variants_are_the_padded_network(variant):
     """DQN_buffer_lite_model (16/16 -> 32 -> 32, models.py:184-227) and DQN_routing_model (dst only: 32 -> 64 -> 64,
     models.py:360-392) laid out with zeros in the unused rows and columns of the dqn_buffer layout: the padded forward equals
@@ -205,13 +205,14 @@ def test_narrower_model_variants_are_the_padded_network(variant):
         obs[:, 0] = rng.integers(0, m, 40)
         obs[:, 1:1 + k] = rng.integers(0, 16000, (40, k))
         x = torch.from_numpy(obs)
-        q = learner.forward(flat[i], x, m, k, k_max)
+        q = learner.forward(flat[i], x, m, k, k_max, hidden=qnet.hidden_layers(variant))
         w = {n: torch.from_numpy(np.ascontiguousarray(v)) for n, v in qnet.narrow_view(nets[i], k, variant).items()}
         parts = [F.elu(w["w_dst"][x[:, 0].long()] + w["b_dst"])]
         if "w_buf" in w:
             parts.append(F.elu(F.layer_norm(x[:, 1:1 + k], (k,), eps=1e-3) @ w["w_buf"] + w["b_buf"]))
         h = F.elu(torch.cat(parts, dim=1) @ w["w1"] + w["b1"])
-        h = F.elu(h @ w["w2"] + w["b2"])
+        if "w2" in w:
+            h = F.elu(h @ w["w2"] + w["b2"])
         ref = F.elu(h @ w["w3"] + w["b3"])
         assert float((q.detach() - ref).abs().max()) < 1e-5
         total = total + (q * q).sum()
