@@ -88,6 +88,7 @@ elu_ (float x)
 #define PRB_QNET_UNROLL 8
 #endif
 constexpr int QNET_UNROLL = PRB_QNET_UNROLL;
+template <bool ONE_HIDDEN = false>
 __device__ PRB_QNET_ATTR int
 qnet_forward (const Static &st, const float *w, const prb_step_rec *r, int lane, float eps, uint64_t seed, uint64_t step, uint64_t eid,
               float *q_row, float *tmin = nullptr)
@@ -130,7 +131,7 @@ qnet_forward (const Static &st, const float *w, const prb_step_rec *r, int lane,
       a1 = fmaf (c, w1[(size_t) (QH1 + i) * QH2 + lane + 32], a1);
     }
   float h0 = elu_ (a0), h1 = elu_ (a1);
-  if (st.q_hidden > 1)         /* the one-hidden-layer models (lighter*) go from here straight to the output layer */
+  if (!ONE_HIDDEN)             /* the one-hidden-layer models (lighter*) go from here straight to the output layer */
     {
       a0 = b2[lane]; a1 = b2[lane + 32];
 #pragma unroll QNET_UNROLL
@@ -212,8 +213,9 @@ k_qnet_act (const __grid_constant__ Static st, const float *w, const prb_step_re
       return;
     }
   float tmin = INFINITY;
-  int action = qnet_forward (st, w, r, lane, eps, seed, step, st.env_id_base + (uint64_t) e, q_out ? q_out + (size_t) e * st.K : nullptr,
-                             tmin_out ? &tmin : nullptr);
+  float *qr = q_out ? q_out + (size_t) e * st.K : nullptr;
+  int action = st.q_hidden > 1 ? qnet_forward<false> (st, w, r, lane, eps, seed, step, st.env_id_base + (uint64_t) e, qr, tmin_out ? &tmin : nullptr)
+                               : qnet_forward<true> (st, w, r, lane, eps, seed, step, st.env_id_base + (uint64_t) e, qr, tmin_out ? &tmin : nullptr);
   if (lane == 0)
     {
       actions[e] = action;
@@ -2495,7 +2497,8 @@ prb_step_qnet (prb_env *env, int32_t n_steps, float eps, uint64_t seed, prb_step
         }
       return rc;
     }
-  if (env->G == 32 && !env->qnet_unfused && env->qnet_mode == PRB_QNET_FUSED)
+  /* the fused kernel holds the two-hidden-layer network only: one-hidden-layer models take the launch sequence below */
+  if (env->G == 32 && !env->qnet_unfused && env->qnet_mode == PRB_QNET_FUSED && env->dst.q_hidden == 2)
     {
       /* one launch: every warp answers the steps of its environment itself (k_advance, gym mode) */
       CUDA_TRY (cudaSetDevice (env->device));

@@ -67,11 +67,20 @@ def test_device_gradients_and_adam_match_autograd(signaling_type, variant):
         assert scale > 1e-4
         assert float((got - ref).abs().max()) <= 2e-5 * max(scale, 1.0), (float((got - ref).abs().max()), scale)
         assert np.allclose(td, ref_td, rtol=1e-4, atol=1e-7)
-        # one Adam step on both
-        L.step(batches)
+        # one Adam step: k_learn_adam against numpy on the SAME gradients (Keras' defaults; an update is g / (|g| + 1e-7)-like, so
+        # comparing two learners through their slightly different near-zero gradients would test the noise, not the kernel)
+        w0, m0, v0 = D.read(0).astype(np.float64), D.read(2).astype(np.float64), D.read(3).astype(np.float64)
+        gnp = got.cpu().numpy().astype(np.float64).ravel()
         D.apply(bucket, 1)
-        assert np.abs(D.weights() - L.weights()).max() < 1e-5
+        t = it + 1
+        m1 = 0.9 * m0 + 0.1 * gnp
+        v1 = 0.999 * v0 + 0.001 * gnp * gnp
+        w1 = w0 - 1e-3 * (m1 / (1 - 0.9 ** t)) / (np.sqrt(v1 / (1 - 0.999 ** t)) + 1e-7)
+        assert np.abs(D.weights() - w1).max() < 2e-6
+        assert np.abs(D.read(2) - m1).max() < 1e-7 and np.abs(D.read(3) - v1).max() < 1e-9
         assert np.array_equal(D.read(4), np.full(L.m, it + 1, dtype=np.float32))
+        with torch.no_grad():                       # the autograd learner follows the device's weights
+            L.W.copy_(torch.from_numpy(D.weights()).view(L.m, -1).cuda())
         if it == 1:
             L.sync_targets()
             D.sync_targets()
