@@ -77,7 +77,9 @@ def test_device_gradients_and_adam_match_autograd(signaling_type, variant):
         v1 = 0.999 * v0 + 0.001 * gnp * gnp
         w1 = w0 - 1e-3 * (m1 / (1 - 0.9 ** t)) / (np.sqrt(v1 / (1 - 0.999 ** t)) + 1e-7)
         assert np.abs(D.weights() - w1).max() < 2e-6
-        assert np.allclose(D.read(2), m1, rtol=1e-4, atol=1e-9) and np.allclose(D.read(3), v1, rtol=1e-4, atol=1e-12)
+        # float32 sums of terms of opposite sign: absolute tolerance relative to the largest moment
+        assert np.allclose(D.read(2), m1, rtol=1e-4, atol=1e-6 * np.abs(m1).max())
+        assert np.allclose(D.read(3), v1, rtol=1e-4, atol=1e-6 * np.abs(v1).max())
         assert np.array_equal(D.read(4), np.full(L.m, it + 1, dtype=np.float32))
         with torch.no_grad():                       # the autograd learner follows the device's weights
             L.W.copy_(torch.from_numpy(D.weights()).view(L.m, -1).cuda())
