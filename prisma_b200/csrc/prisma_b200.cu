@@ -744,44 +744,6 @@ k_advance (const __grid_constant__ Static st, const LaunchArgs a)
   int active_resume = 0;      /* gym mode: the first thing to run is the rest of the suspended Receive */
   int32_t own_action = -1;    /* in-kernel agents: the answer to the pending step */
   int steps_done = 0;
-  /* G < 32 with in-kernel agents: several environments share a warp; their simulators run side by side on G lanes each,
-   * and whenever some of them pause on a step the WHOLE warp evaluates their Q-networks one after the other (answer_ww) */
-  constexpr bool WW = GYM && G < 32;
-  constexpr unsigned FULL = 0xFFFFFFFFu;
-  auto answer_ww = [&] (int flag, bool resume) {
-    unsigned pb = __ballot_sync (FULL, flag && gl == 0);
-    while (pb)
-      {
-        const int ldr = __ffs (pb) - 1;
-        pb &= pb - 1;
-        const prb_step_rec *r = (const prb_step_rec *) __shfl_sync (FULL, (unsigned long long) rec, ldr);
-        const int e = __shfl_sync (FULL, env, ldr);
-        const int sd = __shfl_sync (FULL, steps_done, ldr);
-        int32_t act = 0;
-        float tmin = INFINITY;
-        if (r->need_action)
-          act = qnet_forward (st, a.qw, r, lane, a.eps, a.seed, a.step0 + (uint64_t) sd, st.env_id_base + (uint64_t) e, nullptr,
-                              a.replay.target_mode ? &tmin : nullptr);
-        if (lane == ldr && a.replay.rows) replay_record_one (st, a.replay, e, r, act, tmin);
-        __syncwarp (FULL);
-        if (leader == ldr)
-          {
-            own_action = act;
-            if (resume)
-              {
-                active_resume = 1;
-                active = true;
-              }
-          }
-      }
-  };
-  if (WW && a.qw)
-    {
-      int pend = 0;
-      if (active && gl == 0) pend = sc->pending && !sc->finished && rec->valid;
-      __syncwarp (FULL);
-      answer_ww (pend, false);
-    }
   if (GYM && G == 32 && a.qw && active)
     {
       /* the step this environment is suspended on is answered first (a.out holds its record) */
@@ -838,69 +800,6 @@ k_advance (const __grid_constant__ Static st, const LaunchArgs a)
         scan_flows (st, d, gl, G, fts, fseq, fslot);
     }
 
-  if (WW && a.qw)
-    {
-      /* one event of every running environment of the warp, then the answers of those that paused */
-      auto one_event = [&] () -> int {
-        uint32_t bk = KEY_IDLE;
-        int bslot = -1;
-        if (!active_resume)
-          {
-            scan_keys (st, d, gl, G, bk, bslot);
-            uint32_t fk = flow_key (sc, fts);
-            if (fk < bk || (fk == bk && fk != KEY_IDLE && fseq < d.t_seq[bslot]))
-              {
-                bk = fk;
-                bslot = fslot;
-              }
-          }
-        uint32_t mkey; int mslot;
-        group_min<G> (gmask, d.t_seq, bk, bslot, mkey, mslot);
-        int32_t action = 0;
-        if (active_resume)
-          {
-            mslot = SLOT_RESUME;
-            mkey = 0;
-            action = own_action >= 0 ? own_action : (a.actions ? a.actions[env] : 0);
-            own_action = -1;
-            active_resume = 0;
-          }
-        if (mkey == KEY_FAR)
-          {
-            if (gl == 0)
-              {
-                sim.rebase (sc->now);
-                mslot = slow_min (st, d);
-              }
-            __syncwarp (gmask);
-            mslot = __shfl_sync (gmask, mslot, leader);
-          }
-        int status = ST_CONTINUE;
-        int go = 1;
-        if (gl == 0) go = step_or_stop (st, sim, mslot, until, action, status) ? 1 : 0;
-        __syncwarp (gmask);
-        go = __shfl_sync (gmask, go, leader);
-        status = __shfl_sync (gmask, status, leader);
-        if (two_level && mslot >= st.NK)
-          {
-            const int fg = (mslot - st.NK) >> 5;
-            fg_rescan_coop<G> (st, d, fg, gl, gmask);
-            if (gl == fg % G) scan_flow_groups (st, d, gl, G, fts, fseq, fslot);
-          }
-        else if (mslot == fslot && mslot >= 0)
-          scan_flows (st, d, gl, G, fts, fseq, fslot);
-        if (!go) active = false;
-        return (!go && status == ST_PAUSE && ++steps_done < a.steps) ? 1 : 0;
-      };
-      while (__any_sync (FULL, active))
-        {
-          int paused = 0;
-          if (active) paused = one_event ();
-          __syncwarp (FULL);
-          answer_ww (paused, true);
-        }
-    }
-  else
   while (__any_sync (gmask, active))
     {
       uint32_t bk = KEY_IDLE;
@@ -2599,7 +2498,7 @@ prb_step_qnet (prb_env *env, int32_t n_steps, float eps, uint64_t seed, prb_step
       return rc;
     }
   /* the fused kernel holds the two-hidden-layer network only: one-hidden-layer models take the launch sequence below */
-  if (!env->qnet_unfused && env->qnet_mode == PRB_QNET_FUSED && env->dst.q_hidden == 2)
+  if (env->G == 32 && !env->qnet_unfused && env->qnet_mode == PRB_QNET_FUSED && env->dst.q_hidden == 2)
     {
       /* one launch: every warp answers the steps of its environment itself (k_advance, gym mode) */
       CUDA_TRY (cudaSetDevice (env->device));

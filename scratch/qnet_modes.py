@@ -1,5 +1,5 @@
 """agent-steps/s of prb_step_qnet by Q-network mode and batch size.  usage: qnet_modes.py [envs ...]"""
-import sys, json, os
+import sys, json
 sys.path.insert(0, "/root/repo")
 import numpy as np, torch
 from tests import common
@@ -10,7 +10,7 @@ for envs in [int(x) for x in sys.argv[1:]] or [4096, 16384, 65536]:
         cfg = common.env_config("abilene", num_envs=envs, simTime=60.0, load_factor=0.9, pingAsObs=0, activateUnderlayTraffic=1,
                                 agent_type="dqn_buffer")
         arrays = cfg.load()
-        env = BatchedRoutingEnv(cfg, arrays=arrays, lanes_per_env=int(os.environ.get("LANES", "0")))
+        env = BatchedRoutingEnv(cfg, arrays=arrays)
         deg = [len(n) for n in env.neighbors]
         env.qnet_load(qnet.pack_weights(qnet.init_weights(len(deg), deg, max(deg), seed=1)))
         env.qnet_set_mode(mode)

@@ -229,35 +229,3 @@ def test_one_hidden_layer_models_on_every_forward_path():
             assert np.abs(got[e, :k] - ref).max() < tol, (mode, np.abs(got[e, :k] - ref).max())
     env.check_errors()
     env.close()
-
-
-@pytest.mark.parametrize("lanes", [8, 16])
-def test_fused_loop_with_several_environments_per_warp(lanes):
-    """lanes_per_env = 8 / 16: the simulators of 4 / 2 environments share a warp and the whole warp evaluates the Q-network of
-    whichever of them pauses (k_advance, answer_ww).  Same environments, same Philox streams: every counter equals the
-    one-environment-per-warp loop, and so do the replay rings as multisets."""
-    from prisma_b200 import qnet
-    from prisma_b200.env import BatchedRoutingEnv
-    res = []
-    for g in (32, lanes):
-        cfg = common.env_config("abilene", num_envs=70, simTime=2.0, load_factor=1.5, pingAsObs=0, activateUnderlayTraffic=1)
-        arrays = cfg.load()
-        env = BatchedRoutingEnv(cfg, arrays=arrays, lanes_per_env=g)
-        degrees = [len(n) for n in env.neighbors]
-        env.qnet_load(qnet.pack_weights(qnet.init_weights(len(degrees), degrees, max(degrees), seed=7)))
-        env.replay_enable(rows_per_node=1 << 15)
-        env.step_qnet(150, eps=0.1, seed=4)
-        env.step_qnet(150, eps=0.1, seed=5)              # a second call starts with the pending steps of the first
-        c = env.counters()
-        env.check_errors(c)
-        counts, missed = env.replay_counts()
-        rows = [np.sort(env.replay_rows(i).view([("", np.float32)] * env.replay_rows(i).shape[1]), axis=0) for i in range(3)]
-        res.append((c, counts, missed, rows))
-        env.close()
-    a, b = res
-    for k in common.COUNTER_INTS:
-        assert np.array_equal(a[0][k], b[0][k]), k
-    assert np.array_equal(a[1], b[1]) and a[2] == b[2] == 0
-    for x, y in zip(a[3], b[3]):
-        assert np.array_equal(x, y)
-    assert int(a[0]["env_steps"].sum()) > 70 * 250
