@@ -1482,9 +1482,9 @@ launch_advance_g (prb_env *env, const LaunchArgs &a)
   const int n_envs = a.env_list ? a.n_list : st.E;
   const int blocks = (n_envs + envs_per_block - 1) / envs_per_block;
   size_t smem = (size_t) envs_per_block * st.blob_bytes;
-  /* shared-memory staging pays when the launch executes many events per env (run mode) and the blobs of
-   * a block fit; gym-mode launches execute a handful of events and work on the blob in place */
-  bool use_smem = (!GYM || (a.qw && a.steps >= 8)) && smem + sizeof (prb_step_rec) * envs_per_block + 1024 <= (size_t) env->max_smem;
+  /* shared-memory staging whenever the blobs of a block fit: it pays even for a single Gym step (a launch lasts as long
+   * as the environment that needs the most events to reach its next decision: 137 -> 114 us at 4096 Abilene environments) */
+  bool use_smem = smem + sizeof (prb_step_rec) * envs_per_block + 1024 <= (size_t) env->max_smem;
   if (use_smem)
     {
       auto k = flows_two_level (st) ? k_advance<G, LOG, GYM, true, true> : k_advance<G, LOG, GYM, true, false>;
